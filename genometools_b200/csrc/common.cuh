@@ -1,0 +1,97 @@
+// Device-side helpers shared by all kernels of libgtsfx_b200: packed-text access, the special
+// bitmap, k-mer codes and the 64-bit sort key.  sm_100a only.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define GTB_FULL 0xffffffffu
+#define GTB_POSMODE 0xffffffffu   // depth marker: group is ordered by text position
+
+// ---------------------------------------------------------------------------------------------
+// Text layout in HBM
+//   text : uint64_t words, symbols packed big-endian, BITS per symbol, SPW = 64/BITS per word:
+//          symbol i sits in bits [64-BITS*(i%SPW+1), 64-BITS*(i%SPW)) of word i/SPW.  For DNA
+//          (BITS=2) this IS GtEncseq's twobitencoding (src/core/encseq.c:73-81), uploaded as is.
+//          Other alphabets use BITS=8.  Special positions hold an arbitrary filler.
+//   mask : bitmap, bit (i&63) of word i>>6 (LSB first) is 1 iff position i holds a wildcard or
+//          separator; all bits >= totallength are 1 (the virtual end is a special, GT_UNIQUEINT,
+//          src/core/encseq.h:640).
+// Both arrays are padded with two extra words so a 64-bit window may start at any position <= n.
+// ---------------------------------------------------------------------------------------------
+template <int BITS>
+struct Text {
+  const uint64_t *__restrict__ w;
+  const uint64_t *__restrict__ m;
+  static constexpr int SPW = 64 / BITS;
+  static constexpr int W = 56 / BITS;   // symbols per sort key (low byte of the key is a tag)
+
+  // 64 bits of text starting at symbol p (first symbol in the most significant bits)
+  __device__ __forceinline__ uint64_t window(uint64_t p) const {
+    const uint64_t i = p / SPW;
+    const unsigned off = (unsigned)(p % SPW) * BITS;
+    const uint64_t hi = __ldg(w + i), lo = __ldg(w + i + 1);
+    return off ? (hi << off) | (lo >> (64 - off)) : hi;
+  }
+  // bit j = 1 iff position p+j is special, j = 0..63
+  __device__ __forceinline__ uint64_t maskwin(uint64_t p) const {
+    const uint64_t i = p >> 6;
+    const unsigned s = (unsigned)(p & 63);
+    const uint64_t a = __ldg(m + i), b = __ldg(m + i + 1);
+    return s ? (a >> s) | (b << (64 - s)) : a;
+  }
+  // number of real symbols from p up to the next special, capped at 64
+  __device__ __forceinline__ unsigned reallen(uint64_t p) const {
+    const uint64_t mw = maskwin(p);
+    return mw ? (unsigned)(__ffsll((long long)mw) - 1) : 64u;
+  }
+};
+
+// Sort key of the suffix whose next unread symbol is at position q (= start + depth):
+//   bits 63..8 : the next W symbols, positions at/after the first special padded with ones
+//   bits  7..0 : W - (number of real symbols among them)   (0 = full window, order still open)
+// Comparing (key, start position) reproduces the reference order: a key cut
+// short by a special is larger than every real continuation, and two suffixes cut at the same depth
+// with equal real prefixes are ordered by position.
+template <int BITS>
+__device__ __forceinline__ uint64_t make_key(const Text<BITS> &T, uint64_t q) {
+  constexpr int W = Text<BITS>::W;
+  const uint64_t mw = T.maskwin(q);
+  unsigned avail = mw ? (unsigned)(__ffsll((long long)mw) - 1) : 64u;
+  if (avail > (unsigned)W) avail = W;
+  uint64_t x = T.window(q) >> 8;             // W symbols in bits 55..0
+  if (avail < (unsigned)W) {
+    const unsigned padbits = (W - avail) * BITS;   // 1..56
+    x |= (~0ull) >> (64 - padbits);
+  }
+  return (x << 8) | (uint64_t)(W - avail);
+}
+
+// lcp contribution of two keys taken at the same depth: number of equal leading real symbols
+template <int BITS>
+__device__ __forceinline__ unsigned key_common(uint64_t ka, uint64_t kb) {
+  constexpr int W = Text<BITS>::W;
+  const uint64_t x = ka ^ kb;
+  unsigned common = x ? (unsigned)__clzll((long long)x) / BITS : (unsigned)W;
+  if (common > (unsigned)W) common = W;
+  const unsigned aa = W - (unsigned)(ka & 0xff), ab = W - (unsigned)(kb & 0xff);
+  common = common < aa ? common : aa;
+  return common < ab ? common : ab;
+}
+
+// Code arithmetic (src/match/kmercodes.h:24-46 for sigma = 4; src/match/initbasepower.c:71-106 for
+// the general base-sigma form).  pw[i] = sigma^i.
+struct CodeParams {
+  unsigned sigma, pl;
+  int pow2;                 // sigma == 1 << BITS: codes are plain bit fields
+  uint64_t pw[34];
+};
+
+template <int BITS>
+__device__ __forceinline__ uint64_t prefix_value(uint64_t win, unsigned len, const CodeParams &cp) {
+  // value of the first len symbols of the window read as a base-sigma number
+  if (len == 0) return 0;
+  if (cp.pow2) return win >> (64 - BITS * len);
+  uint64_t v = 0;
+  for (unsigned k = 0; k < len; ++k) v = v * cp.sigma + ((win >> (64 - BITS * (k + 1))) & ((1u << BITS) - 1));
+  return v;
+}

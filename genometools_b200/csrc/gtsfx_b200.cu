@@ -1,0 +1,1485 @@
+// libgtsfx_b200: sm_100a device layer for GenomeTools' enhanced-suffix-array construction path.
+// See include/gtsfx_b200.h for the C ABI and DESIGN.md for the data layout and kernel list.
+//
+// Pipeline per context (one CUDA stream, everything resident in HBM):
+//   open   : upload packed text, build special bitmap (k_mask_*, k_pack_bytes)
+//   count  : k_count (regular pl-mers) + k_padded (special-padded suffixes) -> histogram,
+//            scan -> leftborder; padded list radix-sorted once
+//   part   : k_scatter (regular suffixes into buckets), k_place_padded, k_sort_buckets (warp-level
+//            register bitonic sort of each bucket on the next 28 bases + fused in-bucket LCP),
+//            refinement rounds for buckets that are too large or still tied (segmented LSD radix
+//            sort on deeper text windows), k_boundary (LCP across bucket borders), k_widen.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+#include "../../include/gtsfx_b200.h"
+#include "common.cuh"
+#include "prims.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+  return -1;
+}
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess)                                                                         \
+      return set_error("CUDA error %s at %s:%d (%s)", cudaGetErrorString(e_), __FILE__, __LINE__, #call); \
+  } while (0)
+
+extern "C" const char *gtb200_last_error(void) { return g_err; }
+
+extern "C" int gtb200_device_count(void) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) return set_error("cudaGetDeviceCount: %s", cudaGetErrorString(e));
+  return n;
+}
+
+// ---------------------------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------------------------
+enum KClass { KC_PREP = 0, KC_COUNT, KC_SCAN, KC_PADDED, KC_SCATTER, KC_SORT, KC_REFINE, KC_RADIX,
+              KC_BOUNDARY, KC_WIDEN, KC_TAIL, KC_NUM };
+static const char *const kclass_names[KC_NUM] = {"prep", "count", "scan", "padded", "scatter", "sort_lcp",
+                                                 "refine", "radix", "boundary", "widen", "tail"};
+
+struct PartStats {          // lives in device memory, mirrored to pinned host memory at sync points
+  unsigned long long lcpsum;
+  unsigned long long llv_count;
+  unsigned long long fb_elems;
+  unsigned long long longest;
+  unsigned long long scan_total;
+  unsigned long long scan_total2;
+  unsigned int maxdepth;
+  unsigned int fb_buckets;
+  unsigned int largest;
+  unsigned int pad_;
+};
+
+struct ProfEvent { int cls; cudaEvent_t a, b; };
+
+struct gtb200_ctx {
+  int device;
+  cudaStream_t stream;
+  unsigned bits;
+  CodeParams cp;
+  uint64_t n;
+  uint64_t ntextwords, nmaskwords;
+  uint64_t *d_text, *d_mask;
+  gtb200_range *d_ranges;
+  uint64_t nranges;
+  uint32_t *d_rangeoff;      // [nranges+1] exclusive scan of range lengths (tail paging)
+  uint64_t numcodes, numspecialcodes, numdist;
+  uint32_t *d_lb;            // [numcodes+1] bucket start offsets (.bck leftborder)
+  uint32_t *d_cursor;        // [numcodes]
+  uint32_t *d_csc, *d_dist;
+  uint64_t padcap, npadded;
+  uint64_t *d_padkey;        // (code << 6) | (pl - reallen), sorted
+  uint32_t *d_padpos;
+  uint64_t specialchars, nsort, largestbucket;
+  bool counted;
+  uint32_t sort_maxbucket;   // buckets above this size take the refinement path (testing knob)
+  // per part
+  uint64_t cap_width;
+  uint32_t *d_sa;
+  uint8_t *d_lcp;
+  uint64_t *d_suf64;
+  uint32_t *d_fbbits;
+  uint64_t cap_fbwords;
+  gtb200_largelcp *d_llv;    // sorted records of the last part
+  uint64_t cap_llv;
+  uint64_t part_offset, part_width, part_nllv;
+  PartStats *d_stats, *h_stats;
+  // scratch
+  uint32_t *d_tilesums;
+  uint64_t cap_tilesums;
+  void *d_scratch;
+  size_t cap_scratch;
+  // profiling
+  bool prof_on;
+  std::vector<ProfEvent> pending;
+  std::vector<cudaEvent_t> evpool;
+  double prof_ms[KC_NUM];
+  uint64_t prof_launches[KC_NUM];
+};
+
+static int prof_fold(gtb200_ctx *c) {
+  if (c->pending.empty()) return 0;
+  CK(cudaEventSynchronize(c->pending.back().b));
+  for (auto &p : c->pending) {
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, p.a, p.b));
+    c->prof_ms[p.cls] += ms;
+    c->evpool.push_back(p.a);
+    c->evpool.push_back(p.b);
+  }
+  c->pending.clear();
+  return 0;
+}
+
+static cudaEvent_t prof_event(gtb200_ctx *c) {
+  if (!c->evpool.empty()) {
+    cudaEvent_t e = c->evpool.back();
+    c->evpool.pop_back();
+    return e;
+  }
+  cudaEvent_t e;
+  cudaEventCreate(&e);
+  return e;
+}
+
+struct ProfScope {
+  gtb200_ctx *c;
+  ProfEvent ev;
+  bool on;
+  ProfScope(gtb200_ctx *c_, int cls, int launches = 1) : c(c_), on(c_->prof_on) {
+    c->prof_launches[cls] += launches;
+    if (on) {
+      ev.cls = cls;
+      ev.a = prof_event(c);
+      ev.b = prof_event(c);
+      cudaEventRecord(ev.a, c->stream);
+    }
+  }
+  ~ProfScope() {
+    if (on) {
+      cudaEventRecord(ev.b, c->stream);
+      c->pending.push_back(ev);
+      if (c->pending.size() > 2048) prof_fold(c);
+    }
+  }
+};
+
+static inline unsigned grid_for(uint64_t n, unsigned per_block) {
+  uint64_t g = (n + per_block - 1) / per_block;
+  if (g == 0) g = 1;
+  return (unsigned)g;
+}
+
+static int ensure_scratch(gtb200_ctx *c, size_t bytes) {
+  if (bytes <= c->cap_scratch) return 0;
+  if (c->d_scratch) CK(cudaFree(c->d_scratch));
+  c->d_scratch = nullptr;
+  c->cap_scratch = 0;
+  CK(cudaMalloc(&c->d_scratch, bytes));
+  c->cap_scratch = bytes;
+  return 0;
+}
+
+static int ensure_tilesums(gtb200_ctx *c, uint64_t ntiles) {
+  if (ntiles <= c->cap_tilesums) return 0;
+  if (c->d_tilesums) CK(cudaFree(c->d_tilesums));
+  c->d_tilesums = nullptr;
+  c->cap_tilesums = 0;
+  CK(cudaMalloc(&c->d_tilesums, (ntiles + 1) * sizeof(uint32_t)));
+  c->cap_tilesums = ntiles;
+  return 0;
+}
+
+// exclusive scan on the context's stream; total (64-bit) lands in *d_total if non-null
+static int device_scan(gtb200_ctx *c, const uint32_t *in, uint32_t *out, uint64_t n, int append_total,
+                       unsigned long long *d_total, int cls = KC_SCAN) {
+  if (n == 0) {
+    if (d_total) CK(cudaMemsetAsync(d_total, 0, sizeof *d_total, c->stream));
+    return 0;
+  }
+  const uint64_t ntiles = (n + SC_TILE - 1) / SC_TILE;
+  if (ensure_tilesums(c, ntiles)) return -1;
+  ProfScope ps(c, cls, 3);
+  k_scan_tilesums<<<(unsigned)ntiles, SC_THREADS, 0, c->stream>>>(in, n, c->d_tilesums);
+  k_scan_spine<<<1, SC_THREADS, 0, c->stream>>>(c->d_tilesums, (uint32_t)ntiles, d_total);
+  k_scan_apply<<<(unsigned)ntiles, SC_THREADS, 0, c->stream>>>(in, out, n, c->d_tilesums, append_total);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+// Stable LSD radix sort of n pairs on key bits [bit_lo, bit_hi).  keys_in/vals_in are left intact;
+// (kA,vA) and (kB,vB) are ping-pong buffers, hist holds 256*nblocks+1 words.  Result pointers out.
+static int device_radix_sort(gtb200_ctx *c, const uint64_t *keys_in, const uint32_t *vals_in, uint64_t *kA,
+                             uint32_t *vA, uint64_t *kB, uint32_t *vB, uint32_t *hist, uint32_t n, int bit_lo,
+                             int bit_hi, const uint64_t **keys_out, const uint32_t **vals_out) {
+  const uint64_t *ksrc = keys_in;
+  const uint32_t *vsrc = vals_in;
+  uint64_t *kdst = kA;
+  uint32_t *vdst = vA;
+  const uint32_t nblocks = grid_for(n, RS_TILE);
+  for (int shift = bit_lo; shift < bit_hi; shift += 8) {
+    {
+      ProfScope ps(c, KC_RADIX, 1);
+      k_radix_hist<<<nblocks, RS_THREADS, 0, c->stream>>>(ksrc, n, shift, hist, nblocks);
+    }
+    if (device_scan(c, hist, hist, 256ull * nblocks, 0, nullptr, KC_RADIX)) return -1;
+    {
+      ProfScope ps(c, KC_RADIX, 1);
+      k_radix_scatter<<<nblocks, RS_THREADS, 0, c->stream>>>(ksrc, vsrc, kdst, vdst, n, shift, hist, nblocks);
+    }
+    ksrc = kdst;
+    vsrc = vdst;
+    if (kdst == kA) { kdst = kB; vdst = vB; } else { kdst = kA; vdst = vA; }
+  }
+  CK(cudaGetLastError());
+  *keys_out = ksrc;
+  *vals_out = vsrc;
+  return 0;
+}
+
+static inline int bits_for(uint64_t maxvalue) {
+  int b = 1;
+  while (b < 64 && (maxvalue >> b) != 0) ++b;
+  return b;
+}
+
+// ---------------------------------------------------------------------------------------------
+// open(): bitmap and packing kernels
+// ---------------------------------------------------------------------------------------------
+
+// mask words that lie entirely or partly at/after position n are forced to ones
+__global__ void k_mask_tail(uint64_t *mask, uint64_t n, uint64_t nmaskwords) {
+  const uint64_t i = (n >> 6) + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nmaskwords) return;
+  if (i == (n >> 6)) mask[i] |= ~0ull << (n & 63);
+  else mask[i] = ~0ull;
+}
+
+// one warp per special range: set bits [start,end)
+__global__ void k_mask_from_ranges(uint64_t *mask, const gtb200_range *__restrict__ ranges, uint64_t nranges) {
+  const uint64_t gw = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nw = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  for (uint64_t r = gw; r < nranges; r += nw) {
+    const uint64_t s = ranges[r].start, e = ranges[r].end;   // e > s
+    const uint64_t w0 = s >> 6, w1 = (e - 1) >> 6;
+    for (uint64_t wi = w0 + lane; wi <= w1; wi += 32) {
+      uint64_t bits = ~0ull;
+      if (wi == w0) bits &= ~0ull << (s & 63);
+      if (wi == w1) bits &= ~0ull >> (63 - ((e - 1) & 63));
+      if (wi == w0 || wi == w1) atomicOr((unsigned long long *)&mask[wi], (unsigned long long)bits);
+      else mask[wi] = ~0ull;   // interior words belong to this range alone
+    }
+  }
+}
+
+// bytes (one symbol per byte, 254/255 special) -> packed text words + mask; one thread per 64 positions
+template <int BITS>
+__global__ void k_pack_bytes(const uint8_t *__restrict__ enc, uint64_t n, uint64_t *__restrict__ text,
+                             uint64_t *__restrict__ mask, uint64_t nchunks) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nchunks) return;
+  constexpr int SPW = 64 / BITS;
+  const uint64_t p0 = t << 6;
+  uint64_t mw = 0;
+  for (int wq = 0; wq < 64 / SPW; ++wq) {
+    uint64_t word = 0;
+    for (int k = 0; k < SPW; ++k) {
+      const uint64_t p = p0 + (uint64_t)wq * SPW + k;
+      uint8_t ch = p < n ? enc[p] : (uint8_t)255;
+      const bool sp = ch >= 254;
+      if (sp) { mw |= 1ull << (wq * SPW + k); ch = 0; }
+      word |= (uint64_t)ch << (64 - BITS * (k + 1));
+    }
+    text[t * (64 / SPW) + wq] = word;
+  }
+  mask[t] = mw;
+}
+
+// range derivation from the bitmap (byte input): count run starts per mask word
+__global__ void k_runs_count(const uint64_t *__restrict__ mask, uint64_t n, uint64_t nwords, uint32_t *cnt,
+                             uint32_t *popc) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nwords) return;
+  uint64_t mw = mask[t];
+  const uint64_t lo = t << 6;
+  if (lo + 64 > n) mw &= (n > lo) ? (~0ull >> (64 - (n - lo))) : 0ull;   // positions >= n are not ranges
+  const uint64_t prevbit = t ? (mask[t - 1] >> 63) : 0ull;
+  const uint64_t starts = mw & ~((mw << 1) | prevbit);
+  cnt[t] = __popcll(starts);
+  popc[t] = __popcll(mw);
+}
+
+__global__ void k_runs_write(const uint64_t *__restrict__ mask, uint64_t n, uint64_t nwords,
+                             const uint32_t *__restrict__ off, gtb200_range *ranges) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nwords) return;
+  uint64_t mw = mask[t];
+  const uint64_t lo = t << 6;
+  if (lo + 64 > n) mw &= (n > lo) ? (~0ull >> (64 - (n - lo))) : 0ull;
+  const uint64_t prevbit = t ? (mask[t - 1] >> 63) : 0ull;
+  uint64_t starts = mw & ~((mw << 1) | prevbit);
+  uint32_t o = off[t];
+  while (starts) {
+    const int b = __ffsll((long long)starts) - 1;
+    starts &= starts - 1;
+    // walk to the end of the run (runs are long only for N-blocks; bounded by n)
+    uint64_t p = lo + b, wi = t;
+    uint64_t cur = ~mw >> b;    // zero bits mark the end, relative to b
+    uint64_t e;
+    for (;;) {
+      if (cur) { e = p + (__ffsll((long long)cur) - 1); break; }
+      // run continues into the next word
+      wi++;
+      p = wi << 6;
+      if (p >= n) { e = n; break; }
+      uint64_t nm = mask[wi];
+      if (p + 64 > n) nm &= ~0ull >> (64 - (n - p));
+      cur = ~nm;
+    }
+    if (e > n) e = n;
+    ranges[o].start = lo + b;
+    ranges[o].end = e;
+    o++;
+  }
+}
+
+__global__ void k_range_lengths(const gtb200_range *__restrict__ ranges, uint64_t nranges, uint32_t *len) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < nranges) len[t] = (uint32_t)(ranges[t].end - ranges[t].start);
+}
+
+// ---------------------------------------------------------------------------------------------
+// phase 1: counting
+// ---------------------------------------------------------------------------------------------
+
+// One thread per 32 consecutive positions.  Counts suffixes whose first pl symbols are all real.
+// MODE 0: histogram (hist[code]++).  MODE 1: scatter (sa[cursor[code]++ - partoffset] = pos) for
+// codes in [mincode,maxcode].
+template <int BITS, int MODE>
+__global__ void __launch_bounds__(256) k_kmers(Text<BITS> T, CodeParams cp, uint64_t n, uint32_t *__restrict__ table,
+                                                uint32_t *__restrict__ sa, uint64_t mincode, uint64_t maxcode,
+                                                uint32_t partoffset) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t p0 = t << 5;
+  if (p0 >= n) return;
+  const unsigned pl = cp.pl;
+  const uint64_t mw = T.maskwin(p0);
+  const uint64_t plmask = (pl >= 64) ? ~0ull : ((1ull << pl) - 1ull);
+  if (BITS == 2) {
+    const uint64_t hi = __ldg(T.w + t), lo = __ldg(T.w + t + 1);
+#pragma unroll 8
+    for (int i = 0; i < 32; ++i) {
+      if (((mw >> i) & plmask) != 0) continue;
+      const uint64_t win = i ? (hi << (2 * i)) | (lo >> (64 - 2 * i)) : hi;
+      const uint64_t code = prefix_value<BITS>(win, pl, cp);
+      if (MODE == 0) {
+        atomicAdd(&table[code], 1u);
+      } else if (code >= mincode && code <= maxcode) {
+        const uint32_t slot = atomicAdd(&table[code], 1u);
+        sa[slot - partoffset] = (uint32_t)(p0 + i);
+      }
+    }
+  } else {
+    for (int i = 0; i < 32; ++i) {
+      if (((mw >> i) & plmask) != 0) continue;
+      const uint64_t code = prefix_value<BITS>(T.window(p0 + i), pl, cp);
+      if (MODE == 0) {
+        atomicAdd(&table[code], 1u);
+      } else if (code >= mincode && code <= maxcode) {
+        const uint32_t slot = atomicAdd(&table[code], 1u);
+        sa[slot - partoffset] = (uint32_t)(p0 + i);
+      }
+    }
+  }
+}
+
+// Special-padded suffixes: for every special range (and the virtual end at n) the up to pl-1
+// positions directly left of it.  Thread k handles range k (k == nranges: the end of the text).
+// PASS 0: number of such suffixes per range.  PASS 1: counters + list entries at off[k].
+template <int BITS, int PASS>
+__global__ void k_padded(Text<BITS> T, CodeParams cp, uint64_t n, const gtb200_range *__restrict__ ranges,
+                         uint64_t nranges, uint32_t *__restrict__ cntoff, uint32_t *__restrict__ hist,
+                         uint32_t *__restrict__ csc, uint32_t *__restrict__ dist, uint64_t *__restrict__ padkey,
+                         uint32_t *__restrict__ padpos) {
+  const uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > nranges) return;
+  const uint64_t s = k < nranges ? ranges[k].start : n;
+  const uint64_t prev_end = k ? ranges[k - 1].end : 0;
+  const unsigned pl = cp.pl;
+  uint64_t avail = s - prev_end;
+  if (k == nranges && nranges && ranges[nranges - 1].end >= n) avail = 0;
+  const unsigned cnt = (unsigned)(avail < pl - 1 ? avail : pl - 1);
+  if (PASS == 0) { cntoff[k] = cnt; return; }
+  const uint32_t off = cntoff[k];
+  for (unsigned j = 1; j <= cnt; ++j) {         // suffix s-j has exactly j real symbols
+    const uint64_t p = s - j;
+    const uint64_t pv = prefix_value<BITS>(T.window(p), j, cp);
+    const uint64_t fill = cp.pw[pl - j] - 1;    // pl-j digits of value sigma-1
+    const uint64_t code = pv * (fill + 1) + fill;
+    atomicAdd(&hist[code], 1u);
+    atomicAdd(&csc[(code - (cp.sigma - 1)) / cp.sigma], 1u);
+    if (j + 1 < pl) {
+      uint64_t doff = 0;
+      for (unsigned i = 1; i < j; ++i) doff += cp.pw[i];
+      atomicAdd(&dist[doff + pv], 1u);
+    }
+    padkey[off + (cnt - j)] = (code << 6) | (uint64_t)(pl - j);
+    padpos[off + (cnt - j)] = (uint32_t)p;
+  }
+}
+
+__global__ void k_max_u32(const uint32_t *__restrict__ a, uint64_t n, unsigned int *out) {
+  uint32_t m = 0;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    m = max(m, a[i]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(GTB_FULL, m, o));
+  if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
+}
+
+__global__ void k_sum_u32(const uint32_t *__restrict__ a, uint64_t n, unsigned long long *out) {
+  unsigned long long s = 0;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    s += a[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(GTB_FULL, s, o);
+  if ((threadIdx.x & 31) == 0 && s) atomicAdd(out, s);
+}
+
+// ---------------------------------------------------------------------------------------------
+// LCP emission
+// ---------------------------------------------------------------------------------------------
+struct PartOut {
+  uint32_t *sa;
+  uint8_t *lcp;
+  gtb200_largelcp *llv;      // unordered append buffer (refinement only)
+  PartStats *stats;
+  uint32_t partoffset;
+};
+
+__device__ __forceinline__ void emit_large(const PartOut &o, uint32_t r, uint32_t value) {
+  const unsigned long long slot = atomicAdd(&o.stats->llv_count, 1ull);
+  o.llv[slot].position = (uint64_t)o.partoffset + r;
+  o.llv[slot].value = value;
+}
+
+// ---------------------------------------------------------------------------------------------
+// phase 2: padded placement, bucket sort
+// ---------------------------------------------------------------------------------------------
+
+// padded list is sorted by (code, pl-L) with ascending positions inside equal keys: entry i of
+// code c goes to the right end of bucket c (reference order: src/match/sfx-suffixer.c:476-516)
+__global__ void k_place_padded(const uint64_t *__restrict__ padkey, const uint32_t *__restrict__ padpos,
+                               uint64_t npadded, const uint32_t *__restrict__ lb, const uint32_t *__restrict__ csc,
+                               unsigned sigma, unsigned pl, uint64_t mincode, uint64_t maxcode, PartOut out) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npadded) return;
+  const uint64_t key = padkey[i];
+  const uint64_t code = key >> 6;
+  if (code < mincode || code > maxcode) return;
+  // first list index with this code
+  uint64_t lo = 0, hi = i;
+  const uint64_t target = code << 6;
+  while (lo < hi) {
+    const uint64_t mid = (lo + hi) >> 1;
+    if (padkey[mid] < target) lo = mid + 1; else hi = mid;
+  }
+  const uint32_t npad = csc[(code - (sigma - 1)) / sigma];
+  const uint32_t r = lb[code + 1] - npad + (uint32_t)(i - lo) - out.partoffset;
+  const uint32_t L = pl - (uint32_t)(key & 63);
+  out.sa[r] = padpos[i];
+  out.lcp[r] = (uint8_t)L;               // own number of real symbols (src/match/sfx-lcpvalues.c:125-215);
+  if (r + out.partoffset > lb[code])     // a bucket-first entry is overwritten by k_boundary
+    atomicMax(&out.stats->maxdepth, L);
+}
+
+template <int E>
+struct WarpSorter {
+  __device__ static __forceinline__ bool greater(uint64_t ka, uint32_t va, uint64_t kb, uint32_t vb) {
+    return ka > kb || (ka == kb && va > vb);
+  }
+  // bitonic sort of 32*E (key,val) pairs held as element index = e*32 + lane
+  __device__ static __forceinline__ void sort(uint64_t (&k)[E], uint32_t (&v)[E], int lane) {
+#pragma unroll
+    for (int size = 2; size <= 32 * E; size <<= 1) {
+#pragma unroll
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        if (stride >= 32) {
+          const int es = stride >> 5;
+#pragma unroll
+          for (int e = 0; e < E; ++e) {
+            if ((e & es) == 0) {
+              const bool asc = (((e * 32) & size) == 0);
+              const bool gt = greater(k[e], v[e], k[e | es], v[e | es]);
+              if (gt == asc) {
+                const uint64_t tk = k[e]; k[e] = k[e | es]; k[e | es] = tk;
+                const uint32_t tv = v[e]; v[e] = v[e | es]; v[e | es] = tv;
+              }
+            }
+          }
+        } else {
+#pragma unroll
+          for (int e = 0; e < E; ++e) {
+            const uint64_t ok = __shfl_xor_sync(GTB_FULL, k[e], stride);
+            const uint32_t ov = __shfl_xor_sync(GTB_FULL, v[e], stride);
+            const bool asc = (((e * 32 + lane) & size) == 0);
+            const bool lower = ((lane & stride) == 0);
+            const bool mine_gt = greater(k[e], v[e], ok, ov);
+            const bool take = (lower == asc) ? mine_gt : !mine_gt;
+            if (take) { k[e] = ok; v[e] = ov; }
+          }
+        }
+      }
+    }
+  }
+};
+
+// Sorts one bucket of cnt <= 32*E regular suffixes held by one warp and writes order + in-bucket
+// LCP.  Returns false (nothing written) if two suffixes agree on all pl+W symbols.
+template <int BITS, int E>
+__device__ __forceinline__ bool warp_sort_bucket(const Text<BITS> &T, const PartOut &out, uint32_t start, uint32_t cnt,
+                                                 unsigned pl, int lane, unsigned long long &sum, uint32_t &mx) {
+  uint64_t k[E];
+  uint32_t v[E];
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    const uint32_t i = e * 32 + lane;
+    if (i < cnt) {
+      v[e] = out.sa[start + i];
+      k[e] = make_key<BITS>(T, (uint64_t)v[e] + pl);
+    } else {
+      v[e] = 0xffffffffu;
+      k[e] = ~0ull;
+    }
+  }
+  WarpSorter<E>::sort(k, v, lane);
+  uint32_t l[E];
+  bool tie = false;
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    uint64_t pk = __shfl_up_sync(GTB_FULL, k[e], 1);
+    const uint64_t last = (e > 0) ? __shfl_sync(GTB_FULL, k[e > 0 ? e - 1 : 0], 31) : 0ull;
+    if (lane == 0) pk = last;
+    const uint32_t i = e * 32 + lane;
+    l[e] = 0;
+    if (i >= 1 && i < cnt) {
+      if (pk == k[e] && (k[e] & 0xff) == 0) tie = true;
+      l[e] = pl + key_common<BITS>(pk, k[e]);
+    }
+  }
+  if (__any_sync(GTB_FULL, tie)) return false;
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    const uint32_t i = e * 32 + lane;
+    if (i < cnt) {
+      out.sa[start + i] = v[e];
+      if (i >= 1) {
+        out.lcp[start + i] = (uint8_t)l[e];
+        sum += l[e];
+        mx = max(mx, l[e]);
+      }
+    }
+  }
+  return true;
+}
+
+#define SORT_MAXBUCKET 256
+
+template <int BITS>
+__global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out, const uint32_t *__restrict__ lb,
+                                                      const uint32_t *__restrict__ cursor, uint64_t mincode,
+                                                      uint64_t maxcode, unsigned pl, uint32_t *__restrict__ fbbits,
+                                                      uint32_t maxbucket) {
+  const int lane = threadIdx.x & 31;
+  const uint64_t gw = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nw = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  unsigned long long sum = 0;
+  uint32_t mx = 0;
+  for (uint64_t c = mincode + gw; c <= maxcode; c += nw) {
+    const uint32_t b0 = lb[c];
+    const uint32_t cnt = cursor[c] - b0;
+    if (cnt <= 1) continue;
+    const uint32_t start = b0 - out.partoffset;
+    bool ok = false;
+    if (cnt > maxbucket) ok = false;
+    else if (cnt <= 32) ok = warp_sort_bucket<BITS, 1>(T, out, start, cnt, pl, lane, sum, mx);
+    else if (cnt <= 64) ok = warp_sort_bucket<BITS, 2>(T, out, start, cnt, pl, lane, sum, mx);
+    else if (cnt <= 128) ok = warp_sort_bucket<BITS, 4>(T, out, start, cnt, pl, lane, sum, mx);
+    else if (cnt <= SORT_MAXBUCKET) ok = warp_sort_bucket<BITS, 8>(T, out, start, cnt, pl, lane, sum, mx);
+    if (!ok && lane == 0) {
+      const uint64_t rel = c - mincode;
+      atomicOr(&fbbits[rel >> 5], 1u << (rel & 31));
+      atomicAdd(&out.stats->fb_elems, (unsigned long long)cnt);
+      atomicAdd(&out.stats->fb_buckets, 1u);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sum += __shfl_xor_sync(GTB_FULL, sum, o);
+    mx = max(mx, __shfl_xor_sync(GTB_FULL, mx, o));
+  }
+  if (lane == 0) {
+    if (sum) atomicAdd(&out.stats->lcpsum, sum);
+    if (mx) atomicMax(&out.stats->maxdepth, mx);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// refinement path (buckets > SORT_MAXBUCKET or still tied after pl+W symbols)
+// ---------------------------------------------------------------------------------------------
+__global__ void k_fb_popc(const uint32_t *__restrict__ fbbits, uint64_t nwords, uint32_t *cnt) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < nwords) cnt[t] = __popc(fbbits[t]);
+}
+
+__global__ void k_fb_codes(const uint32_t *__restrict__ fbbits, uint64_t nwords, const uint32_t *__restrict__ off,
+                           uint64_t mincode, const uint32_t *__restrict__ lb, const uint32_t *__restrict__ cursor,
+                           uint32_t *codes, uint32_t *sizes) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nwords) return;
+  uint32_t bits = fbbits[t];
+  uint32_t o = off[t];
+  while (bits) {
+    const int b = __ffs(bits) - 1;
+    bits &= bits - 1;
+    const uint64_t c = mincode + (t << 5) + b;
+    codes[o] = (uint32_t)c;
+    sizes[o] = cursor[c] - lb[c];
+    o++;
+  }
+}
+
+// one warp per flagged bucket: list entries in ascending suffix-array index
+__global__ void k_fb_fill(const uint32_t *__restrict__ codes, const uint32_t *__restrict__ eoff, uint32_t nb,
+                          const uint32_t *__restrict__ lb, const uint32_t *__restrict__ cursor, uint32_t partoffset,
+                          unsigned pl, uint32_t *idx, uint32_t *gs, uint32_t *dep) {
+  const uint64_t gw = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nw = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  for (uint64_t b = gw; b < nb; b += nw) {
+    const uint32_t c = codes[b];
+    const uint32_t start = lb[c] - partoffset, cnt = cursor[c] - lb[c], o = eoff[b];
+    for (uint32_t i = lane; i < cnt; i += 32) {
+      idx[o + i] = start + i;
+      gs[o + i] = start;
+      dep[o + i] = pl;
+    }
+  }
+}
+
+template <int BITS>
+__global__ void k_fb_keys(Text<BITS> T, const uint32_t *__restrict__ sa, const uint32_t *__restrict__ idx,
+                          const uint32_t *__restrict__ dep, uint32_t A, uint64_t *keys, uint32_t *posbuf,
+                          uint32_t *vals) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= A) return;
+  const uint32_t p = sa[idx[j]];
+  const uint32_t d = dep[j];
+  posbuf[j] = p;
+  keys[j] = (d == GTB_POSMODE) ? (uint64_t)p : make_key<BITS>(T, (uint64_t)p + d);
+  vals[j] = j;
+}
+
+__global__ void k_fb_gather_gs(const uint32_t *__restrict__ vals, const uint32_t *__restrict__ gs, uint32_t A,
+                               uint64_t *keys2) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < A) keys2[j] = gs[vals[j]];
+}
+
+// after the segmented sort: write the new order, emit LCPs of newly separated neighbours, flag heads
+template <int BITS>
+__global__ void k_fb_regroup(PartOut out, const uint32_t *__restrict__ vals, const uint32_t *__restrict__ idx,
+                             const uint32_t *__restrict__ gs, const uint32_t *__restrict__ dep,
+                             const uint64_t *__restrict__ keys, const uint32_t *__restrict__ posbuf, uint32_t A,
+                             uint32_t *head, uint32_t *newdep) {
+  constexpr int W = Text<BITS>::W;
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long sum = 0;
+  uint32_t mx = 0;
+  if (j < A) {
+    const uint32_t e = vals[j];
+    const uint32_t g = gs[e], d = dep[e];
+    const uint64_t kc = keys[e];
+    const uint32_t r = idx[j];
+    out.sa[r] = posbuf[e];
+    bool hd = true;
+    if (j > 0) {
+      const uint32_t e0 = vals[j - 1];
+      const uint64_t k0 = keys[e0];
+      if (gs[e0] == g) {
+        if (d == GTB_POSMODE) {
+          hd = true;                        // positions are unique; lcp was emitted when the tie was found
+        } else if (k0 != kc) {
+          const uint32_t l = d + key_common<BITS>(k0, kc);
+          out.lcp[r] = (uint8_t)(l < 255 ? l : 255);
+          if (l >= 255) emit_large(out, r, l);
+          sum = l; mx = l;
+        } else if ((kc & 0xff) != 0) {      // same real symbols, both cut by a special at the same depth
+          const uint32_t l = d + (W - (uint32_t)(kc & 0xff));
+          out.lcp[r] = (uint8_t)(l < 255 ? l : 255);
+          if (l >= 255) emit_large(out, r, l);
+          sum = l; mx = l;
+          hd = false;                       // stays one group, to be ordered by position
+        } else {
+          hd = false;                       // still tied on real symbols
+        }
+      }
+    }
+    head[j] = hd ? 1u : 0u;
+    newdep[j] = (d == GTB_POSMODE) ? GTB_POSMODE : ((kc & 0xff) ? GTB_POSMODE : d + W);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sum += __shfl_xor_sync(GTB_FULL, sum, o);
+    mx = max(mx, __shfl_xor_sync(GTB_FULL, mx, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (sum) atomicAdd(&out.stats->lcpsum, sum);
+    if (mx) atomicMax(&out.stats->maxdepth, mx);
+  }
+}
+
+// groupno = exclusive scan of head; head index table
+__global__ void k_fb_headpos(const uint32_t *__restrict__ head, const uint32_t *__restrict__ hscan, uint32_t A,
+                             uint32_t *headpos, const unsigned long long *__restrict__ ngroups) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < A && head[j]) headpos[hscan[j]] = j;
+  if (j == 0) headpos[*ngroups] = A;
+}
+
+__global__ void k_fb_finalize(const uint32_t *__restrict__ head, const uint32_t *__restrict__ hscan,
+                              const uint32_t *__restrict__ headpos, const uint32_t *__restrict__ idx, uint32_t A,
+                              uint32_t *keep, uint32_t *newgs) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= A) return;
+  const uint32_t g = hscan[j] + head[j] - 1;
+  const uint32_t hs = headpos[g], he = headpos[g + 1];
+  keep[j] = (he - hs) > 1 ? 1u : 0u;
+  newgs[j] = idx[hs];
+}
+
+__global__ void k_fb_compact(const uint32_t *__restrict__ keep, const uint32_t *__restrict__ kscan,
+                             const uint32_t *__restrict__ idx, const uint32_t *__restrict__ newgs,
+                             const uint32_t *__restrict__ newdep, uint32_t A, uint32_t *idx2, uint32_t *gs2,
+                             uint32_t *dep2) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= A || !keep[j]) return;
+  const uint32_t o = kscan[j];
+  idx2[o] = idx[j];
+  gs2[o] = newgs[j];
+  dep2[o] = newdep[j];
+}
+
+__global__ void k_llv_keys(const gtb200_largelcp *__restrict__ llv, uint32_t nl, uint64_t *keys, uint32_t *vals) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < nl) { keys[j] = llv[j].position; vals[j] = j; }
+}
+
+__global__ void k_llv_gather(const gtb200_largelcp *__restrict__ src, const uint32_t *__restrict__ vals, uint32_t nl,
+                             gtb200_largelcp *dst) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < nl) dst[j] = src[vals[j]];
+}
+
+// ---------------------------------------------------------------------------------------------
+// bucket boundaries, widening, tail
+// ---------------------------------------------------------------------------------------------
+
+// lcp of the first entry of every non-empty bucket with its left neighbour in the suffix array
+// (src/match/sfx-lcpvalues.c:91-111,591-693 compute the same value from codes and prefix indices)
+template <int BITS>
+__global__ void k_boundary(Text<BITS> T, PartOut out, const uint32_t *__restrict__ lb, uint64_t mincode,
+                           uint64_t maxcode, unsigned pl) {
+  const uint64_t c = mincode + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c > maxcode) return;
+  const uint32_t b0 = lb[c];
+  if (lb[c + 1] == b0) return;
+  const uint32_t r = b0 - out.partoffset;
+  if (r == 0) return;                       // first entry of the part: k_part_first
+  const uint32_t a = out.sa[r - 1], b = out.sa[r];
+  unsigned la = T.reallen(a), lbn = T.reallen(b);
+  const uint64_t x = T.window(a) ^ T.window(b);
+  unsigned common = x ? (unsigned)__clzll((long long)x) / BITS : 64u / BITS;
+  unsigned l = common < la ? common : la;
+  l = l < lbn ? l : lbn;
+  if (l > pl) l = pl;                       // cannot happen for different buckets; defensive
+  out.lcp[r] = (uint8_t)l;
+  if (lbn >= pl && l) atomicAdd(&out.stats->lcpsum, (unsigned long long)l);
+  if (l) atomicMax(&out.stats->maxdepth, l);
+}
+
+// first entry of a part that is not the first part: its left neighbour lives on another device /
+// in an earlier part, so the value is derived from codes and the padded list alone
+template <int BITS>
+__global__ void k_part_first(Text<BITS> T, CodeParams cp, PartOut out, const uint32_t *__restrict__ lb,
+                             uint64_t numcodes, const uint32_t *__restrict__ csc,
+                             const uint64_t *__restrict__ padkey, uint64_t npadded) {
+  if (blockIdx.x || threadIdx.x) return;
+  const uint32_t po = out.partoffset;
+  // cprev = max{x : lb[x] < po}; ccur = max{x : lb[x] <= po, x < numcodes}
+  uint64_t lo = 0, hi = numcodes;           // invariant lb[lo] < po
+  while (hi - lo > 1) {
+    const uint64_t mid = (lo + hi) >> 1;
+    if (lb[mid] < po) lo = mid; else hi = mid;
+  }
+  const uint64_t cprev = lo;
+  lo = 0; hi = numcodes;                    // invariant lb[lo] <= po
+  while (hi - lo > 1) {
+    const uint64_t mid = (lo + hi) >> 1;
+    if (lb[mid] <= po) lo = mid; else hi = mid;
+  }
+  const uint64_t ccur = lo;
+  const unsigned pl = cp.pl;
+  unsigned la = pl;
+  if (cprev % cp.sigma == cp.sigma - 1 && csc[(cprev - (cp.sigma - 1)) / cp.sigma] > 0) {
+    // last padded entry of cprev = smallest number of real symbols
+    uint64_t l2 = 0, h2 = npadded;          // first index with code > cprev
+    const uint64_t target = (cprev + 1) << 6;
+    while (l2 < h2) {
+      const uint64_t mid = (l2 + h2) >> 1;
+      if (padkey[mid] < target) l2 = mid + 1; else h2 = mid;
+    }
+    la = pl - (unsigned)(padkey[l2 - 1] & 63);
+  }
+  const uint32_t b = out.sa[0];
+  unsigned lbn = T.reallen(b);
+  if (lbn > pl) lbn = pl;
+  // common leading digits of the two codes
+  unsigned common = 0;
+  for (unsigned i = 0; i < pl; ++i) {
+    const uint64_t da = (cprev / cp.pw[pl - 1 - i]) % cp.sigma, db = (ccur / cp.pw[pl - 1 - i]) % cp.sigma;
+    if (da != db) break;
+    common++;
+  }
+  unsigned l = common < la ? common : la;
+  l = l < lbn ? l : lbn;
+  out.lcp[0] = (uint8_t)l;
+  if (lbn >= pl && l) atomicAdd(&out.stats->lcpsum, (unsigned long long)l);
+  if (l) atomicMax(&out.stats->maxdepth, l);
+}
+
+__global__ void k_widen(const uint32_t *__restrict__ sa, uint64_t width, uint64_t *__restrict__ out64,
+                        uint64_t partoffset, PartStats *stats) {
+  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= width) return;
+  const uint32_t p = sa[r];
+  out64[r] = p;
+  if (p == 0) stats->longest = partoffset + r;
+}
+
+template <typename OUT>
+__global__ void k_tail(const gtb200_range *__restrict__ ranges, const uint32_t *__restrict__ rangeoff,
+                       uint64_t nranges, uint64_t specialchars, uint64_t n, uint64_t first, uint64_t count, OUT *out) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= count) return;
+  const uint64_t e = first + t;
+  if (e >= specialchars) { out[t] = (OUT)n; return; }
+  uint64_t lo = 0, hi = nranges;            // rangeoff[lo] <= e < rangeoff[hi]
+  while (hi - lo > 1) {
+    const uint64_t mid = (lo + hi) >> 1;
+    if (rangeoff[mid] <= e) lo = mid; else hi = mid;
+  }
+  out[t] = (OUT)(ranges[lo].start + (e - rangeoff[lo]));
+}
+
+__global__ void k_narrow(const uint64_t *__restrict__ in, uint64_t n, uint32_t *__restrict__ out) {
+  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < n) out[r] = (uint32_t)in[r];
+}
+
+// ---------------------------------------------------------------------------------------------
+// host API
+// ---------------------------------------------------------------------------------------------
+static void free_ctx(gtb200_ctx *c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  void *ptrs[] = {c->d_text, c->d_mask, c->d_ranges, c->d_rangeoff, c->d_lb, c->d_cursor, c->d_csc, c->d_dist,
+                  c->d_padkey, c->d_padpos, c->d_sa, c->d_lcp, c->d_suf64, c->d_fbbits, c->d_llv, c->d_stats,
+                  c->d_tilesums, c->d_scratch};
+  for (void *p : ptrs) if (p) cudaFree(p);
+  if (c->h_stats) cudaFreeHost(c->h_stats);
+  for (auto &p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+  for (auto e : c->evpool) cudaEventDestroy(e);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+extern "C" void gtb200_close(gtb200_ctx *c) { free_ctx(c); }
+
+extern "C" void *gtb200_stream(gtb200_ctx *c) { return (void *)c->stream; }
+
+static int sync_stats(gtb200_ctx *c) {
+  CK(cudaMemcpyAsync(c->h_stats, c->d_stats, sizeof(PartStats), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+template <int BITS>
+static Text<BITS> text_of(gtb200_ctx *c) {
+  Text<BITS> T;
+  T.w = c->d_text;
+  T.m = c->d_mask;
+  return T;
+}
+
+static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
+  const uint64_t n = c->n;
+  const int spw = 64 / c->bits;
+  const cudaMemcpyKind h2d = seq->memory == GTB200_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  // sizes: whole 64-position chunks, plus two spare words
+  const uint64_t nchunks = (n >> 6) + 1;
+  c->nmaskwords = nchunks + 2;
+  c->ntextwords = nchunks * (64 / spw) + 2;
+  CK(cudaMalloc(&c->d_text, c->ntextwords * 8));
+  CK(cudaMalloc(&c->d_mask, c->nmaskwords * 8));
+  CK(cudaMalloc(&c->d_stats, sizeof(PartStats)));
+  CK(cudaMallocHost(&c->h_stats, sizeof(PartStats)));
+  CK(cudaMemsetAsync(c->d_stats, 0, sizeof(PartStats), c->stream));
+  CK(cudaMemsetAsync(c->d_text, 0, c->ntextwords * 8, c->stream));
+  CK(cudaMemsetAsync(c->d_mask, 0, c->nmaskwords * 8, c->stream));
+  if (seq->twobitencoding) {
+    uint64_t nw = (n + 31) / 32;
+    if (seq->numofwords < nw) return set_error("twobitencoding has %llu words, %llu needed",
+                                               (unsigned long long)seq->numofwords, (unsigned long long)nw);
+    {
+      ProfScope ps(c, KC_PREP, 0);
+      if (nw) CK(cudaMemcpyAsync(c->d_text, seq->twobitencoding, nw * 8, h2d, c->stream));
+    }
+    c->nranges = seq->numofspecialranges;
+    CK(cudaMalloc(&c->d_ranges, (c->nranges + 1) * sizeof(gtb200_range)));
+    if (c->nranges) {
+      CK(cudaMemcpyAsync(c->d_ranges, seq->specialranges, c->nranges * sizeof(gtb200_range), h2d, c->stream));
+      ProfScope ps(c, KC_PREP);
+      k_mask_from_ranges<<<grid_for(c->nranges * 32, 256), 256, 0, c->stream>>>(c->d_mask, c->d_ranges, c->nranges);
+    }
+  } else {
+    const uint8_t *d_enc = seq->encoded;
+    uint8_t *tmp = nullptr;
+    if (seq->memory != GTB200_MEM_DEVICE) {
+      CK(cudaMalloc(&tmp, n ? n : 1));
+      if (n) CK(cudaMemcpyAsync(tmp, seq->encoded, n, cudaMemcpyHostToDevice, c->stream));
+      d_enc = tmp;
+    }
+    {
+      ProfScope ps(c, KC_PREP);
+      if (c->bits == 2) k_pack_bytes<2><<<grid_for(nchunks, 256), 256, 0, c->stream>>>(d_enc, n, c->d_text, c->d_mask, nchunks);
+      else k_pack_bytes<8><<<grid_for(nchunks, 256), 256, 0, c->stream>>>(d_enc, n, c->d_text, c->d_mask, nchunks);
+    }
+    // derive the special ranges from the bitmap
+    uint32_t *cnt, *popc;
+    CK(cudaMalloc(&cnt, (nchunks + 1) * 4));
+    CK(cudaMalloc(&popc, (nchunks + 1) * 4));
+    {
+      ProfScope ps(c, KC_PREP);
+      k_runs_count<<<grid_for(nchunks, 256), 256, 0, c->stream>>>(c->d_mask, n, nchunks, cnt, popc);
+    }
+    if (device_scan(c, cnt, cnt, nchunks, 0, &c->d_stats->scan_total, KC_PREP)) return -1;
+    if (sync_stats(c)) return -1;
+    c->nranges = c->h_stats->scan_total;
+    CK(cudaMalloc(&c->d_ranges, (c->nranges + 1) * sizeof(gtb200_range)));
+    if (c->nranges) {
+      ProfScope ps(c, KC_PREP);
+      k_runs_write<<<grid_for(nchunks, 256), 256, 0, c->stream>>>(c->d_mask, n, nchunks, cnt, c->d_ranges);
+    }
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaFree(cnt));
+    CK(cudaFree(popc));
+    if (tmp) CK(cudaFree(tmp));
+  }
+  {
+    ProfScope ps(c, KC_PREP);
+    const uint64_t tailwords = c->nmaskwords - (n >> 6);
+    k_mask_tail<<<grid_for(tailwords, 64), 64, 0, c->stream>>>(c->d_mask, n, c->nmaskwords);
+  }
+  // tail paging table: exclusive scan of range lengths; total = specialcharacters
+  CK(cudaMalloc(&c->d_rangeoff, (c->nranges + 2) * 4));
+  if (c->nranges) {
+    {
+      ProfScope ps(c, KC_PREP);
+      k_range_lengths<<<grid_for(c->nranges, 256), 256, 0, c->stream>>>(c->d_ranges, c->nranges, c->d_rangeoff);
+    }
+    if (device_scan(c, c->d_rangeoff, c->d_rangeoff, c->nranges, 1, &c->d_stats->scan_total, KC_PREP)) return -1;
+  } else {
+    CK(cudaMemsetAsync(c->d_rangeoff, 0, 8, c->stream));
+    CK(cudaMemsetAsync(&c->d_stats->scan_total, 0, 8, c->stream));
+  }
+  if (sync_stats(c)) return -1;
+  c->specialchars = c->h_stats->scan_total;
+  c->nsort = n - c->specialchars;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *seq, unsigned prefixlength) {
+  if (!out || !seq) return set_error("gtb200_open: null argument");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return set_error("gtb200_open: no CUDA device available (%s); this library has no CPU fallback",
+                     e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (device < 0 || device >= ndev) return set_error("gtb200_open: device %d out of range (0..%d)", device, ndev - 1);
+  if (seq->totallength >= 0xfffffffeull)
+    return set_error("gtb200_open: totallength %llu does not fit the 32-bit bucket table (reference: bcktab.c:258-261)",
+                     (unsigned long long)seq->totallength);
+  if (seq->numofchars < 2 || seq->numofchars > 253) return set_error("gtb200_open: numofchars %u unsupported", seq->numofchars);
+  if (!seq->twobitencoding && !seq->encoded && seq->totallength)
+    return set_error("gtb200_open: neither twobitencoding nor encoded given");
+  if (seq->twobitencoding && seq->numofchars != 4) return set_error("gtb200_open: twobitencoding requires numofchars == 4");
+  if (seq->twobitencoding && seq->numofspecialranges && !seq->specialranges)
+    return set_error("gtb200_open: specialranges missing");
+  if (prefixlength < 1) return set_error("gtb200_open: prefixlength must be >= 1");
+  CK(cudaSetDevice(device));
+  gtb200_ctx *c = new gtb200_ctx();
+  c->device = device;
+  c->n = seq->totallength;
+  c->bits = seq->numofchars <= 4 ? 2 : 8;
+  c->cp.sigma = seq->numofchars;
+  c->cp.pl = prefixlength;
+  c->cp.pow2 = (seq->numofchars == (1u << c->bits)) ? 1 : 0;
+  const unsigned maxpl = c->bits == 2 ? 16 : 8;
+  if (prefixlength > maxpl) { delete c; return set_error("gtb200_open: prefixlength %u > %u unsupported", prefixlength, maxpl); }
+  uint64_t pw = 1;
+  for (unsigned i = 0; i < 34; ++i) {
+    c->cp.pw[i] = pw;
+    if (pw < (1ull << 40)) pw *= seq->numofchars;
+  }
+  c->numcodes = c->cp.pw[prefixlength];
+  if (c->numcodes > (1ull << 31)) {
+    const unsigned long long nc = c->numcodes;
+    delete c;
+    return set_error("gtb200_open: %llu buckets are too many", nc);
+  }
+  c->numspecialcodes = c->cp.pw[prefixlength - 1];
+  c->numdist = 0;
+  for (unsigned i = 1; i + 1 < prefixlength; ++i) c->numdist += c->cp.pw[i];
+  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete c;
+    return set_error("gtb200_open: cudaStreamCreate failed");
+  }
+  c->sort_maxbucket = SORT_MAXBUCKET;
+  if (const char *e2 = getenv("GTB200_MAXBUCKET")) {   // testing knob: force buckets into the refinement path
+    const long v = atol(e2);
+    if (v >= 0 && v < SORT_MAXBUCKET) c->sort_maxbucket = (uint32_t)v;
+  }
+  if (open_impl(c, seq)) { free_ctx(c); return -1; }
+  *out = c;
+  return 0;
+}
+
+template <int BITS>
+static int count_impl(gtb200_ctx *c) {
+  const Text<BITS> T = text_of<BITS>(c);
+  const uint64_t n = c->n;
+  CK(cudaMalloc(&c->d_lb, (c->numcodes + 2) * 4));
+  CK(cudaMalloc(&c->d_cursor, (c->numcodes + 2) * 4));
+  CK(cudaMalloc(&c->d_csc, (c->numspecialcodes + 1) * 4));
+  CK(cudaMalloc(&c->d_dist, (c->numdist + 1) * 4));
+  CK(cudaMemsetAsync(c->d_lb, 0, (c->numcodes + 2) * 4, c->stream));
+  CK(cudaMemsetAsync(c->d_csc, 0, (c->numspecialcodes + 1) * 4, c->stream));
+  CK(cudaMemsetAsync(c->d_dist, 0, (c->numdist + 1) * 4, c->stream));
+  CK(cudaMemsetAsync(c->d_stats, 0, sizeof(PartStats), c->stream));
+  if (n) {
+    ProfScope ps(c, KC_COUNT);
+    k_kmers<BITS, 0><<<grid_for((n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, n, c->d_lb, nullptr, 0, 0, 0);
+  }
+  // special-padded suffixes
+  const uint64_t nr1 = c->nranges + 1;
+  c->padcap = nr1 * (c->cp.pl - 1) + 1;
+  uint32_t *cntoff;
+  CK(cudaMalloc(&cntoff, (nr1 + 1) * 4));
+  CK(cudaMalloc(&c->d_padkey, c->padcap * 8));
+  CK(cudaMalloc(&c->d_padpos, c->padcap * 4));
+  {
+    ProfScope ps(c, KC_PADDED);
+    k_padded<BITS, 0><<<grid_for(nr1, 128), 128, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, cntoff, nullptr,
+                                                                 nullptr, nullptr, nullptr, nullptr);
+  }
+  if (device_scan(c, cntoff, cntoff, nr1, 0, &c->d_stats->scan_total, KC_PADDED)) return -1;
+  {
+    ProfScope ps(c, KC_PADDED);
+    k_padded<BITS, 1><<<grid_for(nr1, 128), 128, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, cntoff, c->d_lb,
+                                                                 c->d_csc, c->d_dist, c->d_padkey, c->d_padpos);
+  }
+  {
+    ProfScope ps(c, KC_COUNT);
+    k_max_u32<<<592, 256, 0, c->stream>>>(c->d_lb, c->numcodes, &c->d_stats->largest);
+  }
+  if (device_scan(c, c->d_lb, c->d_lb, c->numcodes, 1, &c->d_stats->scan_total2)) return -1;
+  if (sync_stats(c)) return -1;
+  CK(cudaFree(cntoff));
+  c->npadded = c->h_stats->scan_total;
+  c->largestbucket = c->h_stats->largest;
+  if (c->h_stats->scan_total2 != c->nsort)
+    return set_error("internal: bucket counts sum to %llu, expected %llu", c->h_stats->scan_total2,
+                     (unsigned long long)c->nsort);
+  // sort the padded list by (code, pl-L); stable, so positions stay ascending
+  if (c->npadded > 1) {
+    const uint32_t np = (uint32_t)c->npadded;
+    const uint32_t nblocks = grid_for(np, RS_TILE);
+    const size_t need = (size_t)np * (8 + 8 + 4 + 4) + (256ull * nblocks + 1) * 4 + 64;
+    if (ensure_scratch(c, need)) return -1;
+    char *s = (char *)c->d_scratch;
+    uint64_t *kA = (uint64_t *)s; s += (size_t)np * 8;
+    uint64_t *kB = (uint64_t *)s; s += (size_t)np * 8;
+    uint32_t *vA = (uint32_t *)s; s += (size_t)np * 4;
+    uint32_t *vB = (uint32_t *)s; s += (size_t)np * 4;
+    uint32_t *hist = (uint32_t *)s;
+    const uint64_t *ko;
+    const uint32_t *vo;
+    const int hib = 6 + bits_for(c->numcodes - 1);
+    if (device_radix_sort(c, c->d_padkey, c->d_padpos, kA, vA, kB, vB, hist, np, 0, hib, &ko, &vo)) return -1;
+    CK(cudaMemcpyAsync(c->d_padkey, ko, (size_t)np * 8, cudaMemcpyDeviceToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->d_padpos, vo, (size_t)np * 4, cudaMemcpyDeviceToDevice, c->stream));
+  }
+  CK(cudaGetLastError());
+  c->counted = true;
+  return 0;
+}
+
+extern "C" int gtb200_count(gtb200_ctx *c, uint32_t *leftborder, uint32_t *countspecialcodes, uint32_t *distpfxidx,
+                            gtb200_countinfo *info) {
+  if (!c) return set_error("gtb200_count: null context");
+  CK(cudaSetDevice(c->device));
+  if (!c->counted) {
+    const int rc = c->bits == 2 ? count_impl<2>(c) : count_impl<8>(c);
+    if (rc) return rc;
+  }
+  if (leftborder) CK(cudaMemcpyAsync(leftborder, c->d_lb, (c->numcodes + 1) * 4, cudaMemcpyDeviceToHost, c->stream));
+  if (countspecialcodes)
+    CK(cudaMemcpyAsync(countspecialcodes, c->d_csc, c->numspecialcodes * 4, cudaMemcpyDeviceToHost, c->stream));
+  if (distpfxidx && c->numdist)
+    CK(cudaMemcpyAsync(distpfxidx, c->d_dist, c->numdist * 4, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  if (info) {
+    info->numofallcodes = c->numcodes;
+    info->numofspecialcodes = c->numspecialcodes;
+    info->numofdistpfxidx = c->numdist;
+    info->numofsuffixestosort = c->nsort;
+    info->specialcharacters = c->specialchars;
+    info->largestbucket = c->largestbucket;
+  }
+  return 0;
+}
+
+static int ensure_part_buffers(gtb200_ctx *c, uint64_t width, uint64_t ncodes_in_part) {
+  if (width > c->cap_width) {
+    if (c->d_sa) CK(cudaFree(c->d_sa));
+    if (c->d_lcp) CK(cudaFree(c->d_lcp));
+    if (c->d_suf64) CK(cudaFree(c->d_suf64));
+    c->d_sa = nullptr; c->d_lcp = nullptr; c->d_suf64 = nullptr; c->cap_width = 0;
+    CK(cudaMalloc(&c->d_sa, (width + 1) * 4));
+    CK(cudaMalloc(&c->d_lcp, width + 1));
+    CK(cudaMalloc(&c->d_suf64, (width + 1) * 8));
+    c->cap_width = width;
+  }
+  const uint64_t fbwords = (ncodes_in_part + 31) / 32 + 1;
+  if (fbwords > c->cap_fbwords) {
+    if (c->d_fbbits) CK(cudaFree(c->d_fbbits));
+    c->d_fbbits = nullptr; c->cap_fbwords = 0;
+    CK(cudaMalloc(&c->d_fbbits, fbwords * 4));
+    c->cap_fbwords = fbwords;
+  }
+  return 0;
+}
+
+// refinement of flagged buckets; A elements, nb buckets (both from the sort kernel's counters)
+template <int BITS>
+static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, uint64_t maxcode, uint64_t width,
+                       gtb200_partinfo *info) {
+  const Text<BITS> T = text_of<BITS>(c);
+  const uint32_t A0 = (uint32_t)c->h_stats->fb_elems;
+  const uint32_t nb = c->h_stats->fb_buckets;
+  const uint64_t fbwords = (maxcode - mincode + 1 + 31) / 32;
+  info->fallback_suffixes = A0;
+  // llv append buffer: at most one value per refined suffix
+  if (A0 > c->cap_llv) {
+    if (c->d_llv) CK(cudaFree(c->d_llv));
+    c->d_llv = nullptr; c->cap_llv = 0;
+    CK(cudaMalloc(&c->d_llv, ((size_t)A0 + 1) * sizeof(gtb200_largelcp)));
+    c->cap_llv = A0;
+  }
+  PartOut out = out_in;
+  // scratch carve-up
+  const uint32_t nblocks = grid_for(A0, RS_TILE);
+  size_t need = 0;
+  auto take = [&](size_t bytes) { size_t o = need; need += (bytes + 255) & ~(size_t)255; return o; };
+  const size_t o_wcnt = take((fbwords + 1) * 4), o_codes = take(((size_t)nb + 1) * 4), o_sizes = take(((size_t)nb + 1) * 4);
+  const size_t a4 = ((size_t)A0 + 1) * 4, a8 = ((size_t)A0 + 1) * 8;
+  const size_t o_idx0 = take(a4), o_idx1 = take(a4), o_gs0 = take(a4), o_gs1 = take(a4), o_dep0 = take(a4), o_dep1 = take(a4);
+  const size_t o_keys = take(a8), o_kA = take(a8), o_kB = take(a8), o_vals = take(a4), o_vA = take(a4), o_vB = take(a4);
+  const size_t o_pos = take(a4), o_head = take(a4), o_hscan = take(a4), o_headpos = take(a4 + 4), o_keep = take(a4);
+  const size_t o_kscan = take(a4), o_newgs = take(a4), o_newdep = take(a4), o_hist = take((256ull * nblocks + 1) * 4);
+  const size_t o_llvtmp = take(((size_t)A0 + 1) * sizeof(gtb200_largelcp));
+  if (ensure_scratch(c, need)) return -1;
+  char *S = (char *)c->d_scratch;
+  uint32_t *wcnt = (uint32_t *)(S + o_wcnt), *codes = (uint32_t *)(S + o_codes), *sizes = (uint32_t *)(S + o_sizes);
+  uint32_t *idx[2] = {(uint32_t *)(S + o_idx0), (uint32_t *)(S + o_idx1)};
+  uint32_t *gs[2] = {(uint32_t *)(S + o_gs0), (uint32_t *)(S + o_gs1)};
+  uint32_t *dep[2] = {(uint32_t *)(S + o_dep0), (uint32_t *)(S + o_dep1)};
+  uint64_t *keys = (uint64_t *)(S + o_keys), *kA = (uint64_t *)(S + o_kA), *kB = (uint64_t *)(S + o_kB);
+  uint32_t *vals = (uint32_t *)(S + o_vals), *vA = (uint32_t *)(S + o_vA), *vB = (uint32_t *)(S + o_vB);
+  uint32_t *posbuf = (uint32_t *)(S + o_pos), *head = (uint32_t *)(S + o_head), *hscan = (uint32_t *)(S + o_hscan);
+  uint32_t *headpos = (uint32_t *)(S + o_headpos), *keep = (uint32_t *)(S + o_keep), *kscan = (uint32_t *)(S + o_kscan);
+  uint32_t *newgs = (uint32_t *)(S + o_newgs), *newdep = (uint32_t *)(S + o_newdep), *hist = (uint32_t *)(S + o_hist);
+  gtb200_largelcp *llvtmp = (gtb200_largelcp *)(S + o_llvtmp);
+  out.llv = llvtmp;
+
+  // expand the flagged-bucket bitmap into the ordered element list
+  {
+    ProfScope ps(c, KC_REFINE, 1);
+    k_fb_popc<<<grid_for(fbwords, 256), 256, 0, c->stream>>>(c->d_fbbits, fbwords, wcnt);
+  }
+  if (device_scan(c, wcnt, wcnt, fbwords, 0, nullptr, KC_REFINE)) return -1;
+  {
+    ProfScope ps(c, KC_REFINE, 1);
+    k_fb_codes<<<grid_for(fbwords, 256), 256, 0, c->stream>>>(c->d_fbbits, fbwords, wcnt, mincode, c->d_lb, c->d_cursor,
+                                                              codes, sizes);
+  }
+  if (device_scan(c, sizes, sizes, nb, 0, nullptr, KC_REFINE)) return -1;
+  {
+    ProfScope ps(c, KC_REFINE, 1);
+    k_fb_fill<<<grid_for((uint64_t)nb * 32, 256), 256, 0, c->stream>>>(codes, sizes, nb, c->d_lb, c->d_cursor,
+                                                                       out.partoffset, c->cp.pl, idx[0], gs[0], dep[0]);
+  }
+  CK(cudaGetLastError());
+  uint32_t A = A0;
+  int cur = 0;
+  uint64_t rounds = 0;
+  const int gsbits = ((bits_for(width) + 7) / 8) * 8;
+  while (A > 0) {
+    rounds++;
+    const unsigned g = grid_for(A, 256);
+    {
+      ProfScope ps(c, KC_REFINE, 1);
+      k_fb_keys<BITS><<<g, 256, 0, c->stream>>>(T, out.sa, idx[cur], dep[cur], A, keys, posbuf, vals);
+    }
+    const uint64_t *ko;
+    const uint32_t *vo;
+    if (device_radix_sort(c, keys, vals, kA, vA, kB, vB, hist, A, 0, 64, &ko, &vo)) return -1;
+    // second key: group start; vo must not be one of the output buffers of the next sort's first pass
+    uint64_t *k2 = (ko == kA) ? kB : kA;   // free key buffer
+    {
+      ProfScope ps(c, KC_REFINE, 1);
+      k_fb_gather_gs<<<g, 256, 0, c->stream>>>(vo, gs[cur], A, k2);
+    }
+    // copy vo into vals so that both ping-pong value buffers are free again
+    CK(cudaMemcpyAsync(vals, vo, (size_t)A * 4, cudaMemcpyDeviceToDevice, c->stream));
+    uint64_t *k3a = (k2 == kA) ? kB : kA;
+    // keys buffer `keys` must stay intact (regroup reads it), so ping-pong between k3a and a third buffer:
+    // reuse posbuf? no - use kscan/newgs area is too small; sort (k2 -> k3a -> k2 ...) is safe because
+    // device_radix_sort never writes to its input on the first pass and alternates afterwards.
+    const uint64_t *ko2;
+    const uint32_t *vo2;
+    if (device_radix_sort(c, k2, vals, k3a, vA, k2, vB, hist, A, 0, gsbits, &ko2, &vo2)) return -1;
+    {
+      ProfScope ps(c, KC_REFINE, 1);
+      k_fb_regroup<BITS><<<g, 256, 0, c->stream>>>(out, vo2, idx[cur], gs[cur], dep[cur], keys, posbuf, A, head, newdep);
+    }
+    if (device_scan(c, head, hscan, A, 0, &c->d_stats->scan_total, KC_REFINE)) return -1;
+    {
+      ProfScope ps(c, KC_REFINE, 2);
+      k_fb_headpos<<<g, 256, 0, c->stream>>>(head, hscan, A, headpos, &c->d_stats->scan_total);
+      k_fb_finalize<<<g, 256, 0, c->stream>>>(head, hscan, headpos, idx[cur], A, keep, newgs);
+    }
+    if (device_scan(c, keep, kscan, A, 0, &c->d_stats->scan_total2, KC_REFINE)) return -1;
+    {
+      // newdep is indexed by sorted position j, like idx; gather of dep happened in regroup
+      ProfScope ps(c, KC_REFINE, 1);
+      k_fb_compact<<<g, 256, 0, c->stream>>>(keep, kscan, idx[cur], newgs, newdep, A, idx[cur ^ 1], gs[cur ^ 1], dep[cur ^ 1]);
+    }
+    CK(cudaGetLastError());
+    if (sync_stats(c)) return -1;
+    A = (uint32_t)c->h_stats->scan_total2;
+    cur ^= 1;
+    if (rounds > (c->n / Text<BITS>::W) + 8) return set_error("internal: refinement does not converge");
+  }
+  info->fallback_rounds = rounds;
+  // order the large-lcp records by suffix-array index
+  const uint32_t nl = (uint32_t)c->h_stats->llv_count;
+  if (nl) {
+    const unsigned g = grid_for(nl, 256);
+    {
+      ProfScope ps(c, KC_REFINE, 1);
+      k_llv_keys<<<g, 256, 0, c->stream>>>(llvtmp, nl, keys, vals);
+    }
+    const uint64_t *ko;
+    const uint32_t *vo;
+    const int pbits = ((bits_for(out.partoffset + width) + 7) / 8) * 8;
+    if (device_radix_sort(c, keys, vals, kA, vA, kB, vB, hist, nl, 0, pbits, &ko, &vo)) return -1;
+    {
+      ProfScope ps(c, KC_REFINE, 1);
+      k_llv_gather<<<g, 256, 0, c->stream>>>(llvtmp, vo, nl, c->d_llv);
+    }
+    CK(cudaGetLastError());
+  }
+  return 0;
+}
+
+template <int BITS>
+static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb200_partinfo *info) {
+  const Text<BITS> T = text_of<BITS>(c);
+  // part geometry from the bucket table
+  uint32_t h_lb[2];
+  CK(cudaMemcpyAsync(&h_lb[0], c->d_lb + mincode, 4, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(&h_lb[1], c->d_lb + maxcode + 1, 4, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  const uint64_t partoffset = h_lb[0], width = (uint64_t)h_lb[1] - h_lb[0];
+  const uint64_t ncodes = maxcode - mincode + 1;
+  memset(info, 0, sizeof *info);
+  info->partoffset = partoffset;
+  info->width = width;
+  info->longest = UINT64_MAX;
+  c->part_offset = partoffset;
+  c->part_width = width;
+  c->part_nllv = 0;
+  if (width == 0) return 0;
+  if (ensure_part_buffers(c, width, ncodes)) return -1;
+  CK(cudaMemsetAsync(c->d_stats, 0, sizeof(PartStats), c->stream));
+  CK(cudaMemsetAsync(&c->d_stats->longest, 0xff, 8, c->stream));
+  CK(cudaMemsetAsync(c->d_fbbits, 0, ((ncodes + 31) / 32 + 1) * 4, c->stream));
+  CK(cudaMemsetAsync(c->d_lcp, 0, width, c->stream));
+  CK(cudaMemcpyAsync(c->d_cursor + mincode, c->d_lb + mincode, ncodes * 4, cudaMemcpyDeviceToDevice, c->stream));
+  PartOut out;
+  out.sa = c->d_sa;
+  out.lcp = c->d_lcp;
+  out.llv = nullptr;
+  out.stats = c->d_stats;
+  out.partoffset = (uint32_t)partoffset;
+  {
+    ProfScope ps(c, KC_SCATTER);
+    k_kmers<BITS, 1><<<grid_for((c->n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, c->n, c->d_cursor, c->d_sa, mincode,
+                                                                            maxcode, (uint32_t)partoffset);
+  }
+  if (c->npadded) {
+    ProfScope ps(c, KC_PADDED);
+    k_place_padded<<<grid_for(c->npadded, 256), 256, 0, c->stream>>>(c->d_padkey, c->d_padpos, c->npadded, c->d_lb,
+                                                                     c->d_csc, c->cp.sigma, c->cp.pl, mincode, maxcode, out);
+  }
+  {
+    ProfScope ps(c, KC_SORT);
+    uint64_t warps = ncodes < 148ull * 64 ? ncodes : 148ull * 64;   // 8 blocks of 8 warps per SM
+    k_sort_buckets<BITS><<<grid_for(warps * 32, 256), 256, 0, c->stream>>>(T, out, c->d_lb, c->d_cursor, mincode, maxcode,
+                                                                          c->cp.pl, c->d_fbbits, c->sort_maxbucket);
+  }
+  CK(cudaGetLastError());
+  if (sync_stats(c)) return -1;
+  if (c->h_stats->fb_elems) {
+    if (refine_impl<BITS>(c, out, mincode, maxcode, width, info)) return -1;
+  }
+  {
+    ProfScope ps(c, KC_BOUNDARY);
+    k_boundary<BITS><<<grid_for(ncodes, 256), 256, 0, c->stream>>>(T, out, c->d_lb, mincode, maxcode, c->cp.pl);
+    if (partoffset > 0)
+      k_part_first<BITS><<<1, 32, 0, c->stream>>>(T, c->cp, out, c->d_lb, c->numcodes, c->d_csc, c->d_padkey, c->npadded);
+  }
+  {
+    ProfScope ps(c, KC_WIDEN);
+    k_widen<<<grid_for(width, 256), 256, 0, c->stream>>>(c->d_sa, width, c->d_suf64, partoffset, c->d_stats);
+  }
+  CK(cudaGetLastError());
+  if (sync_stats(c)) return -1;
+  info->numoflargelcpvalues = c->h_stats->llv_count;
+  info->maxbranchdepth = c->h_stats->maxdepth;
+  info->lcptabsum = (double)c->h_stats->lcpsum;
+  info->longest = c->h_stats->longest;
+  c->part_nllv = c->h_stats->llv_count;
+  return 0;
+}
+
+extern "C" int gtb200_sort_part_device(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb200_partinfo *info) {
+  if (!c || !info) return set_error("gtb200_sort_part_device: null argument");
+  if (!c->counted) return set_error("gtb200_sort_part_device: call gtb200_count first");
+  if (mincode > maxcode || maxcode >= c->numcodes)
+    return set_error("gtb200_sort_part_device: code range [%llu,%llu] invalid (numofallcodes %llu)",
+                     (unsigned long long)mincode, (unsigned long long)maxcode, (unsigned long long)c->numcodes);
+  CK(cudaSetDevice(c->device));
+  return c->bits == 2 ? sort_part_impl<2>(c, mincode, maxcode, info) : sort_part_impl<8>(c, mincode, maxcode, info);
+}
+
+extern "C" int gtb200_part_device(gtb200_ctx *c, void **suftab_dev, void **lcptab_dev, void **llv_dev) {
+  if (!c) return set_error("gtb200_part_device: null context");
+  if (suftab_dev) *suftab_dev = c->d_suf64;
+  if (lcptab_dev) *lcptab_dev = c->d_lcp;
+  if (llv_dev) *llv_dev = c->d_llv;
+  return 0;
+}
+
+extern "C" int gtb200_fetch_part(gtb200_ctx *c, void *suftab, int suftab_is_uint32, uint8_t *lcptab,
+                                 gtb200_largelcp *llv, uint64_t llv_capacity) {
+  if (!c) return set_error("gtb200_fetch_part: null context");
+  CK(cudaSetDevice(c->device));
+  const uint64_t w = c->part_width;
+  if (w == 0) return 0;
+  if (suftab) {
+    if (suftab_is_uint32) CK(cudaMemcpyAsync(suftab, c->d_sa, w * 4, cudaMemcpyDeviceToHost, c->stream));
+    else CK(cudaMemcpyAsync(suftab, c->d_suf64, w * 8, cudaMemcpyDeviceToHost, c->stream));
+  }
+  if (lcptab) CK(cudaMemcpyAsync(lcptab, c->d_lcp, w, cudaMemcpyDeviceToHost, c->stream));
+  if (llv && c->part_nllv) {
+    if (c->part_nllv > llv_capacity)
+      return set_error("gtb200_fetch_part: %llu large lcp values, capacity %llu", (unsigned long long)c->part_nllv,
+                       (unsigned long long)llv_capacity);
+    CK(cudaMemcpyAsync(llv, c->d_llv, c->part_nllv * sizeof(gtb200_largelcp), cudaMemcpyDeviceToHost, c->stream));
+  }
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int gtb200_sort_part(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, void *suftab, int suftab_is_uint32,
+                                uint8_t *lcptab, gtb200_largelcp *llv, uint64_t llv_capacity, gtb200_partinfo *info) {
+  if (gtb200_sort_part_device(c, mincode, maxcode, info)) return -1;
+  return gtb200_fetch_part(c, suftab, suftab_is_uint32, lcptab, llv, llv_capacity);
+}
+
+extern "C" int gtb200_tail(gtb200_ctx *c, uint64_t first, uint64_t count, void *suftab, int suftab_is_uint32) {
+  if (!c) return set_error("gtb200_tail: null context");
+  if (first + count > c->specialchars + 1)
+    return set_error("gtb200_tail: [%llu,%llu) exceeds the %llu tail entries", (unsigned long long)first,
+                     (unsigned long long)(first + count), (unsigned long long)(c->specialchars + 1));
+  if (count == 0) return 0;
+  CK(cudaSetDevice(c->device));
+  const size_t esz = suftab_is_uint32 ? 4 : 8;
+  if (ensure_scratch(c, count * esz)) return -1;
+  {
+    ProfScope ps(c, KC_TAIL);
+    if (suftab_is_uint32)
+      k_tail<uint32_t><<<grid_for(count, 256), 256, 0, c->stream>>>(c->d_ranges, c->d_rangeoff, c->nranges, c->specialchars,
+                                                                   c->n, first, count, (uint32_t *)c->d_scratch);
+    else
+      k_tail<uint64_t><<<grid_for(count, 256), 256, 0, c->stream>>>(c->d_ranges, c->d_rangeoff, c->nranges, c->specialchars,
+                                                                   c->n, first, count, (uint64_t *)c->d_scratch);
+  }
+  CK(cudaGetLastError());
+  if (suftab) CK(cudaMemcpyAsync(suftab, c->d_scratch, count * esz, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int gtb200_profile_enable(gtb200_ctx *c, int on) {
+  if (!c) return set_error("null context");
+  if (!on) prof_fold(c);
+  c->prof_on = on != 0;
+  return 0;
+}
+
+extern "C" void gtb200_profile_reset(gtb200_ctx *c) {
+  if (!c) return;
+  prof_fold(c);
+  for (int i = 0; i < KC_NUM; ++i) { c->prof_ms[i] = 0.0; c->prof_launches[i] = 0; }
+}
+
+extern "C" int gtb200_profile_read(gtb200_ctx *c, const char **names, double *ms, uint64_t *launches, int capacity) {
+  if (!c) return set_error("null context");
+  if (prof_fold(c)) return -1;
+  for (int i = 0; i < KC_NUM && i < capacity; ++i) {
+    if (names) names[i] = kclass_names[i];
+    if (ms) ms[i] = c->prof_ms[i];
+    if (launches) launches[i] = c->prof_launches[i];
+  }
+  return KC_NUM;
+}

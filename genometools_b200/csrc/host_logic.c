@@ -1,0 +1,95 @@
+/* Host-side pieces of the Sfxiterator logic that the device layer's callers need and that do not
+ * touch the GPU: the automatic prefix length and the split of the bucket table into parts.
+ * Written from the behaviour of the reference functions cited in include/gtsfx_b200.h. */
+#include <stdint.h>
+#include <stdlib.h>
+
+#include "../../include/gtsfx_b200.h"
+
+static uint64_t ipow(unsigned base, unsigned e) {
+  uint64_t r = 1;
+  while (e--) r *= base;
+  return r;
+}
+
+static uint64_t bcktab_bytes(unsigned sigma, unsigned pl, uint64_t maxvalue) {
+  const uint64_t w = maxvalue <= 0xffffffffULL ? 4 : 8;
+  uint64_t dist = 0;
+  unsigned i;
+  for (i = 1; i + 1 < pl; i++) dist += ipow(sigma, i);
+  return w * (ipow(sigma, pl) + 1) + w * ipow(sigma, pl - 1) + w * dist;
+}
+
+unsigned gtb200_recommendedprefixlength(unsigned numofchars, uint64_t totallength) {
+  /* largest pl whose table, divided by the multiplier 0.25, does not exceed totallength bytes;
+   * capped by the largest exponent for which sigma^pl still fits a code word */
+  unsigned pl, cap = 0;
+  uint64_t p = 1;
+  const uint64_t minfailure = UINT64_MAX / numofchars;
+  while (p < minfailure) {
+    p *= numofchars;
+    cap++;
+  }
+  for (pl = 1;; pl++)
+    if ((double) bcktab_bytes(numofchars, pl, totallength + 1) / 0.25 > (double) totallength) break;
+  pl--;
+  if (pl == 0) return 1;
+  return pl < cap ? pl : cap;
+}
+
+/* end offset of bucket c = start offset of bucket c+1 */
+static uint64_t bucket_end(const uint32_t *leftborder, uint64_t c) { return leftborder[c + 1]; }
+
+/* the reference's binary search over bucket END offsets (gt_bcktab_findfirstlarger): a code whose
+ * end offset is >= target; stops at the first exact hit the bisection meets */
+static uint64_t find_first_larger(const uint32_t *leftborder, uint64_t numofallcodes, uint64_t target) {
+  uint64_t left = 0, right = numofallcodes - 1, found = numofallcodes;
+  while (left <= right) {
+    const uint64_t mid = (left + right) / 2;
+    const uint64_t midval = bucket_end(leftborder, mid);
+    if (target <= midval) {
+      found = mid;
+      if (target < midval) {
+        if (mid == 0) break;
+        right = mid - 1;
+      } else {
+        break;
+      }
+    } else {
+      left = mid + 1;
+    }
+  }
+  return found;
+}
+
+int gtb200_suftabparts(unsigned numofparts, const uint32_t *leftborder, uint64_t numofallcodes,
+                       unsigned prefixlength, uint64_t *mincodes, uint64_t *maxcodes, uint64_t *widths) {
+  const uint64_t total = leftborder[numofallcodes];
+  unsigned parts, part, kept = 0, remainder;
+  uint64_t target = 0, firstbound = 0, per;
+  if (total == 0 || numofparts == 0) return 0;
+  parts = (total < numofparts || prefixlength == 1) ? 1 : numofparts;
+  per = total / parts;
+  remainder = (unsigned) (total % parts);
+  for (part = 0; part < parts; part++) {
+    uint64_t lastcode, secondbound;
+    target += per;
+    if (remainder > 0) {
+      target++;
+      remainder--;
+    }
+    lastcode = (part == parts - 1) ? numofallcodes - 1 : find_first_larger(leftborder, numofallcodes, target);
+    secondbound = bucket_end(leftborder, lastcode);
+    if (secondbound > firstbound) {              /* empty parts are dropped */
+      mincodes[kept] = kept ? maxcodes[kept - 1] + 1 : 0;
+      maxcodes[kept] = lastcode;
+      widths[kept] = secondbound - firstbound;
+      kept++;
+    } else if (kept) {
+      maxcodes[kept - 1] = lastcode;             /* keep the code ranges contiguous */
+    }
+    firstbound = secondbound;
+  }
+  if (kept) maxcodes[kept - 1] = numofallcodes - 1;
+  return (int) kept;
+}

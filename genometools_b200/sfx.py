@@ -1,0 +1,341 @@
+"""Host-side mirror of the reference's Sfxiterator interface over the C ABI of libgtsfx_b200.so.
+
+Inside libgenometools the host side stays C (INTEGRATION.md shows the patched
+src/match/sfx-suffixer.c).  This module is the same control flow for the Python test and
+benchmark harness: `Sfxiterator` has the reference's entry points with the reference's meaning
+
+    gt_Sfxiterator_new_withadditionalvalues  (src/match/sfx-suffixer.c:1363)  -> Sfxiterator(...)
+    gt_Sfxiterator_next                      (:2162)                          -> .next()
+    gt_Sfxiterator_longest                   (:2219)                          -> .longest()
+    gt_Sfxiterator_bcktab2file               (:2206)                          -> .bcktab2file(fp)
+    gt_Sfxiterator_delete                    (:537)                           -> .delete()
+
+and `suffixerator()` is the loop of suffixeratorwithoutput (src/match/sfx-run.c:212-317) that writes
+.suf/.lcp/.llv/.bck exactly as gt_suffixsortspace_to_file, outlcpvalues and
+gt_bcktab_flush_to_file do.  There is no CPU fallback: if the CUDA library or a GPU is missing the
+constructor raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import encseq as _encseq
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgtsfx_b200.so")
+_lib = None
+
+UINT64_MAX = (1 << 64) - 1
+
+
+class Gtb200Error(RuntimeError):
+    pass
+
+
+class Range(C.Structure):
+    _fields_ = [("start", C.c_uint64), ("end", C.c_uint64)]
+
+
+class LargeLcp(C.Structure):
+    _fields_ = [("position", C.c_uint64), ("value", C.c_uint64)]
+
+
+class SeqDesc(C.Structure):
+    _fields_ = [("numofchars", C.c_uint), ("totallength", C.c_uint64),
+                ("twobitencoding", C.c_void_p), ("numofwords", C.c_uint64),
+                ("encoded", C.c_void_p), ("specialranges", C.c_void_p),
+                ("numofspecialranges", C.c_uint64), ("memory", C.c_int)]
+
+
+class CountInfo(C.Structure):
+    _fields_ = [("numofallcodes", C.c_uint64), ("numofspecialcodes", C.c_uint64),
+                ("numofdistpfxidx", C.c_uint64), ("numofsuffixestosort", C.c_uint64),
+                ("specialcharacters", C.c_uint64), ("largestbucket", C.c_uint64)]
+
+
+class PartInfo(C.Structure):
+    _fields_ = [("partoffset", C.c_uint64), ("width", C.c_uint64),
+                ("numoflargelcpvalues", C.c_uint64), ("maxbranchdepth", C.c_uint64),
+                ("lcptabsum", C.c_double), ("longest", C.c_uint64),
+                ("fallback_suffixes", C.c_uint64), ("fallback_rounds", C.c_uint64)]
+
+
+EXPORTS = [
+    "gtb200_device_count", "gtb200_last_error", "gtb200_open", "gtb200_close", "gtb200_stream",
+    "gtb200_count", "gtb200_sort_part_device", "gtb200_part_device", "gtb200_fetch_part",
+    "gtb200_sort_part", "gtb200_tail", "gtb200_recommendedprefixlength", "gtb200_suftabparts",
+    "gtb200_profile_enable", "gtb200_profile_read", "gtb200_profile_reset",
+]
+
+
+def load_library() -> C.CDLL:
+    """dlopen the in-tree CUDA library; a missing build is a hard error, never a fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise Gtb200Error(f"{LIB_PATH} is not built - run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(there is no CPU fallback for this path)")
+    L = C.CDLL(LIB_PATH)
+    L.gtb200_last_error.restype = C.c_char_p
+    L.gtb200_device_count.restype = C.c_int
+    L.gtb200_open.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.POINTER(SeqDesc), C.c_uint]
+    L.gtb200_close.argtypes = [C.c_void_p]
+    L.gtb200_close.restype = None
+    L.gtb200_stream.argtypes = [C.c_void_p]
+    L.gtb200_stream.restype = C.c_void_p
+    L.gtb200_count.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(CountInfo)]
+    L.gtb200_sort_part_device.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(PartInfo)]
+    L.gtb200_part_device.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+    L.gtb200_fetch_part.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64]
+    L.gtb200_sort_part.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_int, C.c_void_p,
+                                   C.c_void_p, C.c_uint64, C.POINTER(PartInfo)]
+    L.gtb200_tail.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_int]
+    L.gtb200_recommendedprefixlength.argtypes = [C.c_uint, C.c_uint64]
+    L.gtb200_recommendedprefixlength.restype = C.c_uint
+    L.gtb200_suftabparts.argtypes = [C.c_uint, C.c_void_p, C.c_uint64, C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.gtb200_profile_enable.argtypes = [C.c_void_p, C.c_int]
+    L.gtb200_profile_read.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_double),
+                                      C.POINTER(C.c_uint64), C.c_int]
+    L.gtb200_profile_reset.argtypes = [C.c_void_p]
+    L.gtb200_profile_reset.restype = None
+    _lib = L
+    return L
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise Gtb200Error(load_library().gtb200_last_error().decode())
+
+
+def recommended_prefixlength(sigma: int, totallength: int) -> int:
+    return int(load_library().gtb200_recommendedprefixlength(sigma, totallength))
+
+
+def suftabparts(numofparts: int, leftborder: np.ndarray, prefixlength: int):
+    """[(mincode, maxcode, width)] - gt_suftabparts_new for the whole code range."""
+    L = load_library()
+    numcodes = leftborder.shape[0] - 1
+    mn = np.zeros(numofparts, dtype=np.uint64)
+    mx = np.zeros(numofparts, dtype=np.uint64)
+    wd = np.zeros(numofparts, dtype=np.uint64)
+    k = L.gtb200_suftabparts(numofparts, leftborder.ctypes.data, numcodes, prefixlength,
+                             mn.ctypes.data, mx.ctypes.data, wd.ctypes.data)
+    return [(int(mn[i]), int(mx[i]), int(wd[i])) for i in range(k)]
+
+
+class Sfxiterator:
+    """Iterates over the suffix array part by part, like gt_Sfxiterator_next.
+
+    sequence: either ``enc`` (uint8 codes incl. 254/255, any alphabet) or, for DNA,
+    ``twobit`` + ``ranges`` exactly as GtEncseq exports them; ``device_ptrs=True`` says the arrays are
+    integers holding device addresses already resident on ``device`` (multi-GPU broadcast).
+    """
+
+    def __init__(self, sigma: int, totallength: int, prefixlength: int | None = None, numofparts: int = 1,
+                 enc: np.ndarray | int | None = None, twobit: np.ndarray | int | None = None,
+                 ranges: np.ndarray | int | None = None, numofwords: int = 0, numofranges: int = 0,
+                 device: int = 0, device_ptrs: bool = False, with_lcp: bool = True, suftabuint: bool = False,
+                 code_range: tuple[int, int] | None = None):
+        L = load_library()
+        self._L = L
+        self._ctx = C.c_void_p()
+        self.sigma = sigma
+        self.totallength = totallength
+        self.prefixlength = prefixlength or recommended_prefixlength(sigma, totallength)
+        self.suftabuint = suftabuint
+        self.with_lcp = with_lcp
+        desc = SeqDesc()
+        desc.numofchars = sigma
+        desc.totallength = totallength
+        desc.memory = 1 if device_ptrs else 0
+        self._keep = []
+        if twobit is not None:
+            if device_ptrs:
+                desc.twobitencoding, desc.numofwords = int(twobit), numofwords
+                desc.specialranges, desc.numofspecialranges = int(ranges or 0), numofranges
+            else:
+                tw = np.ascontiguousarray(twobit, dtype=np.uint64)
+                rg = np.ascontiguousarray(ranges if ranges is not None else np.zeros((0, 2)), dtype=np.uint64)
+                self._keep += [tw, rg]
+                desc.twobitencoding, desc.numofwords = tw.ctypes.data, tw.shape[0]
+                desc.specialranges, desc.numofspecialranges = rg.ctypes.data, rg.shape[0]
+        else:
+            if device_ptrs:
+                desc.encoded = int(enc)
+            else:
+                e = np.ascontiguousarray(enc, dtype=np.uint8)
+                self._keep.append(e)
+                desc.encoded = e.ctypes.data
+        _check(L.gtb200_open(C.byref(self._ctx), device, C.byref(desc), self.prefixlength))
+        # "counting prefix distribution"
+        info = CountInfo()
+        numcodes = sigma ** self.prefixlength
+        self.leftborder = np.zeros(numcodes + 1, dtype=np.uint32)
+        self.countspecialcodes = np.zeros(sigma ** (self.prefixlength - 1), dtype=np.uint32)
+        ndist = sum(sigma ** i for i in range(1, self.prefixlength - 1))
+        self.distpfxidx = np.zeros(ndist, dtype=np.uint32)
+        _check(L.gtb200_count(self._ctx, self.leftborder.ctypes.data, self.countspecialcodes.ctypes.data,
+                              self.distpfxidx.ctypes.data if ndist else None, C.byref(info)))
+        self.countinfo = info
+        self.numofsuffixestosort = int(info.numofsuffixestosort)
+        self.specialcharacters = int(info.specialcharacters)
+        self.parts = suftabparts(numofparts, self.leftborder, self.prefixlength)
+        if code_range is not None:  # one shard of a multi-GPU run: a single, externally chosen part
+            lo, hi = code_range
+            self.parts = [(lo, hi, int(self.leftborder[hi + 1]) - int(self.leftborder[lo]))]
+        self._part = 0
+        self._tail_done = False
+        self._longest = None
+        self.lcptabsum = 0.0
+        self.maxbranchdepth = 0
+        self.numoflargelcpvalues = 0
+        self.fallback_suffixes = 0
+        self.fallback_rounds = 0
+        self.partinfos: list[PartInfo] = []
+
+    # -- raw access for the benchmark ---------------------------------------------------------
+    @property
+    def ctx(self):
+        return self._ctx
+
+    def stream_handle(self) -> int:
+        return int(self._L.gtb200_stream(self._ctx))
+
+    def sort_part_device(self, mincode: int, maxcode: int) -> PartInfo:
+        info = PartInfo()
+        _check(self._L.gtb200_sort_part_device(self._ctx, mincode, maxcode, C.byref(info)))
+        return info
+
+    def part_device_pointers(self):
+        a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        _check(self._L.gtb200_part_device(self._ctx, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def _account(self, info: PartInfo) -> None:
+        self.partinfos.append(info)
+        self.lcptabsum += info.lcptabsum
+        self.maxbranchdepth = max(self.maxbranchdepth, int(info.maxbranchdepth))
+        self.numoflargelcpvalues += int(info.numoflargelcpvalues)
+        self.fallback_suffixes += int(info.fallback_suffixes)
+        self.fallback_rounds += int(info.fallback_rounds)
+        if info.longest != UINT64_MAX:
+            self._longest = int(info.longest)
+
+    # -- the reference's iterator protocol ----------------------------------------------------
+    def next(self):
+        """Returns (suftab, lcptab, llv, specialsuffixes) or None when exhausted.
+        suftab: uint64 (uint32 with suftabuint) array of the part; lcptab: uint8 array (255 =
+        overflow) or None for tail pages; llv: structured (position, value) array."""
+        if self._part < len(self.parts):
+            mincode, maxcode, width = self.parts[self._part]
+            self._part += 1
+            suf = np.empty(width, dtype=np.uint32 if self.suftabuint else np.uint64)
+            lcp = np.empty(width, dtype=np.uint8)
+            info = PartInfo()
+            _check(self._L.gtb200_sort_part_device(self._ctx, mincode, maxcode, C.byref(info)))
+            assert info.width == width, (info.width, width)
+            llv = np.zeros((int(info.numoflargelcpvalues), 2), dtype=np.uint64)
+            _check(self._L.gtb200_fetch_part(self._ctx, suf.ctypes.data, 1 if self.suftabuint else 0,
+                                             lcp.ctypes.data, llv.ctypes.data if llv.size else None, llv.shape[0]))
+            self._account(info)
+            return suf, lcp, llv, False
+        if not self._tail_done:
+            self._tail_done = True
+            count = self.specialcharacters + 1
+            suf = np.empty(count, dtype=np.uint32 if self.suftabuint else np.uint64)
+            _check(self._L.gtb200_tail(self._ctx, 0, count, suf.ctypes.data, 1 if self.suftabuint else 0))
+            if self._longest is None:   # position 0 is a special (or the text is empty)
+                hit = np.flatnonzero(suf == 0)
+                if hit.size:
+                    self._longest = self.numofsuffixestosort + int(hit[0])
+            return suf, None, None, True
+        return None
+
+    def longest(self) -> int:
+        return -1 if self._longest is None else self._longest
+
+    def bcktab_bytes(self) -> bytes:
+        """Byte image of the .bck file: the three tables, each zero-padded to 8 bytes
+        (src/match/bcktab.c:519-570, src/core/mapspec.c:350-365)."""
+        def pad8(b):
+            return b + b"\0" * (-len(b) % 8)
+        out = pad8(self.leftborder.tobytes()) + pad8(self.countspecialcodes.tobytes())
+        if self.prefixlength > 2:
+            out += pad8(self.distpfxidx.tobytes())
+        return out
+
+    def bcktab2file(self, fp) -> None:
+        fp.write(self.bcktab_bytes())
+
+    def profile(self, enable: bool | None = None, reset: bool = False):
+        if enable is not None:
+            _check(self._L.gtb200_profile_enable(self._ctx, 1 if enable else 0))
+        if reset:
+            self._L.gtb200_profile_reset(self._ctx)
+            return None
+        names = (C.c_char_p * 32)()
+        ms = (C.c_double * 32)()
+        ln = (C.c_uint64 * 32)()
+        k = self._L.gtb200_profile_read(self._ctx, names, ms, ln, 32)
+        if k < 0:
+            _check(-1)
+        return {names[i].decode(): (ms[i], int(ln[i])) for i in range(k)}
+
+    def delete(self) -> None:
+        if self._ctx:
+            self._L.gtb200_close(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.delete()
+        except Exception:
+            pass
+
+
+def suffixerator(enc: np.ndarray, alphabet: str = "dna", indexname: str | None = None, parts: int = 1,
+                 prefixlength: int | None = None, device: int = 0, use_twobit: bool | None = None) -> dict:
+    """`gt suffixerator -suf -lcp -bck` on an encoded sequence: runs the iterator to exhaustion and
+    returns the byte images of .suf/.lcp/.llv/.bck plus the .prj statistics; writes the files when
+    ``indexname`` is given."""
+    sigma = _encseq.alphabet_size(alphabet)
+    n = int(enc.shape[0])
+    if use_twobit is None:
+        use_twobit = alphabet == "dna"
+    if use_twobit:
+        it = Sfxiterator(sigma, n, prefixlength, parts, twobit=_encseq.twobit_pack(enc),
+                         ranges=_encseq.special_ranges(enc), device=device)
+    else:
+        it = Sfxiterator(sigma, n, prefixlength, parts, enc=enc, device=device)
+    suf_chunks, lcp_chunks, llv_chunks = [], [], []
+    try:
+        while True:
+            r = it.next()
+            if r is None:
+                break
+            suf, lcp, llv, special = r
+            suf_chunks.append(suf.tobytes())
+            if special:
+                lcp_chunks.append(b"\0" * suf.shape[0])   # outmany0lcpvalues (sfx-lcpvalues.c:435-451)
+            else:
+                lcp_chunks.append(lcp.tobytes())
+                llv_chunks.append(llv.tobytes())
+        out = {
+            "suf": b"".join(suf_chunks), "lcp": b"".join(lcp_chunks), "llv": b"".join(llv_chunks),
+            "bck": it.bcktab_bytes(), "prefixlength": it.prefixlength, "longest": it.longest(),
+            "maxbranchdepth": it.maxbranchdepth, "largelcpvalues": it.numoflargelcpvalues,
+            "averagelcp": "%.2f" % (it.lcptabsum / (n + 1)), "numparts": len(it.parts),
+            "fallback_suffixes": it.fallback_suffixes, "fallback_rounds": it.fallback_rounds,
+            "specialcharacters": it.specialcharacters,
+        }
+    finally:
+        it.delete()
+    if indexname:
+        for ext in ("suf", "lcp", "llv", "bck"):
+            with open(f"{indexname}.{ext}", "wb") as fh:
+                fh.write(out[ext])
+    return out

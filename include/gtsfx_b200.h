@@ -1,0 +1,189 @@
+/*
+ * gtsfx_b200.h -- C ABI of libgtsfx_b200.so: the B200 (sm_100a) device layer behind GenomeTools'
+ * enhanced-suffix-array construction path (`gt suffixerator -suf -lcp -bck`).
+ *
+ * The interface this library sits behind is the reference's Sfxiterator API
+ * (src/match/sfx-suffixer.h:33-71, unchanged).  The functions below are what a B200 build of
+ * src/match/sfx-suffixer.c calls instead of its CPU loops; INTEGRATION.md shows that binding.
+ * All pointers are plain host pointers unless a comment says "device"; sizes are explicit; no
+ * C++/torch types appear.  Every function returns 0 on success and -1 on error, in which case
+ * gtb200_last_error() returns a message to copy into GtError (gt_error_set); there is NO CPU
+ * fallback: without a CUDA device gtb200_open fails.
+ *
+ * Citations are relative to the reference checkout (genometools 1.6.7).
+ */
+#ifndef GTSFX_B200_H
+#define GTSFX_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gtb200_ctx gtb200_ctx;
+
+/* GtRange, half-open [start,end): src/core/range_api.h; produced in ascending order by
+ * gt_specialrangeiterator_next (src/core/encseq.c:3745). */
+typedef struct {
+  uint64_t start, end;
+} gtb200_range;
+
+/* Largelcpvalue: src/match/lcpoverflow.h:24-30 -- one 16-byte .llv record. */
+typedef struct {
+  uint64_t position; /* index into the (global) suffix array */
+  uint64_t value;
+} gtb200_largelcp;
+
+#define GTB200_MEM_HOST   0
+#define GTB200_MEM_DEVICE 1
+
+/*
+ * The sequence as the host side already holds it in a GtEncseq.  Give EITHER
+ *  - twobitencoding (+ the special ranges): the words gt_encseq_twobitencoding_export returns
+ *    (src/core/encseq.c:6697; base i in bits 62-2*(i%32) of word i/32, src/core/intbits.h:78-84),
+ *    only for numofchars == 4; OR
+ *  - encoded: one byte per symbol as gt_encseq_extract_encoded delivers them (codes 0..numofchars-1,
+ *    254 = GT_WILDCARD, 255 = GT_SEPARATOR, src/core/chardef_api.h:34-58), any alphabet; the
+ *    special ranges are then derived on the device and the two range fields are ignored.
+ * memory says where ALL pointers of the descriptor live (GTB200_MEM_DEVICE: already resident in
+ * the HBM of `device`, e.g. after an NCCL broadcast).
+ */
+typedef struct {
+  unsigned numofchars;              /* gt_alphabet_num_of_chars */
+  uint64_t totallength;             /* gt_encseq_total_length; must be < 2^32 - 1 */
+  const uint64_t *twobitencoding;
+  uint64_t numofwords;              /* words readable at twobitencoding */
+  const uint8_t *encoded;
+  const gtb200_range *specialranges;
+  uint64_t numofspecialranges;
+  int memory;
+} gtb200_seqdesc;
+
+/* What gt_Sfxiterator_new logs / needs after the counting phase. */
+typedef struct {
+  uint64_t numofallcodes;        /* sigma^prefixlength */
+  uint64_t numofspecialcodes;    /* sigma^(prefixlength-1) */
+  uint64_t numofdistpfxidx;      /* sum_{i=1}^{pl-2} sigma^i (src/match/bcktab.c:240-256) */
+  uint64_t numofsuffixestosort;  /* totallength - specialcharacters */
+  uint64_t specialcharacters;
+  uint64_t largestbucket;        /* return value of gt_bcktab_leftborderpartialsums */
+} gtb200_countinfo;
+
+/* Per-part results the host needs for GtSuffixsortspace, GtOutlcpinfo and the .prj file. */
+typedef struct {
+  uint64_t partoffset;           /* global suffix-array index of the part's first entry */
+  uint64_t width;                /* number of suffixes in the part */
+  uint64_t numoflargelcpvalues;  /* entries with lcp >= 255 (records delivered in llv) */
+  uint64_t maxbranchdepth;       /* max lcp in the part */
+  double   lcptabsum;            /* sum the reference accumulates in outlcpvalues
+                                    (src/match/sfx-lcpvalues.c:414): special-padded entries excluded */
+  uint64_t longest;              /* global index r with suftab[r] == 0, or UINT64_MAX if not in this part */
+  uint64_t fallback_suffixes;    /* diagnostics: suffixes that needed the refinement path */
+  uint64_t fallback_rounds;
+} gtb200_partinfo;
+
+/* -- life cycle ------------------------------------------------------------------------------ */
+
+/* Number of CUDA devices, or -1 (with message) if the CUDA runtime cannot be initialised. */
+int gtb200_device_count(void);
+
+/* Thread-local message of the last failing call. */
+const char *gtb200_last_error(void);
+
+/*
+ * Replaces the sequence set-up at the top of gt_Sfxiterator_new_withadditionalvalues
+ * (src/match/sfx-suffixer.c:1363-1480): uploads the packed sequence, builds the special-position
+ * bitmap and keeps both resident on `device` until gtb200_close.
+ * prefixlength: as chosen by detpfxlen (src/match/sfx-run.c:319-367).
+ */
+int gtb200_open(gtb200_ctx **ctx, int device, const gtb200_seqdesc *seq, unsigned prefixlength);
+void gtb200_close(gtb200_ctx *ctx);
+
+/* The CUDA stream (cudaStream_t) all kernels of this context are launched on; for callers that
+ * time with CUDA events or order their own copies after the kernels. */
+void *gtb200_stream(gtb200_ctx *ctx);
+
+/* -- phase 1: "counting prefix distribution" ------------------------------------------------- */
+
+/*
+ * Replaces updateleftborder_getencseqkmers_twobitencoding (src/match/sfx-mapped4.gen:232-333 as
+ * instantiated at src/match/sfx-suffixer.c:1132-1138), gt_updateleftborderforspecialkmer
+ * (src/match/sfx-suffixer.c:1081-1102), getencseqkmers+updatekmercount for other alphabets
+ * (src/match/sfx-mappedstr.c:728-779, src/match/sfx-suffixer.c:258-337), the counter part of
+ * gt_bcktab_updatespecials (src/match/bcktab.c:876-901) and gt_bcktab_leftborderpartialsums
+ * (src/match/bcktab.c:1274-1304).
+ * Outputs (any may be NULL to skip the copy), 4-byte entries exactly as the .bck file stores them
+ * (src/match/bcktab.c:519-570):
+ *   leftborder[numofallcodes+1]       start index of each bucket; last = numofsuffixestosort
+ *   countspecialcodes[numofspecialcodes]
+ *   distpfxidx[numofdistpfxidx]
+ */
+int gtb200_count(gtb200_ctx *ctx, uint32_t *leftborder, uint32_t *countspecialcodes,
+                 uint32_t *distpfxidx, gtb200_countinfo *info);
+
+/* -- phase 2+3: insert, sort and LCP-annotate one part --------------------------------------- */
+
+/*
+ * Replaces, for the code range [mincode,maxcode] of one part (gt_suftabparts_minindex/maxindex,
+ * src/match/sfx-partssuf.c): sfx_derivespecialcodesonthefly (src/match/sfx-suffixer.c:476-516),
+ * insertsuffix_getencseqkmers_twobitencoding (:1164-1169, :371-399), gt_sortallbuckets
+ * (src/match/sfx-bentsedg.c:1536-1612) with every sorter below it, the in-sort gt_lcptab_update
+ * calls and the bucket-boundary / special-suffix LCP logic of src/match/sfx-lcpvalues.c:91-215,
+ * 591-795.  The result stays in device buffers owned by the context (see gtb200_part_device).
+ * gtb200_count must have been called.
+ */
+int gtb200_sort_part_device(gtb200_ctx *ctx, uint64_t mincode, uint64_t maxcode, gtb200_partinfo *info);
+
+/* Device pointers of the last sorted part: suftab (uint64_t[width]), lcptab (uint8_t[width], 255 =
+ * overflow), llv (gtb200_largelcp[numoflargelcpvalues], ascending position). */
+int gtb200_part_device(gtb200_ctx *ctx, void **suftab_dev, void **lcptab_dev, void **llv_dev);
+
+/*
+ * Copies the last sorted part to host buffers: suftab is GtUword[width] (or uint32_t[width] when
+ * suftab_is_uint32, the reference's -suftabuint, src/match/sfx-suffixgetset.c:48-55), lcptab
+ * uint8_t[width], llv up to llv_capacity records (error if more are needed).  Any may be NULL.
+ */
+int gtb200_fetch_part(gtb200_ctx *ctx, void *suftab, int suftab_is_uint32, uint8_t *lcptab,
+                      gtb200_largelcp *llv, uint64_t llv_capacity);
+
+/* gtb200_sort_part_device followed by gtb200_fetch_part: the one call the patched
+ * gt_sfxiterator_preparethispart (src/match/sfx-suffixer.c:1947-2160) makes. */
+int gtb200_sort_part(gtb200_ctx *ctx, uint64_t mincode, uint64_t maxcode, void *suftab,
+                     int suftab_is_uint32, uint8_t *lcptab, gtb200_largelcp *llv,
+                     uint64_t llv_capacity, gtb200_partinfo *info);
+
+/*
+ * Replaces gt_SSSPbuf_fillspecialnextpage (src/match/sfx-suffixgetset.c:586-690): entries
+ * [first, first+count) of the tail of the suffix array (positions of all special symbols in
+ * ascending order, then totallength; specialcharacters+1 entries in total).
+ */
+int gtb200_tail(gtb200_ctx *ctx, uint64_t first, uint64_t count, void *suftab, int suftab_is_uint32);
+
+/* -- host-side helpers that mirror reference logic the iterator needs (pure C, no device) ---- */
+
+/* gt_recommendedprefixlength with GT_RECOMMENDED_MULTIPLIER_DEFAULT (src/match/sfx-apfxlen.c:82-107). */
+unsigned gtb200_recommendedprefixlength(unsigned numofchars, uint64_t totallength);
+
+/*
+ * gt_suftabparts_new for a whole-range bucket table (src/match/sfx-partssuf.c:172-343 with
+ * gt_bcktab_findfirstlarger, src/match/bcktab.c:1322-1381): splits [0,numofallcodes) into at most
+ * numofparts code ranges of about equal suffix count, empty parts removed.  leftborder = bucket
+ * START offsets as gtb200_count returns them.  mincodes/maxcodes/widths have room for numofparts
+ * entries; returns the number of parts (>= 0).
+ */
+int gtb200_suftabparts(unsigned numofparts, const uint32_t *leftborder, uint64_t numofallcodes,
+                       unsigned prefixlength, uint64_t *mincodes, uint64_t *maxcodes,
+                       uint64_t *widths);
+
+/* Per-kernel-class device time (ms, CUDA events on the context's stream) accumulated since the
+ * last gtb200_profile_reset; names[i] are static strings.  Returns the number of classes. */
+int gtb200_profile_enable(gtb200_ctx *ctx, int on);
+int gtb200_profile_read(gtb200_ctx *ctx, const char **names, double *ms, uint64_t *launches, int capacity);
+void gtb200_profile_reset(gtb200_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GTSFX_B200_H */

@@ -1,0 +1,76 @@
+"""CPU-side checks of the C-ABI library: it loads, exports every symbol include/gtsfx_b200.h declares,
+its pure-host helpers agree with the oracle / the reference, and without a GPU it fails loudly
+instead of falling back to a CPU path."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+from genometools_b200 import sfx, synth
+from oracle import oracle
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _have_gpu():
+    try:
+        return sfx.load_library().gtb200_device_count() > 0
+    except Exception:
+        return False
+
+
+def test_library_exports_header_symbols():
+    L = sfx.load_library()
+    header = open(os.path.join(ROOT, "include", "gtsfx_b200.h")).read()
+    declared = sorted(set(re.findall(r"\b(gtb200_[a-z0-9_]+)\s*\(", header)))
+    assert declared, "no declarations found"
+    for name in declared:
+        assert hasattr(L, name), f"{name} declared in include/gtsfx_b200.h but not exported"
+    assert set(sfx.EXPORTS) <= set(declared)
+
+
+@pytest.mark.parametrize("sigma,n", [(4, 11817), (4, 4_600_000), (4, 250_000_023), (4, 3_100_000_000),
+                                     (20, 1_003_000_000), (4, 9), (20, 5234), (4, 772376), (4, 1), (20, 40519)])
+def test_prefixlength_matches_oracle(sigma, n):
+    assert sfx.recommended_prefixlength(sigma, n) == oracle.recommended_prefixlength(sigma, n)
+
+
+def test_suftabparts_cover_and_balance():
+    rng = np.random.default_rng(0)
+    counts = rng.poisson(3.0, size=4 ** 6).astype(np.uint32)
+    counts[100:400] = 0
+    lb = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint32)
+    total = int(lb[-1])
+    for parts in (1, 2, 3, 7, 8, 64):
+        p = sfx.suftabparts(parts, lb, 6)
+        assert 1 <= len(p) <= parts
+        assert p[0][0] == 0 and p[-1][1] == 4 ** 6 - 1
+        assert sum(w for _, _, w in p) == total
+        for (a0, b0, _), (a1, _, _) in zip(p[:-1], p[1:]):
+            assert a1 == b0 + 1
+        for a, b, w in p:
+            assert w == int(lb[b + 1]) - int(lb[a]) and w > 0
+            assert abs(w - total / parts) <= counts.max() + 1
+    assert len(sfx.suftabparts(4, lb, 1)) == 1  # prefixlength 1 forces one part (sfx-partssuf.c:216-221)
+
+
+@pytest.mark.skipif(not oracle.have_reference(), reason="oracle/_ref/gt_ref not built")
+def test_suftabparts_widths_match_reference_log(tmp_path):
+    from genometools_b200 import encseq
+    enc = synth.multi_dna_with_nruns(50_000, nseq=4, seed=12)
+    fa = str(tmp_path / "x.fna")
+    encseq.write_fasta(fa, encseq.decode_to_fasta_bytes(enc, "dna"))
+    ref = oracle.run_reference(fa, "dna", parts=3)
+    widths = [int(m) for m in re.findall(r"widthofpart\[\d+\]=(\d+)", ref["log"])]
+    o = oracle.build(enc, 4, int(ref["prj"]["prefixlength"]))
+    mine = sfx.suftabparts(3, o["leftborder"], o["prefixlength"])
+    assert [w for _, _, w in mine] == widths
+
+
+@pytest.mark.skipif(_have_gpu(), reason="a GPU is present")
+def test_no_cpu_fallback_without_gpu():
+    enc = synth.random_dna(1000, seed=3)
+    with pytest.raises(sfx.Gtb200Error) as ei:
+        sfx.suffixerator(enc, "dna")
+    assert "no CPU fallback" in str(ei.value) or "CUDA" in str(ei.value)
