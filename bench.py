@@ -1,0 +1,418 @@
+#!/usr/bin/env python
+"""Benchmark of the enhanced-suffix-array path (`gt suffixerator -suf -lcp -bck`) on B200.
+
+    python bench.py --gpus N --steps K --warmup W [--workload ecoli|chr1|human|protein] [--impl reference]
+
+A step = one pass of the whole hot path over one synthetic genome: k-mer counting + bucket prefix
+sums, insertion, in-bucket sort, LCP, tail.  metric = suffixes/s (suffixes = totallength + 1).
+
+ * value : device time of K steps with the packed sequence already resident in HBM (CUDA events on
+           the library's stream, L2 flushed between steps, max over ranks).
+ * e2e   : the same work through the host-facing call (Sfxiterator over the C ABI) with HOST buffers:
+           pinned H2D of the 2-bit sequence + range table, D2H of .suf (8 B/suffix) + .lcp + .bck tables.
+ * N > 1 : one process per GPU.  The genome grows with N (N x the single-GPU size: weak scaling);
+           rank 0 uploads, the packed sequence is broadcast over NCCL, every rank counts (replicated,
+           n/4 bytes) and sorts + LCP-annotates its own bucket range (the reference's -parts split).
+           No collective inside the timed device region.
+ * --impl reference : the UNMODIFIED reference (oracle/_ref/gt_ref, single thread because -lcp forbids
+           -j > 1, src/match/sfx-opt.c:120-126) on the same workload, rank 0 only.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from genometools_b200 import encseq, synth  # noqa: E402
+
+WORKLOADS = {
+    # name: (per-GPU total length, description)
+    "ecoli": (4_600_000, "configs[1]: synthetic 4.6 Mbp single-sequence random DNA (seed 42)"),
+    "chr1": (250_000_000, "configs[2]: synthetic 250 Mbp DNA, 24 sequences, N-runs (seed 250)"),
+    "human": (3_100_000_000, "configs[3]: synthetic 3.1 Gbp multi-FASTA DNA (seed 31)"),
+    "protein": (1_000_000_000, "configs[4]: synthetic 1 G-residue protein set (seed 5)"),
+}
+
+
+def make_workload(name: str, scale: int):
+    per_gpu, _ = WORKLOADS[name]
+    total = per_gpu * scale
+    if name == "ecoli":
+        return synth.random_dna(total, seed=42), "dna"
+    if name == "chr1":
+        return synth.multi_dna_with_nruns(total, nseq=24, seed=250), "dna"
+    if name == "human":
+        return synth.multi_dna_with_nruns(total, nseq=24, seed=31), "dna"
+    return synth.random_protein(max(1, total // 334), seed=5), "protein"
+
+
+def peak_hbm():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device: int):
+        self.path = tempfile.mktemp(prefix="clocks_", suffix=".csv")
+        self.proc = None
+        try:
+            self.fh = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(device), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=self.fh, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.fh.close()
+        sm, mx, reasons = [], [], set()
+        for line in open(self.path):
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.path)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def write_fasta_for(enc, alphabet, path):
+    encseq.write_fasta(path, encseq.decode_to_fasta_bytes(enc, alphabet))
+
+
+def run_reference_once(fasta, alphabet):
+    from oracle import oracle
+    ref = oracle.run_reference(fasta, alphabet, showtime=True)
+    t = ref["times"]
+    path_s = sum(t.get(k, 0.0) for k in ("counting prefix distribution", "inserting suffixes into buckets",
+                                          "sorting the buckets"))
+    return ref["wall_s"], t.get("overall", ref["wall_s"]), path_s
+
+
+def cpu_baseline(enc, alphabet, budget_n=12_000_000):
+    """The reference's own CPU implementation on a bounded sample of the workload (rank 0, N=1)."""
+    from oracle import oracle
+    n = enc.shape[0]
+    sample = enc if n <= budget_n else enc[:budget_n]
+    what = "whole workload" if n <= budget_n else f"first {budget_n} symbols of the workload"
+    if oracle.have_reference():
+        with tempfile.TemporaryDirectory() as tmp:
+            fa = os.path.join(tmp, "sample.fna")
+            write_fasta_for(sample, alphabet, fa)
+            wall, overall, path_s = run_reference_once(fa, alphabet)
+        secs = max(overall, 1e-9)
+        return {"value": (sample.shape[0] + 1) / secs, "unit": "suffixes/s", "cores": 1, "kind": "reference",
+                "sample": f"{what}; oracle/_ref/gt_ref suffixerator -suf -lcp -bck -tis, 1 thread (-lcp forbids -j>1), "
+                          f"TIME overall {overall:.2f} s of which count+insert+sort {path_s:.2f} s, wall {wall:.2f} s",
+                "host_cores_available": os.cpu_count()}
+    small = sample[:2_000_000]
+    t0 = time.perf_counter()
+    oracle.build(small, encseq.alphabet_size(alphabet))
+    secs = time.perf_counter() - t0
+    return {"value": (small.shape[0] + 1) / secs, "unit": "suffixes/s", "cores": 1, "kind": "port",
+            "sample": f"first {small.shape[0]} symbols, oracle/sfx_oracle.c (reference binary not built)",
+            "host_cores_available": os.cpu_count()}
+
+
+def bench_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import oracle
+    enc, alphabet = make_workload(args.workload, args.gpus)
+    budget = 12_000_000
+    sample = enc if enc.shape[0] <= budget else enc[:budget]
+    what = "whole workload" if sample is enc else f"first {budget} symbols"
+    times = []
+    kind = "reference" if oracle.have_reference() else "port"
+    with tempfile.TemporaryDirectory() as tmp:
+        fa = os.path.join(tmp, "w.fna")
+        write_fasta_for(sample, alphabet, fa)
+        for i in range(args.warmup + args.steps):
+            if kind == "reference":
+                _, overall, _ = run_reference_once(fa, alphabet)
+            else:
+                t0 = time.perf_counter()
+                oracle.build(sample, encseq.alphabet_size(alphabet))
+                overall = time.perf_counter() - t0
+            if i >= args.warmup:
+                times.append(overall)
+    per = sum(times) / len(times)
+    value = (sample.shape[0] + 1) / per
+    line = {
+        "impl": "reference", "metric": "suffixes/sec for SA+LCP", "value": value, "unit": "suffixes/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": per * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": WORKLOADS[args.workload][1], "totallength": int(enc.shape[0]), "sample": what},
+        "cpu_baseline": {"value": value, "unit": "suffixes/s", "cores": 1, "kind": kind,
+                         "sample": f"{what}; gt suffixerator -suf -lcp -bck -tis, single thread (the reference "
+                                   f"refuses -lcp with -j>1), TIME overall per run"},
+        "e2e": {"value": value, "unit": "suffixes/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="ecoli", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-steps", type=int, default=None)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        bench_reference(args)
+        return
+
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    from genometools_b200 import sfx
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    L = sfx.load_library()
+    alphabet = "protein" if args.workload == "protein" else "dna"
+    sigma = encseq.alphabet_size(alphabet)
+
+    # ---- inputs: rank 0 synthesises, packs and pins; NCCL broadcast puts them in every GPU's HBM ----
+    meta = torch.zeros(3, dtype=torch.int64, device=dev)
+    enc = None
+    if rank == 0:
+        enc, _ = make_workload(args.workload, world)
+        n = int(enc.shape[0])
+        if alphabet == "dna":
+            words_h = torch.from_numpy(encseq.twobit_pack(enc).view(np.int64)).pin_memory()
+            ranges_h = torch.from_numpy(encseq.special_ranges(enc).astype(np.uint64).view(np.int64).reshape(-1)).pin_memory()
+        else:
+            words_h = torch.from_numpy(enc).pin_memory()
+            ranges_h = torch.zeros(0, dtype=torch.int64).pin_memory()
+        meta = torch.tensor([n, words_h.numel(), ranges_h.numel()], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.broadcast(meta, 0)
+    n, nwords, nrangewords = (int(x) for x in meta.tolist())
+    wdtype = torch.int64 if alphabet == "dna" else torch.uint8
+    words_d = torch.empty(nwords, dtype=wdtype, device=dev)
+    ranges_d = torch.empty(max(nrangewords, 1), dtype=torch.int64, device=dev)
+
+    def upload_and_broadcast():
+        if rank == 0:
+            words_d.copy_(words_h, non_blocking=True)
+            if nrangewords:
+                ranges_d[:nrangewords].copy_(ranges_h, non_blocking=True)
+        if world > 1:
+            dist.broadcast(words_d, 0)
+            if nrangewords:
+                dist.broadcast(ranges_d, 0)
+        torch.cuda.synchronize()
+
+    def open_iter():
+        if alphabet == "dna":
+            return sfx.Sfxiterator(sigma, n, None, world, twobit=words_d.data_ptr(), ranges=ranges_d.data_ptr(),
+                                   numofwords=nwords, numofranges=nrangewords // 2, device=local, device_ptrs=True)
+        return sfx.Sfxiterator(sigma, n, None, world, enc=words_d.data_ptr(), device=local, device_ptrs=True)
+
+    upload_and_broadcast()
+    it = open_iter()
+    parts = it.parts
+    if len(parts) != world:
+        raise SystemExit(f"bucket table splits into {len(parts)} parts, {world} ranks")
+    mincode, maxcode, width = parts[rank]
+    stream = torch.cuda.ExternalStream(it.stream_handle(), device=dev)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
+    info = sfx.CountInfo()
+
+    def device_step():
+        sfx._check(L.gtb200_count(it.ctx, None, None, None, C.byref(info)))
+        pinfo = it.sort_part_device(mincode, maxcode)
+        if rank == world - 1:
+            sfx._check(L.gtb200_tail(it.ctx, 0, it.specialcharacters + 1, None, 0))
+        return pinfo
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        with torch.cuda.stream(stream):
+            flush.zero_()
+        device_step()
+    it.profile(enable=True)
+    it.profile(reset=True)
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    evs = []
+    t_wall0 = time.perf_counter()
+    pinfo = None
+    for _ in range(args.steps):
+        with torch.cuda.stream(stream):
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        pinfo = device_step()
+        b.record(stream)
+        evs.append((a, b))
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    clocks = sampler.stop() if sampler else None
+    dev_ms = sum(a.elapsed_time(b) for a, b in evs)
+    prof = it.profile()
+    it.profile(enable=False)
+    t = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms = float(t.item())
+    ms_per_step = dev_ms / args.steps
+    value = (n + 1) / (ms_per_step * 1e-3)
+
+    # ---- e2e: host buffers in, host buffers out, through the Sfxiterator mirror ----
+    e2e_steps = args.e2e_steps or max(2, min(args.steps, 5))
+    suf_h = torch.empty(width + (it.specialcharacters + 1 if rank == world - 1 else 0), dtype=torch.int64).pin_memory()
+    lcp_h = torch.empty(max(width, 1), dtype=torch.uint8).pin_memory()
+    suf_np, lcp_np = suf_h.numpy().view(np.uint64), lcp_h.numpy()
+    numcodes = sigma ** it.prefixlength
+    lb_h = torch.empty(numcodes + 1, dtype=torch.int32).pin_memory()
+    csc_h = torch.empty(sigma ** (it.prefixlength - 1), dtype=torch.int32).pin_memory()
+    dist_h = torch.empty(max(1, int(it.countinfo.numofdistpfxidx)), dtype=torch.int32).pin_memory()
+    it.delete()
+
+    def e2e_step():
+        upload_and_broadcast()                                  # pinned H2D (rank 0) + NVLink broadcast
+        it2 = open_iter_raw()
+        sfx._check(L.gtb200_count(it2, lb_h.data_ptr(), csc_h.data_ptr(), dist_h.data_ptr(), C.byref(info)))
+        pi = sfx.PartInfo()
+        sfx._check(L.gtb200_sort_part(it2, mincode, maxcode, suf_np.ctypes.data, 0, lcp_np.ctypes.data, None, 0,
+                                      C.byref(pi)))
+        if rank == world - 1:
+            sfx._check(L.gtb200_tail(it2, 0, int(info.specialcharacters) + 1, suf_np[width:].ctypes.data, 0))
+        L.gtb200_close(it2)
+        return pi
+
+    def open_iter_raw():
+        desc = sfx.SeqDesc()
+        desc.numofchars, desc.totallength, desc.memory = sigma, n, 1
+        if alphabet == "dna":
+            desc.twobitencoding, desc.numofwords = words_d.data_ptr(), nwords
+            desc.specialranges, desc.numofspecialranges = ranges_d.data_ptr(), nrangewords // 2
+        else:
+            desc.encoded = words_d.data_ptr()
+        ctx = C.c_void_p()
+        sfx._check(L.gtb200_open(C.byref(ctx), local, C.byref(desc), it.prefixlength))
+        return ctx
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item())
+    h2d = (words_h.numel() * words_h.element_size() + ranges_h.numel() * 8) if rank == 0 else 0
+    d2h = suf_h.numel() * 8 + width + (numcodes + 1) * 4 + csc_h.numel() * 4 + int(it.countinfo.numofdistpfxidx) * 4
+    tb = torch.tensor([h2d, d2h], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(tb)
+    h2d, d2h = (int(x) for x in tb.tolist())
+
+    if rank == 0:
+        # ---- roofline of the dominant kernel class (rank 0's profile; all ranks do the same work) ----
+        bits = 2 if alphabet == "dna" else 8
+        text_bytes = n * bits / 8 + n / 8                       # packed text + special bitmap, read once
+        m = width
+        algo = {   # algorithmic bytes per step and kernel class (DESIGN.md "Kernels")
+            "count": text_bytes + 4 * numcodes,
+            "scan": 8 * numcodes,
+            "scatter": text_bytes + 4 * m,
+            "sort_lcp": (4 + 8 + 4 + 1) * m,                    # pos in, 8-byte text window, pos out, lcp out
+            "boundary": 8 * (maxcode - mincode + 1),
+            "widen": 12 * m,
+        }
+        kern = {k: v for k, v in prof.items() if v[1] > 0}
+        total_ms = sum(v[0] for v in kern.values())
+        dominant = max((k for k in kern if k in algo), key=lambda k: kern[k][0])
+        d_ms, d_launches = kern[dominant]
+        launches_per_step = max(1, d_launches // args.steps)
+        per_launch_s = d_ms * 1e-3 / d_launches
+        achieved = algo[dominant] / launches_per_step / per_launch_s / 1e9
+        peak, peak_src = peak_hbm()
+        line = {
+            "metric": "suffixes/sec for SA+LCP", "value": value, "unit": "suffixes/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u32 positions / u64 keys", "data": "synthetic",
+            "config": {"workload": WORKLOADS[args.workload][1] + (f" x{world} (genome grows with N)" if world > 1 else ""),
+                       "totallength": n, "prefixlength": it.prefixlength, "suffixes": n + 1,
+                       "sharding": f"{world} bucket ranges (-parts split), text broadcast over NCCL",
+                       "l2": "flushed (256 MiB write) before every timed step",
+                       "fallback_suffixes": int(pinfo.fallback_suffixes)},
+            "e2e": {"value": (n + 1) / e2e_s, "unit": "suffixes/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "steps": e2e_steps},
+            "gpu_launches": int(sum(v[1] for v in kern.values())),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": algo[dominant] / launches_per_step,
+                         "avg_launch_ms": per_launch_s * 1e3,
+                         "share_of_step": d_ms / total_ms if total_ms else None,
+                         "whole_path_frac": (n + 1) / world * (9.25 if alphabet == "dna" else 9.625)
+                                            / (ms_per_step * 1e-3) / 1e9 / peak},
+            "kernel_ms_per_step": {k: round(v[0] / args.steps, 5) for k, v in kern.items()},
+            "wall_s_timed_region": t_wall,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(enc, alphabet)
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

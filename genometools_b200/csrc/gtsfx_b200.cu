@@ -92,6 +92,7 @@ struct gtb200_ctx {
   uint64_t padcap, npadded;
   uint64_t *d_padkey;        // (code << 6) | (pl - reallen), sorted
   uint32_t *d_padpos;
+  uint32_t *d_padcnt;
   uint64_t specialchars, nsort, largestbucket;
   bool counted;
   uint32_t sort_maxbucket;   // buckets above this size take the refinement path (testing knob)
@@ -898,7 +899,7 @@ static void free_ctx(gtb200_ctx *c) {
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   void *ptrs[] = {c->d_text, c->d_mask, c->d_ranges, c->d_rangeoff, c->d_lb, c->d_cursor, c->d_csc, c->d_dist,
-                  c->d_padkey, c->d_padpos, c->d_sa, c->d_lcp, c->d_suf64, c->d_fbbits, c->d_llv, c->d_stats,
+                  c->d_padkey, c->d_padpos, c->d_padcnt, c->d_sa, c->d_lcp, c->d_suf64, c->d_fbbits, c->d_llv, c->d_stats,
                   c->d_tilesums, c->d_scratch};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (c->h_stats) cudaFreeHost(c->h_stats);
@@ -1075,10 +1076,18 @@ template <int BITS>
 static int count_impl(gtb200_ctx *c) {
   const Text<BITS> T = text_of<BITS>(c);
   const uint64_t n = c->n;
-  CK(cudaMalloc(&c->d_lb, (c->numcodes + 2) * 4));
-  CK(cudaMalloc(&c->d_cursor, (c->numcodes + 2) * 4));
-  CK(cudaMalloc(&c->d_csc, (c->numspecialcodes + 1) * 4));
-  CK(cudaMalloc(&c->d_dist, (c->numdist + 1) * 4));
+  const uint64_t nr1 = c->nranges + 1;
+  if (!c->d_lb) {                            // first call: allocate the tables once
+    c->padcap = nr1 * (c->cp.pl - 1) + 1;
+    CK(cudaMalloc(&c->d_lb, (c->numcodes + 2) * 4));
+    CK(cudaMalloc(&c->d_cursor, (c->numcodes + 2) * 4));
+    CK(cudaMalloc(&c->d_csc, (c->numspecialcodes + 1) * 4));
+    CK(cudaMalloc(&c->d_dist, (c->numdist + 1) * 4));
+    CK(cudaMalloc(&c->d_padcnt, (nr1 + 1) * 4));
+    CK(cudaMalloc(&c->d_padkey, c->padcap * 8));
+    CK(cudaMalloc(&c->d_padpos, c->padcap * 4));
+  }
+  uint32_t *cntoff = c->d_padcnt;
   CK(cudaMemsetAsync(c->d_lb, 0, (c->numcodes + 2) * 4, c->stream));
   CK(cudaMemsetAsync(c->d_csc, 0, (c->numspecialcodes + 1) * 4, c->stream));
   CK(cudaMemsetAsync(c->d_dist, 0, (c->numdist + 1) * 4, c->stream));
@@ -1088,12 +1097,6 @@ static int count_impl(gtb200_ctx *c) {
     k_kmers<BITS, 0><<<grid_for((n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, n, c->d_lb, nullptr, 0, 0, 0);
   }
   // special-padded suffixes
-  const uint64_t nr1 = c->nranges + 1;
-  c->padcap = nr1 * (c->cp.pl - 1) + 1;
-  uint32_t *cntoff;
-  CK(cudaMalloc(&cntoff, (nr1 + 1) * 4));
-  CK(cudaMalloc(&c->d_padkey, c->padcap * 8));
-  CK(cudaMalloc(&c->d_padpos, c->padcap * 4));
   {
     ProfScope ps(c, KC_PADDED);
     k_padded<BITS, 0><<<grid_for(nr1, 128), 128, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, cntoff, nullptr,
@@ -1111,7 +1114,6 @@ static int count_impl(gtb200_ctx *c) {
   }
   if (device_scan(c, c->d_lb, c->d_lb, c->numcodes, 1, &c->d_stats->scan_total2)) return -1;
   if (sync_stats(c)) return -1;
-  CK(cudaFree(cntoff));
   c->npadded = c->h_stats->scan_total;
   c->largestbucket = c->h_stats->largest;
   if (c->h_stats->scan_total2 != c->nsort)
@@ -1145,7 +1147,7 @@ extern "C" int gtb200_count(gtb200_ctx *c, uint32_t *leftborder, uint32_t *count
                             gtb200_countinfo *info) {
   if (!c) return set_error("gtb200_count: null context");
   CK(cudaSetDevice(c->device));
-  if (!c->counted) {
+  {                                           // recomputed on every call (the tables are reused)
     const int rc = c->bits == 2 ? count_impl<2>(c) : count_impl<8>(c);
     if (rc) return rc;
   }

@@ -4,7 +4,10 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from genometools_b200 import sfx, synth, encseq
 from oracle import oracle
-from tests.conftest import golden_names, load_golden
+import importlib.util
+_spec = importlib.util.spec_from_file_location('gt_conftest', os.path.join(os.path.dirname(os.path.abspath(__file__)), 'conftest.py'))
+_cf = importlib.util.module_from_spec(_spec); _spec.loader.exec_module(_cf)
+golden_names, load_golden = _cf.golden_names, _cf.load_golden
 
 def cmp(got, want, label):
     bad = []

@@ -48,7 +48,8 @@ def test_golden_vectors_refinement_only(golden, monkeypatch):
     monkeypatch.setenv("GTB200_MAXBUCKET", "0")
     got = sfx.suffixerator(golden["enc"], golden["alphabet"], parts=2, prefixlength=golden["prefixlength"])
     _compare(got, golden, f"{golden['name']}/refine")
-    assert got["fallback_suffixes"] > 0 or golden["totallength"] < 16
+    if golden["maxbranchdepth"] > 0:   # some bucket holds at least two suffixes
+        assert got["fallback_suffixes"] > 0
 
 
 CASES = {
