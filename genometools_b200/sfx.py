@@ -68,6 +68,7 @@ EXPORTS = [
     "gtb200_count", "gtb200_sort_part_device", "gtb200_part_device", "gtb200_fetch_part",
     "gtb200_sort_part", "gtb200_tail", "gtb200_recommendedprefixlength", "gtb200_suftabparts",
     "gtb200_profile_enable", "gtb200_profile_read", "gtb200_profile_reset",
+    "gtb200_leftborder_partialsums_noalloc",
 ]
 
 
@@ -102,6 +103,8 @@ def load_library() -> C.CDLL:
                                       C.POINTER(C.c_uint64), C.c_int]
     L.gtb200_profile_reset.argtypes = [C.c_void_p]
     L.gtb200_profile_reset.restype = None
+    L.gtb200_leftborder_partialsums_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
+                                                        C.c_char_p, C.c_size_t]
     _lib = L
     return L
 

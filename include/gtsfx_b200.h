@@ -183,6 +183,33 @@ int gtb200_profile_enable(gtb200_ctx *ctx, int on);
 int gtb200_profile_read(gtb200_ctx *ctx, const char **names, double *ms, uint64_t *launches, int capacity);
 void gtb200_profile_reset(gtb200_ctx *ctx);
 
+/* -- entry point that never allocates -------------------------------------------------------- */
+
+/*
+ * No counterpart in the reference: this exists for hosts that cannot let a library allocate device
+ * memory - an application whose own pool already owns all of the GPU's memory (a library cudaMalloc
+ * would fail or fragment it), or one that cannot afford the device-wide synchronisation hidden in
+ * cudaMalloc/cudaFree while its other streams are busy.
+ *
+ * It is the prefix-sum step of gtb200_count on its own: from the bucket sizes counts_dev[0 ..
+ * numofallcodes) it writes the bucket start offsets leftborder_dev[0 .. numofallcodes] (last entry =
+ * total), both in device memory owned by the caller; leftborder_dev may be the same buffer as
+ * counts_dev if it has room for the extra entry.  The partial sums go to a fixed array inside the
+ * library (about 64 KB, resident on every GPU that loads the library until the process ends), so
+ * no cudaMalloc/cudaFree or other allocating call is made.  numofallcodes above
+ * GTB200_NOALLOC_MAX_CODES (4^13, the table of a 3.1 Gbp DNA index) is rejected with an error.
+ * The first call on a device resolves the array's address; issue it before starting any stream
+ * capture.  The array is shared by all calls on that device and keeps the previous call's
+ * contents - what must start at zero is cleared on entry - so calls that run concurrently on one
+ * GPU corrupt each other; keep them on one stream or otherwise serialised.
+ * Work is enqueued on `stream` (a cudaStream_t, NULL = default stream) of the current device and
+ * is asynchronous.  Returns 0, or -1 with a message in errbuf (may be NULL).
+ */
+#define GTB200_NOALLOC_MAX_CODES 67108864ull
+int gtb200_leftborder_partialsums_noalloc(const uint32_t *counts_dev, uint32_t *leftborder_dev,
+                                          uint64_t numofallcodes, void *stream, char *errbuf,
+                                          size_t errbuf_len);
+
 #ifdef __cplusplus
 }
 #endif
