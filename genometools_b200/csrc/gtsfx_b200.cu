@@ -16,6 +16,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <vector>
 
 #include "../../include/gtsfx_b200.h"
@@ -66,13 +67,15 @@ struct PartStats {          // lives in device memory, mirrored to pinned host m
   unsigned long long longest;
   unsigned long long scan_total;
   unsigned long long scan_total2;
+  unsigned long long bsum;       // bucket-boundary part of lcpsum
   unsigned int maxdepth;
   unsigned int fb_buckets;
   unsigned int largest;
-  unsigned int pad_;
+  unsigned int bmax;             // bucket-boundary part of maxdepth
 };
 
 struct ProfEvent { int cls; cudaEvent_t a, b; };
+struct PoolBlock { void *p; size_t sz; };
 
 struct gtb200_ctx {
   int device;
@@ -112,6 +115,7 @@ struct gtb200_ctx {
   uint64_t cap_tilesums;
   void *d_scratch;
   size_t cap_scratch;
+  std::vector<PoolBlock> blocks;   // every device allocation of this context
   // profiling
   bool prof_on;
   std::vector<ProfEvent> pending;
@@ -167,6 +171,84 @@ struct ProfScope {
   }
 };
 
+// ---------------------------------------------------------------------------------------------
+// Device memory: every buffer comes from a process-wide cache of freed blocks, so that opening a
+// context for the next sequence (or the next benchmark step) costs no cudaMalloc/cudaFree - both
+// are expensive and cudaFree synchronises the device.  gtb200_release_cached_memory() empties it.
+// ---------------------------------------------------------------------------------------------
+static std::mutex g_pool_mu;
+static std::vector<PoolBlock> g_pool[64];
+static std::vector<void *> g_pinned_pool;
+
+static void pool_release_device(int dev) {   // caller holds g_pool_mu
+  for (auto &b : g_pool[dev]) cudaFree(b.p);
+  g_pool[dev].clear();
+}
+
+template <typename T>
+static cudaError_t dmalloc(gtb200_ctx *c, T **out, size_t bytes) {
+  bytes = (bytes + 511) & ~(size_t)511;
+  if (bytes == 0) bytes = 512;
+  void *p = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_pool_mu);
+    auto &fl = g_pool[c->device];
+    size_t best = (size_t)-1;
+    for (size_t i = 0; i < fl.size(); ++i)
+      if (fl[i].sz >= bytes && fl[i].sz <= bytes + bytes / 4 + (1u << 16) &&
+          (best == (size_t)-1 || fl[i].sz < fl[best].sz))
+        best = i;
+    if (best != (size_t)-1) {
+      p = fl[best].p;
+      bytes = fl[best].sz;
+      fl[best] = fl.back();
+      fl.pop_back();
+    }
+  }
+  if (!p) {
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) {                  // give cached blocks back to the driver and retry once
+      (void)cudaGetLastError();
+      {
+        std::lock_guard<std::mutex> lock(g_pool_mu);
+        pool_release_device(c->device);
+      }
+      e = cudaMalloc(&p, bytes);
+      if (e != cudaSuccess) return e;
+    }
+  }
+  c->blocks.push_back({p, bytes});
+  *out = (T *)p;
+  return cudaSuccess;
+}
+
+static void dfree(gtb200_ctx *c, void *p) {
+  if (!p) return;
+  if (c->stream) cudaStreamSynchronize(c->stream);   // the block may be handed to another context
+  for (size_t i = 0; i < c->blocks.size(); ++i)
+    if (c->blocks[i].p == p) {
+      std::lock_guard<std::mutex> lock(g_pool_mu);
+      g_pool[c->device].push_back(c->blocks[i]);
+      c->blocks[i] = c->blocks.back();
+      c->blocks.pop_back();
+      return;
+    }
+}
+
+extern "C" void gtb200_release_cached_memory(void) {
+  std::lock_guard<std::mutex> lock(g_pool_mu);
+  int cur = 0;
+  cudaGetDevice(&cur);
+  for (int d = 0; d < 64; ++d)
+    if (!g_pool[d].empty()) {
+      cudaSetDevice(d);
+      pool_release_device(d);
+    }
+  for (void *h : g_pinned_pool) cudaFreeHost(h);
+  g_pinned_pool.clear();
+  cudaSetDevice(cur);
+}
+
 static inline unsigned grid_for(uint64_t n, unsigned per_block) {
   uint64_t g = (n + per_block - 1) / per_block;
   if (g == 0) g = 1;
@@ -175,20 +257,20 @@ static inline unsigned grid_for(uint64_t n, unsigned per_block) {
 
 static int ensure_scratch(gtb200_ctx *c, size_t bytes) {
   if (bytes <= c->cap_scratch) return 0;
-  if (c->d_scratch) CK(cudaFree(c->d_scratch));
+  dfree(c, c->d_scratch);
   c->d_scratch = nullptr;
   c->cap_scratch = 0;
-  CK(cudaMalloc(&c->d_scratch, bytes));
+  CK(dmalloc(c, &c->d_scratch, bytes));
   c->cap_scratch = bytes;
   return 0;
 }
 
 static int ensure_tilesums(gtb200_ctx *c, uint64_t ntiles) {
   if (ntiles <= c->cap_tilesums) return 0;
-  if (c->d_tilesums) CK(cudaFree(c->d_tilesums));
+  dfree(c, c->d_tilesums);
   c->d_tilesums = nullptr;
   c->cap_tilesums = 0;
-  CK(cudaMalloc(&c->d_tilesums, (ntiles + 1) * sizeof(uint32_t)));
+  CK(dmalloc(c, &c->d_tilesums, (ntiles + 1) * sizeof(uint32_t)));
   c->cap_tilesums = ntiles;
   return 0;
 }
@@ -432,6 +514,72 @@ __global__ void k_padded(Text<BITS> T, CodeParams cp, uint64_t n, const gtb200_r
   }
 }
 
+// Few special ranges (a genome with a handful of N-runs, or none): enumerate, count and sort the
+// special-padded suffixes in ONE single-block launch instead of two passes + scan + radix passes.
+#define PADSMALL_CAP 2048
+template <int BITS>
+__global__ void __launch_bounds__(256) k_padded_small(Text<BITS> T, CodeParams cp, uint64_t n,
+                                                      const gtb200_range *__restrict__ ranges, uint64_t nranges,
+                                                      uint32_t *__restrict__ hist, uint32_t *__restrict__ csc,
+                                                      uint32_t *__restrict__ dist, uint64_t *__restrict__ padkey,
+                                                      uint32_t *__restrict__ padpos, unsigned long long *npadded) {
+  __shared__ uint64_t skey[PADSMALL_CAP];
+  __shared__ uint32_t spos[PADSMALL_CAP];
+  __shared__ uint32_t sm[8];
+  const unsigned pl = cp.pl;
+  uint32_t carry = 0;
+  for (uint64_t base = 0; base <= nranges; base += 256) {
+    const uint64_t k = base + threadIdx.x;
+    unsigned cnt = 0;
+    uint64_t s0 = 0;
+    if (k <= nranges) {
+      s0 = k < nranges ? ranges[k].start : n;
+      const uint64_t prev_end = k ? ranges[k - 1].end : 0;
+      const uint64_t avail = s0 - prev_end;
+      cnt = (unsigned)(avail < pl - 1 ? avail : pl - 1);
+    }
+    uint32_t tot;
+    const uint32_t off = carry + block_excl_scan256(cnt, &tot, sm);
+    for (unsigned j = 1; j <= cnt; ++j) {
+      const uint64_t p = s0 - j;
+      const uint64_t pv = prefix_value<BITS>(T.window(p), j, cp);
+      const uint64_t fill = cp.pw[pl - j] - 1;
+      const uint64_t code = pv * (fill + 1) + fill;
+      atomicAdd(&hist[code], 1u);
+      atomicAdd(&csc[(code - (cp.sigma - 1)) / cp.sigma], 1u);
+      if (j + 1 < pl) {
+        uint64_t doff = 0;
+        for (unsigned i = 1; i < j; ++i) doff += cp.pw[i];
+        atomicAdd(&dist[doff + pv], 1u);
+      }
+      skey[off + (cnt - j)] = (code << 6) | (uint64_t)(pl - j);
+      spos[off + (cnt - j)] = (uint32_t)p;
+    }
+    carry += tot;
+  }
+  const uint32_t total = carry;
+  uint32_t P = 1;
+  while (P < total) P <<= 1;
+  __syncthreads();
+  for (uint32_t i = total + threadIdx.x; i < P; i += 256) { skey[i] = ~0ull; spos[i] = 0xffffffffu; }
+  __syncthreads();
+  for (uint32_t size = 2; size <= P; size <<= 1) {
+    for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+      for (uint32_t i = threadIdx.x; i < P / 2; i += 256) {
+        const uint32_t lo = 2 * i - (i & (stride - 1)), hi = lo + stride;
+        const bool asc = ((lo & size) == 0);
+        const uint64_t ka = skey[lo], kb = skey[hi];
+        const uint32_t pa = spos[lo], pb = spos[hi];
+        const bool gt = ka > kb || (ka == kb && pa > pb);
+        if (gt == asc) { skey[lo] = kb; skey[hi] = ka; spos[lo] = pb; spos[hi] = pa; }
+      }
+      __syncthreads();
+    }
+  }
+  for (uint32_t i = threadIdx.x; i < total; i += 256) { padkey[i] = skey[i]; padpos[i] = spos[i]; }
+  if (threadIdx.x == 0) *npadded = total;
+}
+
 __global__ void k_max_u32(const uint32_t *__restrict__ a, uint64_t n, unsigned int *out) {
   uint32_t m = 0;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
@@ -587,14 +735,122 @@ __device__ __forceinline__ bool warp_sort_bucket(const Text<BITS> &T, const Part
   return true;
 }
 
+// 32-bit variant: keys are (12 leading bases of the window << 8) | slot; min/max network
+template <int E>
+struct WarpSorter32 {
+  __device__ static __forceinline__ void sort(uint32_t (&k)[E], int lane) {
+#pragma unroll
+    for (int size = 2; size <= 32 * E; size <<= 1) {
+#pragma unroll
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        if (stride >= 32) {
+          const int es = stride >> 5;
+#pragma unroll
+          for (int e = 0; e < E; ++e) {
+            if ((e & es) == 0) {
+              const bool asc = (((e * 32) & size) == 0);
+              const uint32_t lo = min(k[e], k[e | es]), hi = max(k[e], k[e | es]);
+              k[e] = asc ? lo : hi;
+              k[e | es] = asc ? hi : lo;
+            }
+          }
+        } else {
+#pragma unroll
+          for (int e = 0; e < E; ++e) {
+            const uint32_t o = __shfl_xor_sync(GTB_FULL, k[e], stride);
+            const bool keepmin = ((((e * 32 + lane) & size) == 0) == ((lane & stride) == 0));
+            k[e] = keepmin ? min(k[e], o) : max(k[e], o);
+          }
+        }
+      }
+    }
+  }
+};
+
 #define SORT_MAXBUCKET 256
+#define SORT_WARPS 8
+
+// Fast path: order the bucket by the 12 bases that follow the prefix (one 32-bit compare per
+// network step), full 64-bit keys parked in shared memory and fetched by slot afterwards.  The
+// order is then verified with the full keys; any pair it does not strictly separate (equal 12-mers
+// whose rest is out of order, ties, cut-off suffixes) sends the bucket to the exact 64-bit sorter.
+// Returns 0 = done, 1 = redo with warp_sort_bucket.
+template <int BITS, int E>
+__device__ __forceinline__ int warp_sort_bucket32(const Text<BITS> &T, const PartOut &out, uint32_t start, uint32_t cnt,
+                                                  unsigned pl, int lane, uint64_t *skey, uint32_t *spos,
+                                                  unsigned long long &sum, uint32_t &mx) {
+  uint32_t k[E];
+  __syncwarp();
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    const uint32_t i = e * 32 + lane;
+    k[e] = 0xffffffffu;
+    if (i < cnt) {
+      const uint32_t p = out.sa[start + i];
+      const uint64_t fk = make_key<BITS>(T, (uint64_t)p + pl);
+      skey[i] = fk;
+      spos[i] = p;
+      k[e] = ((uint32_t)(fk >> 40) << 8) | i;
+    }
+  }
+  __syncwarp();
+  WarpSorter32<E>::sort(k, lane);
+  uint64_t fk[E];
+  uint32_t l[E];
+  bool bad = false;
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    const uint32_t i = e * 32 + lane;
+    fk[e] = (i < cnt) ? skey[k[e] & 0xff] : ~0ull;
+  }
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    uint64_t pk = __shfl_up_sync(GTB_FULL, fk[e], 1);
+    const uint64_t last = (e > 0) ? __shfl_sync(GTB_FULL, fk[e > 0 ? e - 1 : 0], 31) : 0ull;
+    if (lane == 0) pk = last;
+    const uint32_t i = e * 32 + lane;
+    l[e] = 0;
+    if (i >= 1 && i < cnt) {
+      if (pk >= fk[e]) bad = true;
+      l[e] = pl + key_common<BITS>(pk, fk[e]);
+    }
+  }
+  if (__any_sync(GTB_FULL, bad)) return 1;
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    const uint32_t i = e * 32 + lane;
+    if (i < cnt) {
+      out.sa[start + i] = spos[k[e] & 0xff];
+      if (i >= 1) {
+        out.lcp[start + i] = (uint8_t)l[e];
+        sum += l[e];
+        mx = max(mx, l[e]);
+      }
+    }
+  }
+  return 0;
+}
+
+template <int BITS, int E>
+__device__ __forceinline__ bool warp_sort_any(const Text<BITS> &T, const PartOut &out, uint32_t start, uint32_t cnt,
+                                              unsigned pl, int lane, uint64_t *skey, uint32_t *spos,
+                                              unsigned long long &sum, uint32_t &mx) {
+  if (BITS == 2) {
+    if (warp_sort_bucket32<BITS, E>(T, out, start, cnt, pl, lane, skey, spos, sum, mx) == 0) return true;
+  }
+  return warp_sort_bucket<BITS, E>(T, out, start, cnt, pl, lane, sum, mx);
+}
 
 template <int BITS>
 __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out, const uint32_t *__restrict__ lb,
                                                       const uint32_t *__restrict__ cursor, uint64_t mincode,
                                                       uint64_t maxcode, unsigned pl, uint32_t *__restrict__ fbbits,
                                                       uint32_t maxbucket) {
+  __shared__ uint64_t s_key[SORT_WARPS][SORT_MAXBUCKET];
+  __shared__ uint32_t s_pos[SORT_WARPS][SORT_MAXBUCKET];
   const int lane = threadIdx.x & 31;
+  uint64_t *skey = s_key[threadIdx.x >> 5];
+  uint32_t *spos = s_pos[threadIdx.x >> 5];
   const uint64_t gw = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const uint64_t nw = ((uint64_t)gridDim.x * blockDim.x) >> 5;
   unsigned long long sum = 0;
@@ -606,10 +862,10 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
     const uint32_t start = b0 - out.partoffset;
     bool ok = false;
     if (cnt > maxbucket) ok = false;
-    else if (cnt <= 32) ok = warp_sort_bucket<BITS, 1>(T, out, start, cnt, pl, lane, sum, mx);
-    else if (cnt <= 64) ok = warp_sort_bucket<BITS, 2>(T, out, start, cnt, pl, lane, sum, mx);
-    else if (cnt <= 128) ok = warp_sort_bucket<BITS, 4>(T, out, start, cnt, pl, lane, sum, mx);
-    else if (cnt <= SORT_MAXBUCKET) ok = warp_sort_bucket<BITS, 8>(T, out, start, cnt, pl, lane, sum, mx);
+    else if (cnt <= 32) ok = warp_sort_any<BITS, 1>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
+    else if (cnt <= 64) ok = warp_sort_any<BITS, 2>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
+    else if (cnt <= 128) ok = warp_sort_any<BITS, 4>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
+    else if (cnt <= SORT_MAXBUCKET) ok = warp_sort_any<BITS, 8>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
     if (!ok && lane == 0) {
       const uint64_t rel = c - mincode;
       atomicOr(&fbbits[rel >> 5], 1u << (rel & 31));
@@ -795,21 +1051,33 @@ template <int BITS>
 __global__ void k_boundary(Text<BITS> T, PartOut out, const uint32_t *__restrict__ lb, uint64_t mincode,
                            uint64_t maxcode, unsigned pl) {
   const uint64_t c = mincode + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (c > maxcode) return;
-  const uint32_t b0 = lb[c];
-  if (lb[c + 1] == b0) return;
-  const uint32_t r = b0 - out.partoffset;
-  if (r == 0) return;                       // first entry of the part: k_part_first
-  const uint32_t a = out.sa[r - 1], b = out.sa[r];
-  unsigned la = T.reallen(a), lbn = T.reallen(b);
-  const uint64_t x = T.window(a) ^ T.window(b);
-  unsigned common = x ? (unsigned)__clzll((long long)x) / BITS : 64u / BITS;
-  unsigned l = common < la ? common : la;
-  l = l < lbn ? l : lbn;
-  if (l > pl) l = pl;                       // cannot happen for different buckets; defensive
-  out.lcp[r] = (uint8_t)l;
-  if (lbn >= pl && l) atomicAdd(&out.stats->lcpsum, (unsigned long long)l);
-  if (l) atomicMax(&out.stats->maxdepth, l);
+  unsigned long long sum = 0;
+  uint32_t mx = 0;
+  if (c <= maxcode) {
+    const uint32_t b0 = lb[c];
+    const uint32_t r = b0 - out.partoffset;
+    if (lb[c + 1] != b0 && r != 0) {          // non-empty and not the first entry of the part (k_part_first)
+      const uint32_t a = out.sa[r - 1], b = out.sa[r];
+      const unsigned la = T.reallen(a), lbn = T.reallen(b);
+      const uint64_t x = T.window(a) ^ T.window(b);
+      const unsigned common = x ? (unsigned)__clzll((long long)x) / BITS : 64u / BITS;
+      unsigned l = common < la ? common : la;
+      l = l < lbn ? l : lbn;
+      if (l > pl) l = pl;                     // cannot happen for different buckets; defensive
+      out.lcp[r] = (uint8_t)l;
+      if (lbn >= pl) sum = l;                 // special-padded entries do not enter lcptabsum
+      mx = l;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sum += __shfl_xor_sync(GTB_FULL, sum, o);
+    mx = max(mx, __shfl_xor_sync(GTB_FULL, mx, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (sum) atomicAdd(&out.stats->bsum, sum);
+    if (mx) atomicMax(&out.stats->bmax, mx);
+  }
 }
 
 // first entry of a part that is not the first part: its left neighbour lives on another device /
@@ -858,8 +1126,29 @@ __global__ void k_part_first(Text<BITS> T, CodeParams cp, PartOut out, const uin
   unsigned l = common < la ? common : la;
   l = l < lbn ? l : lbn;
   out.lcp[0] = (uint8_t)l;
-  if (lbn >= pl && l) atomicAdd(&out.stats->lcpsum, (unsigned long long)l);
-  if (l) atomicMax(&out.stats->maxdepth, l);
+  if (lbn >= pl && l) atomicAdd(&out.stats->bsum, (unsigned long long)l);
+  if (l) atomicMax(&out.stats->bmax, l);
+}
+
+// per-part initialisation in one launch: scatter cursors, refinement flags, statistics
+__global__ void k_part_init(const uint32_t *__restrict__ lb, uint32_t *__restrict__ cursor, uint64_t mincode,
+                            uint64_t ncodes, uint32_t *__restrict__ fbbits, uint64_t fbwords, PartStats *stats,
+                            uint8_t *lcp) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < ncodes) cursor[mincode + i] = lb[mincode + i];
+  if (i < fbwords) fbbits[i] = 0;
+  if (i == 0) {
+    PartStats z;
+    memset(&z, 0, sizeof z);
+    z.longest = ~0ull;
+    *stats = z;
+    lcp[0] = 0;
+  }
+}
+
+__global__ void k_reset_boundary_stats(PartStats *stats) {
+  stats->bsum = 0;
+  stats->bmax = 0;
 }
 
 __global__ void k_widen(const uint32_t *__restrict__ sa, uint64_t width, uint64_t *__restrict__ out64,
@@ -898,11 +1187,12 @@ static void free_ctx(gtb200_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
-  void *ptrs[] = {c->d_text, c->d_mask, c->d_ranges, c->d_rangeoff, c->d_lb, c->d_cursor, c->d_csc, c->d_dist,
-                  c->d_padkey, c->d_padpos, c->d_padcnt, c->d_sa, c->d_lcp, c->d_suf64, c->d_fbbits, c->d_llv, c->d_stats,
-                  c->d_tilesums, c->d_scratch};
-  for (void *p : ptrs) if (p) cudaFree(p);
-  if (c->h_stats) cudaFreeHost(c->h_stats);
+  {
+    std::lock_guard<std::mutex> lock(g_pool_mu);
+    for (auto &b : c->blocks) g_pool[c->device].push_back(b);
+    c->blocks.clear();
+    if (c->h_stats) g_pinned_pool.push_back(c->h_stats);
+  }
   for (auto &p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
   for (auto e : c->evpool) cudaEventDestroy(e);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -935,10 +1225,14 @@ static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
   const uint64_t nchunks = (n >> 6) + 1;
   c->nmaskwords = nchunks + 2;
   c->ntextwords = nchunks * (64 / spw) + 2;
-  CK(cudaMalloc(&c->d_text, c->ntextwords * 8));
-  CK(cudaMalloc(&c->d_mask, c->nmaskwords * 8));
-  CK(cudaMalloc(&c->d_stats, sizeof(PartStats)));
-  CK(cudaMallocHost(&c->h_stats, sizeof(PartStats)));
+  CK(dmalloc(c, &c->d_text, c->ntextwords * 8));
+  CK(dmalloc(c, &c->d_mask, c->nmaskwords * 8));
+  CK(dmalloc(c, &c->d_stats, sizeof(PartStats)));
+  {
+    std::lock_guard<std::mutex> lock(g_pool_mu);
+    if (!g_pinned_pool.empty()) { c->h_stats = (PartStats *)g_pinned_pool.back(); g_pinned_pool.pop_back(); }
+  }
+  if (!c->h_stats) CK(cudaMallocHost(&c->h_stats, 256));
   CK(cudaMemsetAsync(c->d_stats, 0, sizeof(PartStats), c->stream));
   CK(cudaMemsetAsync(c->d_text, 0, c->ntextwords * 8, c->stream));
   CK(cudaMemsetAsync(c->d_mask, 0, c->nmaskwords * 8, c->stream));
@@ -951,7 +1245,7 @@ static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
       if (nw) CK(cudaMemcpyAsync(c->d_text, seq->twobitencoding, nw * 8, h2d, c->stream));
     }
     c->nranges = seq->numofspecialranges;
-    CK(cudaMalloc(&c->d_ranges, (c->nranges + 1) * sizeof(gtb200_range)));
+    CK(dmalloc(c, &c->d_ranges, (c->nranges + 1) * sizeof(gtb200_range)));
     if (c->nranges) {
       CK(cudaMemcpyAsync(c->d_ranges, seq->specialranges, c->nranges * sizeof(gtb200_range), h2d, c->stream));
       ProfScope ps(c, KC_PREP);
@@ -961,7 +1255,7 @@ static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
     const uint8_t *d_enc = seq->encoded;
     uint8_t *tmp = nullptr;
     if (seq->memory != GTB200_MEM_DEVICE) {
-      CK(cudaMalloc(&tmp, n ? n : 1));
+      CK(dmalloc(c, &tmp, n ? n : 1));
       if (n) CK(cudaMemcpyAsync(tmp, seq->encoded, n, cudaMemcpyHostToDevice, c->stream));
       d_enc = tmp;
     }
@@ -972,8 +1266,8 @@ static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
     }
     // derive the special ranges from the bitmap
     uint32_t *cnt, *popc;
-    CK(cudaMalloc(&cnt, (nchunks + 1) * 4));
-    CK(cudaMalloc(&popc, (nchunks + 1) * 4));
+    CK(dmalloc(c, &cnt, (nchunks + 1) * 4));
+    CK(dmalloc(c, &popc, (nchunks + 1) * 4));
     {
       ProfScope ps(c, KC_PREP);
       k_runs_count<<<grid_for(nchunks, 256), 256, 0, c->stream>>>(c->d_mask, n, nchunks, cnt, popc);
@@ -981,15 +1275,15 @@ static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
     if (device_scan(c, cnt, cnt, nchunks, 0, &c->d_stats->scan_total, KC_PREP)) return -1;
     if (sync_stats(c)) return -1;
     c->nranges = c->h_stats->scan_total;
-    CK(cudaMalloc(&c->d_ranges, (c->nranges + 1) * sizeof(gtb200_range)));
+    CK(dmalloc(c, &c->d_ranges, (c->nranges + 1) * sizeof(gtb200_range)));
     if (c->nranges) {
       ProfScope ps(c, KC_PREP);
       k_runs_write<<<grid_for(nchunks, 256), 256, 0, c->stream>>>(c->d_mask, n, nchunks, cnt, c->d_ranges);
     }
     CK(cudaStreamSynchronize(c->stream));
-    CK(cudaFree(cnt));
-    CK(cudaFree(popc));
-    if (tmp) CK(cudaFree(tmp));
+    dfree(c, cnt);
+    dfree(c, popc);
+    dfree(c, tmp);
   }
   {
     ProfScope ps(c, KC_PREP);
@@ -997,7 +1291,7 @@ static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
     k_mask_tail<<<grid_for(tailwords, 64), 64, 0, c->stream>>>(c->d_mask, n, c->nmaskwords);
   }
   // tail paging table: exclusive scan of range lengths; total = specialcharacters
-  CK(cudaMalloc(&c->d_rangeoff, (c->nranges + 2) * 4));
+  CK(dmalloc(c, &c->d_rangeoff, (c->nranges + 2) * 4));
   if (c->nranges) {
     {
       ProfScope ps(c, KC_PREP);
@@ -1077,36 +1371,42 @@ static int count_impl(gtb200_ctx *c) {
   const Text<BITS> T = text_of<BITS>(c);
   const uint64_t n = c->n;
   const uint64_t nr1 = c->nranges + 1;
-  if (!c->d_lb) {                            // first call: allocate the tables once
+  const uint64_t tablewords = (c->numcodes + 2) + (c->numspecialcodes + 1) + (c->numdist + 1);
+  if (!c->d_lb) {                            // first call: allocate the tables once, contiguously
     c->padcap = nr1 * (c->cp.pl - 1) + 1;
-    CK(cudaMalloc(&c->d_lb, (c->numcodes + 2) * 4));
-    CK(cudaMalloc(&c->d_cursor, (c->numcodes + 2) * 4));
-    CK(cudaMalloc(&c->d_csc, (c->numspecialcodes + 1) * 4));
-    CK(cudaMalloc(&c->d_dist, (c->numdist + 1) * 4));
-    CK(cudaMalloc(&c->d_padcnt, (nr1 + 1) * 4));
-    CK(cudaMalloc(&c->d_padkey, c->padcap * 8));
-    CK(cudaMalloc(&c->d_padpos, c->padcap * 4));
+    CK(dmalloc(c, &c->d_lb, tablewords * 4));
+    c->d_csc = c->d_lb + (c->numcodes + 2);
+    c->d_dist = c->d_csc + (c->numspecialcodes + 1);
+    CK(dmalloc(c, &c->d_cursor, (c->numcodes + 2) * 4));
+    CK(dmalloc(c, &c->d_padcnt, (nr1 + 1) * 4));
+    CK(dmalloc(c, &c->d_padkey, c->padcap * 8));
+    CK(dmalloc(c, &c->d_padpos, c->padcap * 4));
   }
+  const bool small = nr1 <= PADSMALL_CAP && c->padcap <= PADSMALL_CAP;
   uint32_t *cntoff = c->d_padcnt;
-  CK(cudaMemsetAsync(c->d_lb, 0, (c->numcodes + 2) * 4, c->stream));
-  CK(cudaMemsetAsync(c->d_csc, 0, (c->numspecialcodes + 1) * 4, c->stream));
-  CK(cudaMemsetAsync(c->d_dist, 0, (c->numdist + 1) * 4, c->stream));
+  CK(cudaMemsetAsync(c->d_lb, 0, tablewords * 4, c->stream));
   CK(cudaMemsetAsync(c->d_stats, 0, sizeof(PartStats), c->stream));
   if (n) {
     ProfScope ps(c, KC_COUNT);
     k_kmers<BITS, 0><<<grid_for((n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, n, c->d_lb, nullptr, 0, 0, 0);
   }
   // special-padded suffixes
-  {
+  if (small) {
     ProfScope ps(c, KC_PADDED);
-    k_padded<BITS, 0><<<grid_for(nr1, 128), 128, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, cntoff, nullptr,
-                                                                 nullptr, nullptr, nullptr, nullptr);
-  }
-  if (device_scan(c, cntoff, cntoff, nr1, 0, &c->d_stats->scan_total, KC_PADDED)) return -1;
-  {
-    ProfScope ps(c, KC_PADDED);
-    k_padded<BITS, 1><<<grid_for(nr1, 128), 128, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, cntoff, c->d_lb,
-                                                                 c->d_csc, c->d_dist, c->d_padkey, c->d_padpos);
+    k_padded_small<BITS><<<1, 256, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, c->d_lb, c->d_csc, c->d_dist,
+                                                   c->d_padkey, c->d_padpos, &c->d_stats->scan_total);
+  } else {
+    {
+      ProfScope ps(c, KC_PADDED);
+      k_padded<BITS, 0><<<grid_for(nr1, 128), 128, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, cntoff, nullptr,
+                                                                   nullptr, nullptr, nullptr, nullptr);
+    }
+    if (device_scan(c, cntoff, cntoff, nr1, 0, &c->d_stats->scan_total, KC_PADDED)) return -1;
+    {
+      ProfScope ps(c, KC_PADDED);
+      k_padded<BITS, 1><<<grid_for(nr1, 128), 128, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, cntoff, c->d_lb,
+                                                                   c->d_csc, c->d_dist, c->d_padkey, c->d_padpos);
+    }
   }
   {
     ProfScope ps(c, KC_COUNT);
@@ -1119,8 +1419,8 @@ static int count_impl(gtb200_ctx *c) {
   if (c->h_stats->scan_total2 != c->nsort)
     return set_error("internal: bucket counts sum to %llu, expected %llu", c->h_stats->scan_total2,
                      (unsigned long long)c->nsort);
-  // sort the padded list by (code, pl-L); stable, so positions stay ascending
-  if (c->npadded > 1) {
+  // large lists: sort by (code, pl-L); stable, so positions stay ascending
+  if (!small && c->npadded > 1) {
     const uint32_t np = (uint32_t)c->npadded;
     const uint32_t nblocks = grid_for(np, RS_TILE);
     const size_t need = (size_t)np * (8 + 8 + 4 + 4) + (256ull * nblocks + 1) * 4 + 64;
@@ -1170,20 +1470,20 @@ extern "C" int gtb200_count(gtb200_ctx *c, uint32_t *leftborder, uint32_t *count
 
 static int ensure_part_buffers(gtb200_ctx *c, uint64_t width, uint64_t ncodes_in_part) {
   if (width > c->cap_width) {
-    if (c->d_sa) CK(cudaFree(c->d_sa));
-    if (c->d_lcp) CK(cudaFree(c->d_lcp));
-    if (c->d_suf64) CK(cudaFree(c->d_suf64));
+    dfree(c, c->d_sa);
+    dfree(c, c->d_lcp);
+    dfree(c, c->d_suf64);
     c->d_sa = nullptr; c->d_lcp = nullptr; c->d_suf64 = nullptr; c->cap_width = 0;
-    CK(cudaMalloc(&c->d_sa, (width + 1) * 4));
-    CK(cudaMalloc(&c->d_lcp, width + 1));
-    CK(cudaMalloc(&c->d_suf64, (width + 1) * 8));
+    CK(dmalloc(c, &c->d_sa, (width + 1) * 4));
+    CK(dmalloc(c, &c->d_lcp, width + 1));
+    CK(dmalloc(c, &c->d_suf64, (width + 1) * 8));
     c->cap_width = width;
   }
   const uint64_t fbwords = (ncodes_in_part + 31) / 32 + 1;
   if (fbwords > c->cap_fbwords) {
-    if (c->d_fbbits) CK(cudaFree(c->d_fbbits));
+    dfree(c, c->d_fbbits);
     c->d_fbbits = nullptr; c->cap_fbwords = 0;
-    CK(cudaMalloc(&c->d_fbbits, fbwords * 4));
+    CK(dmalloc(c, &c->d_fbbits, fbwords * 4));
     c->cap_fbwords = fbwords;
   }
   return 0;
@@ -1200,9 +1500,9 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   info->fallback_suffixes = A0;
   // llv append buffer: at most one value per refined suffix
   if (A0 > c->cap_llv) {
-    if (c->d_llv) CK(cudaFree(c->d_llv));
+    dfree(c, c->d_llv);
     c->d_llv = nullptr; c->cap_llv = 0;
-    CK(cudaMalloc(&c->d_llv, ((size_t)A0 + 1) * sizeof(gtb200_largelcp)));
+    CK(dmalloc(c, &c->d_llv, ((size_t)A0 + 1) * sizeof(gtb200_largelcp)));
     c->cap_llv = A0;
   }
   PartOut out = out_in;
@@ -1325,13 +1625,18 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
 template <int BITS>
 static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb200_partinfo *info) {
   const Text<BITS> T = text_of<BITS>(c);
-  // part geometry from the bucket table
-  uint32_t h_lb[2];
-  CK(cudaMemcpyAsync(&h_lb[0], c->d_lb + mincode, 4, cudaMemcpyDeviceToHost, c->stream));
-  CK(cudaMemcpyAsync(&h_lb[1], c->d_lb + maxcode + 1, 4, cudaMemcpyDeviceToHost, c->stream));
-  CK(cudaStreamSynchronize(c->stream));
-  const uint64_t partoffset = h_lb[0], width = (uint64_t)h_lb[1] - h_lb[0];
+  // part geometry from the bucket table (known without a round trip when the part is everything)
+  uint64_t partoffset = 0, width = c->nsort;
+  if (!(mincode == 0 && maxcode == c->numcodes - 1)) {
+    uint32_t h_lb[2];
+    CK(cudaMemcpyAsync(&h_lb[0], c->d_lb + mincode, 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(&h_lb[1], c->d_lb + maxcode + 1, 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    partoffset = h_lb[0];
+    width = (uint64_t)h_lb[1] - h_lb[0];
+  }
   const uint64_t ncodes = maxcode - mincode + 1;
+  const uint64_t fbwords = (ncodes + 31) / 32;
   memset(info, 0, sizeof *info);
   info->partoffset = partoffset;
   info->width = width;
@@ -1341,11 +1646,6 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
   c->part_nllv = 0;
   if (width == 0) return 0;
   if (ensure_part_buffers(c, width, ncodes)) return -1;
-  CK(cudaMemsetAsync(c->d_stats, 0, sizeof(PartStats), c->stream));
-  CK(cudaMemsetAsync(&c->d_stats->longest, 0xff, 8, c->stream));
-  CK(cudaMemsetAsync(c->d_fbbits, 0, ((ncodes + 31) / 32 + 1) * 4, c->stream));
-  CK(cudaMemsetAsync(c->d_lcp, 0, width, c->stream));
-  CK(cudaMemcpyAsync(c->d_cursor + mincode, c->d_lb + mincode, ncodes * 4, cudaMemcpyDeviceToDevice, c->stream));
   PartOut out;
   out.sa = c->d_sa;
   out.lcp = c->d_lcp;
@@ -1353,7 +1653,9 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
   out.stats = c->d_stats;
   out.partoffset = (uint32_t)partoffset;
   {
-    ProfScope ps(c, KC_SCATTER);
+    ProfScope ps(c, KC_SCATTER, 2);
+    k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, fbwords,
+                                                              c->d_stats, c->d_lcp);
     k_kmers<BITS, 1><<<grid_for((c->n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, c->n, c->d_cursor, c->d_sa, mincode,
                                                                             maxcode, (uint32_t)partoffset);
   }
@@ -1368,26 +1670,32 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
     k_sort_buckets<BITS><<<grid_for(warps * 32, 256), 256, 0, c->stream>>>(T, out, c->d_lb, c->d_cursor, mincode, maxcode,
                                                                           c->cp.pl, c->d_fbbits, c->sort_maxbucket);
   }
-  CK(cudaGetLastError());
-  if (sync_stats(c)) return -1;
-  if (c->h_stats->fb_elems) {
+  // Bucket borders and the 64-bit image are launched right away: in the common case (no bucket
+  // needs refinement) the part is finished with a single host round trip.  If refinement was
+  // needed, both are simply repeated on the final order.
+  for (int pass = 0; pass < 2; ++pass) {
+    {
+      ProfScope ps(c, KC_BOUNDARY, partoffset > 0 ? 2 : 1);
+      k_boundary<BITS><<<grid_for(ncodes, 256), 256, 0, c->stream>>>(T, out, c->d_lb, mincode, maxcode, c->cp.pl);
+      if (partoffset > 0)
+        k_part_first<BITS><<<1, 32, 0, c->stream>>>(T, c->cp, out, c->d_lb, c->numcodes, c->d_csc, c->d_padkey, c->npadded);
+    }
+    {
+      ProfScope ps(c, KC_WIDEN);
+      k_widen<<<grid_for(width, 256), 256, 0, c->stream>>>(c->d_sa, width, c->d_suf64, partoffset, c->d_stats);
+    }
+    CK(cudaGetLastError());
+    if (sync_stats(c)) return -1;
+    if (pass == 1 || c->h_stats->fb_elems == 0) break;
     if (refine_impl<BITS>(c, out, mincode, maxcode, width, info)) return -1;
+    {
+      ProfScope ps(c, KC_BOUNDARY);
+      k_reset_boundary_stats<<<1, 1, 0, c->stream>>>(c->d_stats);
+    }
   }
-  {
-    ProfScope ps(c, KC_BOUNDARY);
-    k_boundary<BITS><<<grid_for(ncodes, 256), 256, 0, c->stream>>>(T, out, c->d_lb, mincode, maxcode, c->cp.pl);
-    if (partoffset > 0)
-      k_part_first<BITS><<<1, 32, 0, c->stream>>>(T, c->cp, out, c->d_lb, c->numcodes, c->d_csc, c->d_padkey, c->npadded);
-  }
-  {
-    ProfScope ps(c, KC_WIDEN);
-    k_widen<<<grid_for(width, 256), 256, 0, c->stream>>>(c->d_sa, width, c->d_suf64, partoffset, c->d_stats);
-  }
-  CK(cudaGetLastError());
-  if (sync_stats(c)) return -1;
   info->numoflargelcpvalues = c->h_stats->llv_count;
-  info->maxbranchdepth = c->h_stats->maxdepth;
-  info->lcptabsum = (double)c->h_stats->lcpsum;
+  info->maxbranchdepth = c->h_stats->maxdepth > c->h_stats->bmax ? c->h_stats->maxdepth : c->h_stats->bmax;
+  info->lcptabsum = (double)(c->h_stats->lcpsum + c->h_stats->bsum);
   info->longest = c->h_stats->longest;
   c->part_nllv = c->h_stats->llv_count;
   return 0;

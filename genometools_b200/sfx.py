@@ -68,7 +68,7 @@ EXPORTS = [
     "gtb200_count", "gtb200_sort_part_device", "gtb200_part_device", "gtb200_fetch_part",
     "gtb200_sort_part", "gtb200_tail", "gtb200_recommendedprefixlength", "gtb200_suftabparts",
     "gtb200_profile_enable", "gtb200_profile_read", "gtb200_profile_reset",
-    "gtb200_leftborder_partialsums_noalloc",
+    "gtb200_leftborder_partialsums_noalloc", "gtb200_release_cached_memory",
 ]
 
 

@@ -101,6 +101,11 @@ const char *gtb200_last_error(void);
 int gtb200_open(gtb200_ctx **ctx, int device, const gtb200_seqdesc *seq, unsigned prefixlength);
 void gtb200_close(gtb200_ctx *ctx);
 
+/* Device buffers of closed contexts are kept in a process-wide cache so that the next gtb200_open
+ * costs no cudaMalloc/cudaFree (gt_Sfxiterator_delete followed by a new iterator, e.g. in
+ * src/match/esa-mmsearch.c:609-636).  This returns the cached memory to the driver. */
+void gtb200_release_cached_memory(void);
+
 /* The CUDA stream (cudaStream_t) all kernels of this context are launched on; for callers that
  * time with CUDA events or order their own copies after the kernels. */
 void *gtb200_stream(gtb200_ctx *ctx);
