@@ -191,6 +191,7 @@ def main():
     ap.add_argument("--workload", default="ecoli", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=None)
+    ap.add_argument("--skip-e2e", action="store_true", help="exploratory runs only: leaves e2e out of the line")
     args = ap.parse_args()
     if args.impl == "reference":
         bench_reference(args)

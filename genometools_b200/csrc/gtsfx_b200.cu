@@ -99,6 +99,7 @@ struct gtb200_ctx {
   uint64_t specialchars, nsort, largestbucket;
   bool counted;
   uint32_t sort_maxbucket;   // buckets above this size take the refinement path (testing knob)
+  uint64_t twolevel_bytes;   // parts whose 4-byte suffix array exceeds this use the two-level insertion
   // per part
   uint64_t cap_width;
   uint32_t *d_sa;
@@ -477,6 +478,125 @@ __global__ void __launch_bounds__(256) k_kmers(Text<BITS> T, CodeParams cp, uint
       }
     }
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Two-level insertion for parts whose suffix array does not fit L2.  A direct scatter writes 4
+// bytes to a random place in a multi-GB array: every store evicts a partially filled sector.
+// Instead k_partition first groups (code,pos) records by the leading bits of the code into <= 1024
+// coarse bins (block-local histogram in shared memory, one global reservation per block and bin,
+// so each bin is written as a stream), and k_scatter_records then walks the records in order:
+// neighbouring records now hit a 64 KB slice of the cursor table and a few MB of the suffix array,
+// both L2-resident, where the 4-byte stores are combined into full sectors.
+// ---------------------------------------------------------------------------------------------
+#define PT_MAXBINS 2048
+
+template <int BITS>
+__global__ void __launch_bounds__(256) k_partition(Text<BITS> T, CodeParams cp, uint64_t n, uint64_t mincode,
+                                                    uint64_t maxcode, int shift, uint32_t nbins,
+                                                    uint32_t *__restrict__ gcursor, uint64_t *__restrict__ rec) {
+  __shared__ uint32_t h[PT_MAXBINS];
+  for (uint32_t i = threadIdx.x; i < nbins; i += 256) h[i] = 0;
+  __syncthreads();
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t p0 = t << 5;
+  const unsigned pl = cp.pl;
+  const uint64_t plmask = (1ull << pl) - 1ull;
+  uint64_t mw = ~0ull, hi = 0, lo = 0;
+  if (p0 < n) {
+    mw = T.maskwin(p0);
+    if (BITS == 2) { hi = __ldg(T.w + t); lo = __ldg(T.w + t + 1); }
+  }
+  uint32_t rk[16];   // rank of each of the 32 positions inside its bin (block-local, < 8192): two per word
+#pragma unroll
+  for (int i = 0; i < 16; ++i) rk[i] = 0;
+  // pass 0: block-local rank = old value of the shared-memory bin counter
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    if (p0 < n && ((mw >> i) & plmask) == 0) {
+      uint64_t win;
+      if (BITS == 2) win = i ? (hi << (2 * i)) | (lo >> (64 - 2 * i)) : hi;
+      else win = T.window(p0 + i);
+      const uint64_t code = prefix_value<BITS>(win, pl, cp);
+      if (code >= mincode && code <= maxcode) {
+        const uint32_t r = atomicAdd(&h[(uint32_t)((code - mincode) >> shift)], 1u);
+        rk[i >> 1] |= r << ((i & 1) * 16);
+      }
+    }
+  }
+  __syncthreads();
+  // one global reservation per (block, bin); h[] becomes the bin's base offset for this block
+  for (uint32_t i = threadIdx.x; i < nbins; i += 256) {
+    const uint32_t cnt = h[i];
+    h[i] = cnt ? atomicAdd(&gcursor[i], cnt) : 0u;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    if (p0 < n && ((mw >> i) & plmask) == 0) {
+      uint64_t win;
+      if (BITS == 2) win = i ? (hi << (2 * i)) | (lo >> (64 - 2 * i)) : hi;
+      else win = T.window(p0 + i);
+      const uint64_t code = prefix_value<BITS>(win, pl, cp);
+      if (code >= mincode && code <= maxcode) {
+        const uint32_t r = (rk[i >> 1] >> ((i & 1) * 16)) & 0xffffu;
+        rec[h[(uint32_t)((code - mincode) >> shift)] + r] = (code << 32) | (uint64_t)(uint32_t)(p0 + i);
+      }
+    }
+  }
+}
+
+// record offsets of the coarse bins = suffix-array offsets of their first bucket
+__global__ void k_partition_init(const uint32_t *__restrict__ lb, uint64_t mincode, int shift, uint32_t nbins,
+                                 uint32_t partoffset, uint32_t *gcursor) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < nbins) gcursor[j] = lb[mincode + ((uint64_t)j << shift)] - partoffset;
+}
+
+// slots a bin did not fill (its special-padded members are inserted separately) are marked empty
+__global__ void k_partition_gaps(const uint32_t *__restrict__ gcursor, const uint32_t *__restrict__ lb, uint64_t mincode,
+                                 uint64_t maxcode, int shift, uint32_t nbins, uint32_t partoffset, uint64_t *rec) {
+  const uint32_t j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (j >= nbins) return;
+  uint64_t next = mincode + ((uint64_t)(j + 1) << shift);
+  if (next > maxcode + 1) next = maxcode + 1;
+  const uint32_t end = lb[next] - partoffset;
+  for (uint32_t i = gcursor[j] + lane; i < end; i += 32) rec[i] = ~0ull;
+}
+
+// second level with the bin's slice of the cursor table in shared memory: one block per coarse bin
+__global__ void __launch_bounds__(1024) k_scatter_bins(const uint64_t *__restrict__ rec, const uint32_t *__restrict__ gcursor,
+                                                        const uint32_t *__restrict__ lb, uint32_t *__restrict__ cursor,
+                                                        uint32_t *__restrict__ sa, uint64_t mincode, uint64_t maxcode,
+                                                        int shift, uint32_t partoffset) {
+  extern __shared__ uint32_t scur[];
+  const uint32_t j = blockIdx.x;
+  const uint64_t c0 = mincode + ((uint64_t)j << shift);
+  uint64_t c1 = c0 + (1ull << shift);
+  if (c1 > maxcode + 1) c1 = maxcode + 1;
+  const uint32_t ncf = (uint32_t)(c1 - c0);
+  for (uint32_t i = threadIdx.x; i < ncf; i += blockDim.x) scur[i] = lb[c0 + i];
+  __syncthreads();
+  const uint32_t rbeg = lb[c0] - partoffset, rend = gcursor[j];
+  for (uint32_t i = rbeg + threadIdx.x; i < rend; i += blockDim.x) {
+    const uint64_t r = rec[i];
+    const uint32_t slot = atomicAdd(&scur[(uint32_t)((r >> 32) - c0)], 1u);
+    sa[slot - partoffset] = (uint32_t)r;
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < ncf; i += blockDim.x) cursor[c0 + i] = scur[i];
+}
+
+__global__ void __launch_bounds__(256) k_scatter_records(const uint64_t *__restrict__ rec, uint64_t width,
+                                                          uint32_t *__restrict__ cursor, uint32_t *__restrict__ sa,
+                                                          uint32_t partoffset) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= width) return;
+  const uint64_t r = rec[i];
+  if (r == ~0ull) return;
+  const uint32_t slot = atomicAdd(&cursor[r >> 32], 1u);
+  sa[slot - partoffset] = (uint32_t)r;
 }
 
 // Special-padded suffixes: for every special range (and the virtual end at n) the up to pl-1
@@ -1361,6 +1481,8 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
     const long v = atol(e2);
     if (v >= 0 && v < SORT_MAXBUCKET) c->sort_maxbucket = (uint32_t)v;
   }
+  c->twolevel_bytes = 48ull << 20;
+  if (const char *e3 = getenv("GTB200_TWOLEVEL_BYTES")) c->twolevel_bytes = strtoull(e3, nullptr, 10);   // testing knob
   if (open_impl(c, seq)) { free_ctx(c); return -1; }
   *out = c;
   return 0;
@@ -1652,12 +1774,37 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
   out.llv = nullptr;
   out.stats = c->d_stats;
   out.partoffset = (uint32_t)partoffset;
-  {
+  const bool twolevel = width * 4 > c->twolevel_bytes && ncodes >= 4096;
+  if (!twolevel) {
     ProfScope ps(c, KC_SCATTER, 2);
     k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, fbwords,
                                                               c->d_stats, c->d_lcp);
     k_kmers<BITS, 1><<<grid_for((c->n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, c->n, c->d_cursor, c->d_sa, mincode,
                                                                             maxcode, (uint32_t)partoffset);
+  } else {
+    int shift = 0;
+    while (((ncodes - 1) >> shift) + 1 > PT_MAXBINS) ++shift;
+    const uint32_t nbins = (uint32_t)(((ncodes - 1) >> shift) + 1);
+    if (ensure_tilesums(c, PT_MAXBINS)) return -1;          // reused as the bins' record cursors
+    uint32_t *gcursor = c->d_tilesums;
+    ProfScope ps(c, KC_SCATTER, 4);
+    k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, fbwords,
+                                                              c->d_stats, c->d_lcp);
+    k_partition_init<<<grid_for(nbins, 256), 256, 0, c->stream>>>(c->d_lb, mincode, shift, nbins, (uint32_t)partoffset, gcursor);
+    k_partition<BITS><<<grid_for((c->n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, c->n, mincode, maxcode, shift, nbins,
+                                                                             gcursor, c->d_suf64);
+    const size_t smem = ((size_t)4 << shift);
+    if (smem <= 160 * 1024) {
+      if (smem > 48 * 1024)
+        CK(cudaFuncSetAttribute(k_scatter_bins, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      k_scatter_bins<<<nbins, 1024, smem, c->stream>>>(c->d_suf64, gcursor, c->d_lb, c->d_cursor, c->d_sa, mincode, maxcode,
+                                                       shift, (uint32_t)partoffset);
+    } else {
+      k_partition_gaps<<<grid_for((uint64_t)nbins * 32, 256), 256, 0, c->stream>>>(gcursor, c->d_lb, mincode, maxcode, shift,
+                                                                                  nbins, (uint32_t)partoffset, c->d_suf64);
+      k_scatter_records<<<grid_for(width, 256), 256, 0, c->stream>>>(c->d_suf64, width, c->d_cursor, c->d_sa,
+                                                                     (uint32_t)partoffset);
+    }
   }
   if (c->npadded) {
     ProfScope ps(c, KC_PADDED);

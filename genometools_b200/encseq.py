@@ -80,28 +80,35 @@ def encode_fasta(path: str, alphabet: str = "dna") -> np.ndarray:
 def special_ranges(enc: np.ndarray) -> np.ndarray:
     """Maximal runs of special symbols as half-open [start, end) pairs, ascending: what
     gt_specialrangeiterator_next yields in forward direction."""
-    sp = enc >= WILDCARD
-    if not sp.any():
+    pos = np.flatnonzero(enc >= WILDCARD)
+    if pos.size == 0:
         return np.zeros((0, 2), dtype=np.uint64)
-    d = np.diff(sp.astype(np.int8), prepend=0, append=0)
-    starts = np.flatnonzero(d == 1)
-    ends = np.flatnonzero(d == -1)
+    brk = np.flatnonzero(np.diff(pos) != 1)
+    starts = np.concatenate([pos[:1], pos[brk + 1]])
+    ends = np.concatenate([pos[brk], pos[-1:]]) + 1
     return np.stack([starts, ends], axis=1).astype(np.uint64)
 
 
-def twobit_pack(enc: np.ndarray) -> np.ndarray:
+def twobit_pack(enc: np.ndarray, chunk: int = 1 << 26) -> np.ndarray:
     """GtTwobitencoding words of a DNA sequence (src/core/encseq.c:73-81).  Special positions get
     the 2-bit filler 0; like in the reference they must never be interpreted without the
     special-range table.  One spare word is appended, as gt_unitsoftwobitencoding does
-    (src/core/intbits.h:194-205)."""
+    (src/core/intbits.h:194-205).  Works in chunks so that a 3.1 Gbp genome needs no large temporaries."""
     n = int(enc.shape[0])
     nwords = (n + 31) // 32 + 1
-    codes = np.where(enc >= WILDCARD, 0, enc).astype(np.uint64)
-    padded = np.zeros(nwords * 32, dtype=np.uint64)
-    padded[:n] = codes
-    padded = padded.reshape(nwords, 32)
-    shifts = (62 - 2 * np.arange(32, dtype=np.uint64)).astype(np.uint64)
-    return np.bitwise_or.reduce(padded << shifts, axis=1).astype(np.uint64)
+    out = np.zeros(nwords, dtype=np.uint64)
+    for lo in range(0, n, chunk):          # chunk is a multiple of 32
+        hi = min(n, lo + chunk)
+        c = enc[lo:hi]
+        c = np.where(c >= WILDCARD, 0, c).astype(np.uint8)
+        pad = (-c.shape[0]) % 32
+        if pad:
+            c = np.concatenate([c, np.zeros(pad, dtype=np.uint8)])
+        q = c.reshape(-1, 4)
+        by = (q[:, 0] << 6) | (q[:, 1] << 4) | (q[:, 2] << 2) | q[:, 3]     # 4 bases per byte, first base on top
+        words = by.view(">u8").astype(np.uint64)                             # 8 bytes big-endian = 32 bases
+        out[lo // 32: lo // 32 + words.shape[0]] = words
+    return out
 
 
 def write_fasta(path: str, seqs: list[bytes], width: int = 80) -> None:

@@ -77,6 +77,20 @@ def test_against_oracle(case, parts):
     _compare(got, want, f"{case}/parts{parts}")
 
 
+@pytest.mark.parametrize("parts", [1, 3])
+def test_twolevel_insertion_forced(parts, monkeypatch):
+    """The partition-then-scatter insertion used for parts larger than L2, forced on a small input."""
+    monkeypatch.setenv("GTB200_TWOLEVEL_BYTES", "0")
+    enc = synth.multi_dna_with_nruns(400_000, nseq=7, seed=31)
+    want = oracle.build(enc, 4, 7)
+    got = sfx.suffixerator(enc, "dna", parts=parts, prefixlength=7)
+    _compare(got, want, f"twolevel/parts{parts}")
+    prot = synth.random_protein(400, seed=32)
+    want = oracle.build(prot, 20, 3)
+    got = sfx.suffixerator(prot, "protein", parts=parts, prefixlength=3)
+    _compare(got, want, f"twolevel-protein/parts{parts}")
+
+
 def test_config2_ecoli_size_full_parity():
     """BASELINE.json configs[1]: 4.6 Mbp random DNA, single sequence, seed 42, pl = 8."""
     enc = synth.random_dna(4_600_000, seed=42)
