@@ -42,9 +42,12 @@ WORKLOADS = {
 }
 
 
+SHRINK = 1   # --shrink D: exploratory runs on 1/D of the named size (the line says so in config)
+
+
 def make_workload(name: str, scale: int):
     per_gpu, _ = WORKLOADS[name]
-    total = per_gpu * scale
+    total = per_gpu * scale // SHRINK
     if name == "ecoli":
         return synth.random_dna(total, seed=42), "dna"
     if name == "chr1":
@@ -192,7 +195,12 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=None)
     ap.add_argument("--skip-e2e", action="store_true", help="exploratory runs only: leaves e2e out of the line")
+    ap.add_argument("--shrink", type=int, default=1, help="exploratory: run on 1/D of the named workload size")
     args = ap.parse_args()
+    global SHRINK
+    SHRINK = max(1, args.shrink)
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"        # keep stdout to the one JSON line
     if args.impl == "reference":
         bench_reference(args)
         return
@@ -388,7 +396,8 @@ def main():
             "metric": "suffixes/sec for SA+LCP", "value": value, "unit": "suffixes/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u32 positions / u64 keys", "data": "synthetic",
-            "config": {"workload": WORKLOADS[args.workload][1] + (f" x{world} (genome grows with N)" if world > 1 else ""),
+            "config": {"workload": WORKLOADS[args.workload][1] + (f" x{world} (genome grows with N)" if world > 1 else "")
+                       + (f" SHRUNK 1/{SHRINK}" if SHRINK > 1 else ""),
                        "totallength": n, "prefixlength": it.prefixlength, "suffixes": n + 1,
                        "sharding": f"{world} bucket ranges (-parts split), text broadcast over NCCL",
                        "l2": "flushed (256 MiB write) before every timed step",

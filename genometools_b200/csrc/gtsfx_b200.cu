@@ -72,6 +72,8 @@ struct PartStats {          // lives in device memory, mirrored to pinned host m
   unsigned int fb_buckets;
   unsigned int largest;
   unsigned int bmax;             // bucket-boundary part of maxdepth
+  unsigned int med_count;        // buckets queued for the block-level sorter
+  unsigned int pad_;
 };
 
 struct ProfEvent { int cls; cudaEvent_t a, b; };
@@ -105,6 +107,7 @@ struct gtb200_ctx {
   uint32_t *d_sa;
   uint8_t *d_lcp;
   uint64_t *d_suf64;
+  uint32_t *d_medlist;       // codes of buckets handed to the block-level sorter
   uint32_t *d_fbbits;
   uint64_t cap_fbwords;
   gtb200_largelcp *d_llv;    // sorted records of the last part
@@ -965,7 +968,8 @@ template <int BITS>
 __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out, const uint32_t *__restrict__ lb,
                                                       const uint32_t *__restrict__ cursor, uint64_t mincode,
                                                       uint64_t maxcode, unsigned pl, uint32_t *__restrict__ fbbits,
-                                                      uint32_t maxbucket) {
+                                                      uint32_t maxbucket, uint32_t *__restrict__ medlist,
+                                                      uint32_t medmax) {
   __shared__ uint64_t s_key[SORT_WARPS][SORT_MAXBUCKET];
   __shared__ uint32_t s_pos[SORT_WARPS][SORT_MAXBUCKET];
   const int lane = threadIdx.x & 31;
@@ -981,8 +985,13 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
     if (cnt <= 1) continue;
     const uint32_t start = b0 - out.partoffset;
     bool ok = false;
-    if (cnt > maxbucket) ok = false;
-    else if (cnt <= 32) ok = warp_sort_any<BITS, 1>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
+    if (cnt > maxbucket) {
+      if (cnt <= medmax) {                 // too large for one warp: queue for k_sort_medium
+        if (lane == 0) medlist[atomicAdd(&out.stats->med_count, 1u)] = (uint32_t)c;
+        continue;
+      }
+      ok = false;
+    } else if (cnt <= 32) ok = warp_sort_any<BITS, 1>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
     else if (cnt <= 64) ok = warp_sort_any<BITS, 2>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
     else if (cnt <= 128) ok = warp_sort_any<BITS, 4>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
     else if (cnt <= SORT_MAXBUCKET) ok = warp_sort_any<BITS, 8>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
@@ -1004,8 +1013,87 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
   }
 }
 
+// Buckets of 257..MED_MAX suffixes: one block per bucket, (key,pos) pairs in shared memory, bitonic
+// network with __syncthreads between steps; LCP and tie detection as in the warp sorter.
+#define MED_MAX 4096
+template <int BITS>
+__global__ void __launch_bounds__(256) k_sort_medium(Text<BITS> T, PartOut out, const uint32_t *__restrict__ lb,
+                                                     const uint32_t *__restrict__ cursor,
+                                                     const uint32_t *__restrict__ medlist, uint64_t mincode,
+                                                     unsigned pl, uint32_t *__restrict__ fbbits) {
+  extern __shared__ __align__(16) unsigned char sm_raw[];
+  uint64_t *skey = (uint64_t *)sm_raw;
+  uint32_t *spos = (uint32_t *)(skey + MED_MAX);
+  __shared__ int s_tie;
+  const uint32_t nmed = out.stats->med_count;
+  unsigned long long sum = 0;
+  uint32_t mx = 0;
+  for (uint32_t b = blockIdx.x; b < nmed; b += gridDim.x) {
+    const uint32_t c = medlist[b];
+    const uint32_t b0 = lb[c], cnt = cursor[c] - b0, start = b0 - out.partoffset;
+    uint32_t P = 512;
+    while (P < cnt) P <<= 1;
+    for (uint32_t i = threadIdx.x; i < P; i += 256) {
+      if (i < cnt) {
+        const uint32_t p = out.sa[start + i];
+        skey[i] = make_key<BITS>(T, (uint64_t)p + pl);
+        spos[i] = p;
+      } else {
+        skey[i] = ~0ull;
+        spos[i] = 0xffffffffu;
+      }
+    }
+    if (threadIdx.x == 0) s_tie = 0;
+    __syncthreads();
+    for (uint32_t size = 2; size <= P; size <<= 1) {
+      for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+        for (uint32_t i = threadIdx.x; i < P / 2; i += 256) {
+          const uint32_t lo = 2 * i - (i & (stride - 1)), hi = lo + stride;
+          const bool asc = ((lo & size) == 0);
+          const uint64_t ka = skey[lo], kb = skey[hi];
+          const uint32_t pa = spos[lo], pb = spos[hi];
+          const bool gt = ka > kb || (ka == kb && pa > pb);
+          if (gt == asc) { skey[lo] = kb; skey[hi] = ka; spos[lo] = pb; spos[hi] = pa; }
+        }
+        __syncthreads();
+      }
+    }
+    for (uint32_t i = threadIdx.x + 1; i < cnt; i += 256)
+      if (skey[i - 1] == skey[i] && (skey[i] & 0xff) == 0) s_tie = 1;
+    __syncthreads();
+    if (s_tie) {
+      if (threadIdx.x == 0) {
+        const uint64_t rel = c - mincode;
+        atomicOr(&fbbits[rel >> 5], 1u << (rel & 31));
+        atomicAdd(&out.stats->fb_elems, (unsigned long long)cnt);
+        atomicAdd(&out.stats->fb_buckets, 1u);
+      }
+    } else {
+      for (uint32_t i = threadIdx.x; i < cnt; i += 256) {
+        out.sa[start + i] = spos[i];
+        if (i >= 1) {
+          const uint32_t l = pl + key_common<BITS>(skey[i - 1], skey[i]);
+          out.lcp[start + i] = (uint8_t)l;
+          sum += l;
+          mx = max(mx, l);
+        }
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sum += __shfl_xor_sync(GTB_FULL, sum, o);
+    mx = max(mx, __shfl_xor_sync(GTB_FULL, mx, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (sum) atomicAdd(&out.stats->lcpsum, sum);
+    if (mx) atomicMax(&out.stats->maxdepth, mx);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
-// refinement path (buckets > SORT_MAXBUCKET or still tied after pl+W symbols)
+// refinement path (buckets > MED_MAX or still tied after pl+W symbols)
 // ---------------------------------------------------------------------------------------------
 __global__ void k_fb_popc(const uint32_t *__restrict__ fbbits, uint64_t nwords, uint32_t *cnt) {
   const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1595,10 +1683,12 @@ static int ensure_part_buffers(gtb200_ctx *c, uint64_t width, uint64_t ncodes_in
     dfree(c, c->d_sa);
     dfree(c, c->d_lcp);
     dfree(c, c->d_suf64);
+    dfree(c, c->d_medlist);
     c->d_sa = nullptr; c->d_lcp = nullptr; c->d_suf64 = nullptr; c->cap_width = 0;
     CK(dmalloc(c, &c->d_sa, (width + 1) * 4));
     CK(dmalloc(c, &c->d_lcp, width + 1));
     CK(dmalloc(c, &c->d_suf64, (width + 1) * 8));
+    CK(dmalloc(c, &c->d_medlist, (width / (SORT_MAXBUCKET + 1) + 2) * 4));
     c->cap_width = width;
   }
   const uint64_t fbwords = (ncodes_in_part + 31) / 32 + 1;
@@ -1814,8 +1904,17 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
   {
     ProfScope ps(c, KC_SORT);
     uint64_t warps = ncodes < 148ull * 64 ? ncodes : 148ull * 64;   // 8 blocks of 8 warps per SM
+    const uint32_t medmax = c->sort_maxbucket == SORT_MAXBUCKET ? MED_MAX : 0;   // testing knob disables both
     k_sort_buckets<BITS><<<grid_for(warps * 32, 256), 256, 0, c->stream>>>(T, out, c->d_lb, c->d_cursor, mincode, maxcode,
-                                                                          c->cp.pl, c->d_fbbits, c->sort_maxbucket);
+                                                                          c->cp.pl, c->d_fbbits, c->sort_maxbucket,
+                                                                          c->d_medlist, medmax);
+  }
+  if (c->sort_maxbucket == SORT_MAXBUCKET && width > SORT_MAXBUCKET) {
+    ProfScope ps(c, KC_SORT);
+    const size_t smem = (size_t)MED_MAX * 12;
+    CK(cudaFuncSetAttribute(k_sort_medium<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_sort_medium<BITS><<<148 * 4, 256, smem, c->stream>>>(T, out, c->d_lb, c->d_cursor, c->d_medlist, mincode, c->cp.pl,
+                                                          c->d_fbbits);
   }
   // Bucket borders and the 64-bit image are launched right away: in the common case (no bucket
   // needs refinement) the part is finished with a single host round trip.  If refinement was

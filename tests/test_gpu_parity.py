@@ -148,6 +148,50 @@ def test_config3_shape_scaled_properties_and_parts():
         assert one[k] == eight[k]
 
 
+def test_device_resident_input_matches_host_input():
+    """GTB200_MEM_DEVICE descriptors (what a rank holds after the NCCL broadcast): same bytes out."""
+    import torch
+    enc = synth.multi_dna_with_nruns(200_000, nseq=4, seed=41)
+    want = oracle.build(enc, 4)
+    tw = torch.from_numpy(encseq.twobit_pack(enc).view(np.int64)).cuda()
+    rg = torch.from_numpy(encseq.special_ranges(enc).view(np.int64).reshape(-1)).cuda()
+    it = sfx.Sfxiterator(4, enc.shape[0], None, 2, twobit=tw.data_ptr(), ranges=rg.data_ptr(), numofwords=tw.numel(),
+                         numofranges=rg.numel() // 2, device_ptrs=True)
+    sufs, lcps = [], []
+    while True:
+        r = it.next()
+        if r is None:
+            break
+        sufs.append(r[0])
+        lcps.append(r[1] if r[1] is not None else np.zeros(r[0].shape[0], dtype=np.uint8))
+    it.delete()
+    assert np.concatenate(sufs).tobytes() == want["suf"]
+    assert np.concatenate(lcps).tobytes() == want["lcp"]
+    # byte-encoded protein resident on the device
+    prot = synth.random_protein(300, seed=42)
+    wantp = oracle.build(prot, 20, 3)
+    pe = torch.from_numpy(prot).cuda()
+    it = sfx.Sfxiterator(20, prot.shape[0], 3, 1, enc=pe.data_ptr(), device_ptrs=True)
+    suf, lcp, llv, _ = it.next()
+    tail = it.next()[0]
+    it.delete()
+    assert np.concatenate([suf, tail]).tobytes() == wantp["suf"]
+
+
+def test_medium_buckets_block_sorter():
+    """Buckets of 257..4096 suffixes take the block-level sorter (k_sort_medium), not the refinement path."""
+    rng = np.random.default_rng(43)
+    enc = rng.integers(0, 4, size=600_000, dtype=np.uint8)
+    want = oracle.build(enc, 4, 4)            # 256 buckets of ~2300 suffixes
+    got = sfx.suffixerator(enc, "dna", prefixlength=4)
+    _compare(got, want, "medium/dna")
+    assert got["fallback_suffixes"] == 0
+    prot = synth.random_protein(1500, seed=44)
+    want = oracle.build(prot, 20, 2)          # 400 buckets of ~1200 residues
+    got = sfx.suffixerator(prot, "protein", prefixlength=2, parts=2)
+    _compare(got, want, "medium/protein")
+
+
 def test_suftabuint_and_tail_paging():
     enc = synth.multi_dna_with_nruns(100_000, nseq=5, seed=21)
     want = oracle.build(enc, 4)
