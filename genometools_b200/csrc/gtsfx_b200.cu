@@ -890,7 +890,7 @@ struct WarpSorter32 {
   }
 };
 
-#define SORT_MAXBUCKET 256
+#define SORT_MAXBUCKET 128   // warp path: 4 elements per lane keep the kernel at 64 registers (32 warps/SM)
 #define SORT_WARPS 8
 
 // Fast path: order the bucket by the 12 bases that follow the prefix (one 32-bit compare per
@@ -979,9 +979,12 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
   const uint64_t nw = ((uint64_t)gridDim.x * blockDim.x) >> 5;
   unsigned long long sum = 0;
   uint32_t mx = 0;
+  uint32_t nb0 = 0, ncur = 0;
+  if (mincode + gw <= maxcode) { nb0 = lb[mincode + gw]; ncur = cursor[mincode + gw]; }
   for (uint64_t c = mincode + gw; c <= maxcode; c += nw) {
-    const uint32_t b0 = lb[c];
-    const uint32_t cnt = cursor[c] - b0;
+    const uint32_t b0 = nb0;
+    const uint32_t cnt = ncur - b0;
+    if (c + nw <= maxcode) { nb0 = lb[c + nw]; ncur = cursor[c + nw]; }   // bounds of the next bucket, in flight early
     if (cnt <= 1) continue;
     const uint32_t start = b0 - out.partoffset;
     bool ok = false;
@@ -994,7 +997,6 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
     } else if (cnt <= 32) ok = warp_sort_any<BITS, 1>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
     else if (cnt <= 64) ok = warp_sort_any<BITS, 2>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
     else if (cnt <= 128) ok = warp_sort_any<BITS, 4>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
-    else if (cnt <= SORT_MAXBUCKET) ok = warp_sort_any<BITS, 8>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
     if (!ok && lane == 0) {
       const uint64_t rel = c - mincode;
       atomicOr(&fbbits[rel >> 5], 1u << (rel & 31));
@@ -1031,7 +1033,7 @@ __global__ void __launch_bounds__(256) k_sort_medium(Text<BITS> T, PartOut out, 
   for (uint32_t b = blockIdx.x; b < nmed; b += gridDim.x) {
     const uint32_t c = medlist[b];
     const uint32_t b0 = lb[c], cnt = cursor[c] - b0, start = b0 - out.partoffset;
-    uint32_t P = 512;
+    uint32_t P = 256;
     while (P < cnt) P <<= 1;
     for (uint32_t i = threadIdx.x; i < P; i += 256) {
       if (i < cnt) {
