@@ -66,6 +66,19 @@ __device__ __forceinline__ uint64_t make_key(const Text<BITS> &T, uint64_t q) {
   return (x << 8) | (uint64_t)(W - avail);
 }
 
+// same key when the number of real symbols ahead of q is already known (no bitmap access)
+template <int BITS>
+__device__ __forceinline__ uint64_t make_key_known(const Text<BITS> &T, uint64_t q, unsigned avail) {
+  constexpr int W = Text<BITS>::W;
+  if (avail > (unsigned)W) avail = W;
+  uint64_t x = T.window(q) >> 8;
+  if (avail < (unsigned)W) {
+    const unsigned padbits = (W - avail) * BITS;
+    x |= (~0ull) >> (64 - padbits);
+  }
+  return (x << 8) | (uint64_t)(W - avail);
+}
+
 // lcp contribution of two keys taken at the same depth: number of equal leading real symbols
 template <int BITS>
 __device__ __forceinline__ unsigned key_common(uint64_t ka, uint64_t kb) {

@@ -73,7 +73,7 @@ struct PartStats {          // lives in device memory, mirrored to pinned host m
   unsigned int largest;
   unsigned int bmax;             // bucket-boundary part of maxdepth
   unsigned int med_count;        // buckets queued for the block-level sorter
-  unsigned int pad_;
+  unsigned int tile_leftover;    // buckets the tile sorter handed to the global sorters
 };
 
 struct ProfEvent { int cls; cudaEvent_t a, b; };
@@ -102,6 +102,12 @@ struct gtb200_ctx {
   bool counted;
   uint32_t sort_maxbucket;   // buckets above this size take the refinement path (testing knob)
   uint64_t twolevel_bytes;   // parts whose 4-byte suffix array exceeds this use the two-level insertion
+  bool l2_window;            // persisting-L2 window set on the stream
+  int tile_mode;             // 0 off, 1 automatic, 2 forced (GTB200_TILE, testing knob)
+  int tile_levels;           // 0 automatic, 1/2 forced (GTB200_TILE_LEVELS, testing knob)
+  uint64_t *d_recB;          // second record buffer of the tile path (two partition levels)
+  uint32_t *d_bins;          // bin cursors / starts / chunk table of the tile path
+  uint64_t cap_recB, cap_bins;
   // per part
   uint64_t cap_width;
   uint32_t *d_sa;
@@ -812,16 +818,18 @@ struct WarpSorter {
 // Sorts one bucket of cnt <= 32*E regular suffixes held by one warp and writes order + in-bucket
 // LCP.  Returns false (nothing written) if two suffixes agree on all pl+W symbols.
 template <int BITS, int E>
-__device__ __forceinline__ bool warp_sort_bucket(const Text<BITS> &T, const PartOut &out, uint32_t start, uint32_t cnt,
-                                                 unsigned pl, int lane, unsigned long long &sum, uint32_t &mx) {
+__device__ __forceinline__ bool warp_sort_bucket(const Text<BITS> &T, const PartOut &out, const uint32_t *src,
+                                                 const uint8_t *srcL, uint32_t start, uint32_t cnt, unsigned pl, int lane,
+                                                 unsigned long long &sum, uint32_t &mx) {
   uint64_t k[E];
   uint32_t v[E];
 #pragma unroll
   for (int e = 0; e < E; ++e) {
     const uint32_t i = e * 32 + lane;
     if (i < cnt) {
-      v[e] = out.sa[start + i];
-      k[e] = make_key<BITS>(T, (uint64_t)v[e] + pl);
+      v[e] = src[i];
+      k[e] = srcL ? make_key_known<BITS>(T, (uint64_t)v[e] + pl, (unsigned)srcL[i] - pl)
+                  : make_key<BITS>(T, (uint64_t)v[e] + pl);
     } else {
       v[e] = 0xffffffffu;
       k[e] = ~0ull;
@@ -847,9 +855,9 @@ __device__ __forceinline__ bool warp_sort_bucket(const Text<BITS> &T, const Part
   for (int e = 0; e < E; ++e) {
     const uint32_t i = e * 32 + lane;
     if (i < cnt) {
-      out.sa[start + i] = v[e];
+      __stcs(out.sa + start + i, v[e]);
       if (i >= 1) {
-        out.lcp[start + i] = (uint8_t)l[e];
+        __stcs(out.lcp + start + i, (uint8_t)l[e]);
         sum += l[e];
         mx = max(mx, l[e]);
       }
@@ -899,9 +907,9 @@ struct WarpSorter32 {
 // whose rest is out of order, ties, cut-off suffixes) sends the bucket to the exact 64-bit sorter.
 // Returns 0 = done, 1 = redo with warp_sort_bucket.
 template <int BITS, int E>
-__device__ __forceinline__ int warp_sort_bucket32(const Text<BITS> &T, const PartOut &out, uint32_t start, uint32_t cnt,
-                                                  unsigned pl, int lane, uint64_t *skey, uint32_t *spos,
-                                                  unsigned long long &sum, uint32_t &mx) {
+__device__ __forceinline__ int warp_sort_bucket32(const Text<BITS> &T, const PartOut &out, const uint32_t *src,
+                                                  const uint8_t *srcL, uint32_t start, uint32_t cnt, unsigned pl, int lane,
+                                                  uint64_t *skey, uint32_t *spos, unsigned long long &sum, uint32_t &mx) {
   uint32_t k[E];
   __syncwarp();
 #pragma unroll
@@ -909,8 +917,9 @@ __device__ __forceinline__ int warp_sort_bucket32(const Text<BITS> &T, const Par
     const uint32_t i = e * 32 + lane;
     k[e] = 0xffffffffu;
     if (i < cnt) {
-      const uint32_t p = out.sa[start + i];
-      const uint64_t fk = make_key<BITS>(T, (uint64_t)p + pl);
+      const uint32_t p = src[i];
+      const uint64_t fk = srcL ? make_key_known<BITS>(T, (uint64_t)p + pl, (unsigned)srcL[i] - pl)
+                               : make_key<BITS>(T, (uint64_t)p + pl);
       skey[i] = fk;
       spos[i] = p;
       k[e] = ((uint32_t)(fk >> 40) << 8) | i;
@@ -943,9 +952,9 @@ __device__ __forceinline__ int warp_sort_bucket32(const Text<BITS> &T, const Par
   for (int e = 0; e < E; ++e) {
     const uint32_t i = e * 32 + lane;
     if (i < cnt) {
-      out.sa[start + i] = spos[k[e] & 0xff];
+      __stcs(out.sa + start + i, spos[k[e] & 0xff]);
       if (i >= 1) {
-        out.lcp[start + i] = (uint8_t)l[e];
+        __stcs(out.lcp + start + i, (uint8_t)l[e]);
         sum += l[e];
         mx = max(mx, l[e]);
       }
@@ -955,13 +964,13 @@ __device__ __forceinline__ int warp_sort_bucket32(const Text<BITS> &T, const Par
 }
 
 template <int BITS, int E>
-__device__ __forceinline__ bool warp_sort_any(const Text<BITS> &T, const PartOut &out, uint32_t start, uint32_t cnt,
-                                              unsigned pl, int lane, uint64_t *skey, uint32_t *spos,
-                                              unsigned long long &sum, uint32_t &mx) {
+__device__ __forceinline__ bool warp_sort_any(const Text<BITS> &T, const PartOut &out, const uint32_t *src,
+                                              const uint8_t *srcL, uint32_t start, uint32_t cnt, unsigned pl, int lane,
+                                              uint64_t *skey, uint32_t *spos, unsigned long long &sum, uint32_t &mx) {
   if (BITS == 2) {
-    if (warp_sort_bucket32<BITS, E>(T, out, start, cnt, pl, lane, skey, spos, sum, mx) == 0) return true;
+    if (warp_sort_bucket32<BITS, E>(T, out, src, srcL, start, cnt, pl, lane, skey, spos, sum, mx) == 0) return true;
   }
-  return warp_sort_bucket<BITS, E>(T, out, start, cnt, pl, lane, sum, mx);
+  return warp_sort_bucket<BITS, E>(T, out, src, srcL, start, cnt, pl, lane, sum, mx);
 }
 
 template <int BITS>
@@ -969,7 +978,8 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
                                                       const uint32_t *__restrict__ cursor, uint64_t mincode,
                                                       uint64_t maxcode, unsigned pl, uint32_t *__restrict__ fbbits,
                                                       uint32_t maxbucket, uint32_t *__restrict__ medlist,
-                                                      uint32_t medmax) {
+                                                      uint32_t medmax, int only_leftovers) {
+  if (only_leftovers && out.stats->tile_leftover == 0) return;   // the tile sorter finished every bucket
   __shared__ uint64_t s_key[SORT_WARPS][SORT_MAXBUCKET];
   __shared__ uint32_t s_pos[SORT_WARPS][SORT_MAXBUCKET];
   const int lane = threadIdx.x & 31;
@@ -994,9 +1004,9 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
         continue;
       }
       ok = false;
-    } else if (cnt <= 32) ok = warp_sort_any<BITS, 1>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
-    else if (cnt <= 64) ok = warp_sort_any<BITS, 2>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
-    else if (cnt <= 128) ok = warp_sort_any<BITS, 4>(T, out, start, cnt, pl, lane, skey, spos, sum, mx);
+    } else if (cnt <= 32) ok = warp_sort_any<BITS, 1>(T, out, out.sa + start, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
+    else if (cnt <= 64) ok = warp_sort_any<BITS, 2>(T, out, out.sa + start, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
+    else if (cnt <= 128) ok = warp_sort_any<BITS, 4>(T, out, out.sa + start, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
     if (!ok && lane == 0) {
       const uint64_t rel = c - mincode;
       atomicOr(&fbbits[rel >> 5], 1u << (rel & 31));
@@ -1014,6 +1024,8 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
     if (mx) atomicMax(&out.stats->maxdepth, mx);
   }
 }
+
+#include "tiles.cuh"
 
 // Buckets of 257..MED_MAX suffixes: one block per bucket, (key,pos) pairs in shared memory, bitonic
 // network with __syncthreads between steps; LCP and tie detection as in the warp sorter.
@@ -1397,6 +1409,7 @@ static void free_ctx(gtb200_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
+  if (c->l2_window) cudaCtxResetPersistingL2Cache();
   {
     std::lock_guard<std::mutex> lock(g_pool_mu);
     for (auto &b : c->blocks) g_pool[c->device].push_back(b);
@@ -1435,8 +1448,34 @@ static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
   const uint64_t nchunks = (n >> 6) + 1;
   c->nmaskwords = nchunks + 2;
   c->ntextwords = nchunks * (64 / spw) + 2;
-  CK(dmalloc(c, &c->d_text, c->ntextwords * 8));
-  CK(dmalloc(c, &c->d_mask, c->nmaskwords * 8));
+  CK(dmalloc(c, &c->d_text, (c->ntextwords + c->nmaskwords) * 8));   // one block: text, then the bitmap
+  c->d_mask = c->d_text + c->ntextwords;
+  {
+    // Keep the packed sequence + bitmap in L2 while suffix-array sized streams pass through: the
+    // sort kernels gather 16+16 bytes per suffix from it at random.  Persisting-L2 set-aside and an
+    // access-policy window on this context's stream; scaled down if the sequence is larger.
+    int maxpersist = 0, maxwin = 0;
+    cudaDeviceGetAttribute(&maxpersist, cudaDevAttrMaxPersistingL2CacheSize, c->device);
+    cudaDeviceGetAttribute(&maxwin, cudaDevAttrMaxAccessPolicyWindowSize, c->device);
+    const size_t bytes = (c->ntextwords + c->nmaskwords) * 8;
+    const char *off = getenv("GTB200_L2_PERSIST");
+    // Opt-in (GTB200_L2_PERSIST=1): measured on B200 the set-aside speeds the tile sorter up by ~20 % at
+    // 250 Mbp but starves every other kernel of L2, a net loss; the default keeps L2 unpartitioned.
+    if (maxpersist > 0 && maxwin > 0 && bytes >= (8u << 20) && off && atoi(off) == 1) {
+      const size_t setaside = bytes < (size_t)maxpersist ? bytes : (size_t)maxpersist;
+      if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, setaside) == cudaSuccess) {
+        cudaStreamAttrValue av;
+        memset(&av, 0, sizeof av);
+        av.accessPolicyWindow.base_ptr = c->d_text;
+        av.accessPolicyWindow.num_bytes = bytes < (size_t)maxwin ? bytes : (size_t)maxwin;
+        av.accessPolicyWindow.hitRatio = bytes <= setaside ? 1.0f : (float)((double)setaside / (double)bytes);
+        av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        if (cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &av) == cudaSuccess) c->l2_window = true;
+      }
+      (void)cudaGetLastError();
+    }
+  }
   CK(dmalloc(c, &c->d_stats, sizeof(PartStats)));
   {
     std::lock_guard<std::mutex> lock(g_pool_mu);
@@ -1444,8 +1483,7 @@ static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
   }
   if (!c->h_stats) CK(cudaMallocHost(&c->h_stats, 256));
   CK(cudaMemsetAsync(c->d_stats, 0, sizeof(PartStats), c->stream));
-  CK(cudaMemsetAsync(c->d_text, 0, c->ntextwords * 8, c->stream));
-  CK(cudaMemsetAsync(c->d_mask, 0, c->nmaskwords * 8, c->stream));
+  CK(cudaMemsetAsync(c->d_text, 0, (c->ntextwords + c->nmaskwords) * 8, c->stream));
   if (seq->twobitencoding) {
     uint64_t nw = (n + 31) / 32;
     if (seq->numofwords < nw) return set_error("twobitencoding has %llu words, %llu needed",
@@ -1571,6 +1609,9 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
     const long v = atol(e2);
     if (v >= 0 && v < SORT_MAXBUCKET) c->sort_maxbucket = (uint32_t)v;
   }
+  c->tile_mode = 1;
+  if (const char *e4 = getenv("GTB200_TILE")) c->tile_mode = atoi(e4);
+  if (const char *e5 = getenv("GTB200_TILE_LEVELS")) c->tile_levels = atoi(e5);
   c->twolevel_bytes = 48ull << 20;
   if (const char *e3 = getenv("GTB200_TWOLEVEL_BYTES")) c->twolevel_bytes = strtoull(e3, nullptr, 10);   // testing knob
   if (open_impl(c, seq)) { free_ctx(c); return -1; }
@@ -1866,8 +1907,80 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
   out.llv = nullptr;
   out.stats = c->d_stats;
   out.partoffset = (uint32_t)partoffset;
-  const bool twolevel = width * 4 > c->twolevel_bytes && ncodes >= 4096;
-  if (!twolevel) {
+  // ---- tile path (DNA): staged partition into shared-memory sized bins, then sort inside the tile ----
+  bool tile = BITS == 2 && c->tile_mode != 0 && ncodes >= 2 && (c->tile_mode == 2 || (width >= (1u << 24) && ncodes >= 1024));
+  int shiftF = 0, shift1 = 0;
+  uint32_t nbinsF = 0, nb1 = 0;
+  if (tile) {
+    if (width / ncodes > 4096) tile = false;                      // buckets alone exceed a tile
+    while (tile && shiftF < 10 && (((uint64_t)width << (shiftF + 1)) / ncodes) <= 4608 && (ncodes >> (shiftF + 1)) >= 1) ++shiftF;
+    const uint64_t nf = ((ncodes - 1) >> shiftF) + 1;
+    bool two = nf > SP_MAXBINS;
+    if (c->tile_levels == 2 && nf >= 4) two = true;
+    if (c->tile_levels == 1 && nf <= SP_MAXBINS) two = false;
+    if (nf > (1ull << 20)) tile = false;
+    nbinsF = (uint32_t)nf;
+    if (tile && two) {
+      int lg = 0;
+      while ((1ull << lg) < nf) ++lg;
+      shift1 = shiftF + (lg + 1) / 2;
+      while ((((ncodes - 1) >> shift1) + 1) > SP_MAXBINS) ++shift1;
+      if (shift1 - shiftF > 10) tile = false;
+      nb1 = (uint32_t)(((ncodes - 1) >> shift1) + 1);
+    }
+  }
+  if (tile) {
+    const uint64_t binwords = (uint64_t)nbinsF + 3 * SP_MAXBINS + 64;
+    if (binwords > c->cap_bins) {
+      dfree(c, c->d_bins);
+      CK(dmalloc(c, &c->d_bins, binwords * 4));
+      c->cap_bins = binwords;
+    }
+    if (nb1 && width > c->cap_recB) {
+      dfree(c, c->d_recB);
+      CK(dmalloc(c, &c->d_recB, (width + 1) * 8));
+      c->cap_recB = width;
+    }
+    uint32_t *gcurF = c->d_bins, *gcur1 = gcurF + nbinsF, *start1 = gcur1 + SP_MAXBINS, *blkfirst = start1 + SP_MAXBINS;
+    CK(cudaFuncSetAttribute(k_stage_partition<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SP_SMEM));
+    CK(cudaFuncSetAttribute(k_stage_partition<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SP_SMEM));
+    const unsigned textblocks = grid_for(c->n, SP_CHUNK);
+    // records carry min(real length, 63) in their top 6 bits when the code leaves room for it
+    const int recL = (c->numcodes <= (1ull << 26) && c->cp.pl + Text<BITS>::W <= 63) ? 1 : 0;
+    {
+      ProfScope ps(c, KC_SCATTER, nb1 ? 6 : 3);
+      k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, fbwords,
+                                                                c->d_stats, c->d_lcp);
+      k_bins_init<<<grid_for(nbinsF, 256), 256, 0, c->stream>>>(c->d_lb, mincode, shiftF, nbinsF, (uint32_t)partoffset, gcurF,
+                                                                nullptr);
+      if (!nb1) {
+        k_stage_partition<BITS, true><<<textblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, mincode, maxcode, shiftF, nbinsF,
+                                                                               nullptr, nullptr, nullptr, nullptr, 0, 0, gcurF,
+                                                                               c->d_suf64, recL);
+      } else {
+        k_bins_init<<<grid_for(nb1, 256), 256, 0, c->stream>>>(c->d_lb, mincode, shift1, nb1, (uint32_t)partoffset, gcur1, start1);
+        k_stage_partition<BITS, true><<<textblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, mincode, maxcode, shift1, nb1,
+                                                                               nullptr, nullptr, nullptr, nullptr, 0, 0, gcur1,
+                                                                               c->d_recB, recL);
+        k_chunk_table<<<1, 256, 0, c->stream>>>(start1, gcur1, nb1, blkfirst);
+        const unsigned recblocks = (unsigned)(width / SP_CHUNK + nb1 + 1);
+        k_stage_partition<BITS, false><<<recblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, mincode, maxcode, shiftF,
+                                                                               1u << (shift1 - shiftF), c->d_recB, start1, gcur1,
+                                                                               blkfirst, nb1, shift1, gcurF, c->d_suf64, recL);
+      }
+    }
+    {
+      ProfScope ps(c, KC_SORT);
+      const unsigned tb = nbinsF < 148u * 5 ? nbinsF : 148u * 5;
+      k_tile_sort<BITS><<<tb, 256, 0, c->stream>>>(T, out, c->d_lb, c->d_cursor, c->d_suf64, gcurF, mincode, maxcode, shiftF,
+                                                   nbinsF, c->cp.pl, recL);
+    }
+    CK(cudaGetLastError());
+  }
+  const bool twolevel = !tile && width * 4 > c->twolevel_bytes && ncodes >= 4096;
+  if (tile) {
+    // insertion already done
+  } else if (!twolevel) {
     ProfScope ps(c, KC_SCATTER, 2);
     k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, fbwords,
                                                               c->d_stats, c->d_lcp);
@@ -1909,7 +2022,7 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
     const uint32_t medmax = c->sort_maxbucket == SORT_MAXBUCKET ? MED_MAX : 0;   // testing knob disables both
     k_sort_buckets<BITS><<<grid_for(warps * 32, 256), 256, 0, c->stream>>>(T, out, c->d_lb, c->d_cursor, mincode, maxcode,
                                                                           c->cp.pl, c->d_fbbits, c->sort_maxbucket,
-                                                                          c->d_medlist, medmax);
+                                                                          c->d_medlist, medmax, tile ? 1 : 0);
   }
   if (c->sort_maxbucket == SORT_MAXBUCKET && width > SORT_MAXBUCKET) {
     ProfScope ps(c, KC_SORT);

@@ -91,6 +91,29 @@ def test_twolevel_insertion_forced(parts, monkeypatch):
     _compare(got, want, f"twolevel-protein/parts{parts}")
 
 
+TILE_CASES = {
+    "nruns": lambda: (synth.multi_dna_with_nruns(500_000, nseq=7, seed=51), None),
+    "nruns_pl5": lambda: (synth.multi_dna_with_nruns(300_000, nseq=3, seed=52), 5),
+    "skewed": lambda: (np.random.default_rng(53).choice(4, size=400_000, p=[0.75, 0.1, 0.1, 0.05]).astype(np.uint8), 7),
+    "repeats": lambda: (synth.repeat_rich_dna(unit=5000, copies=10, seed=54), None),
+    "polyT_mixed": lambda: (np.concatenate([np.full(20_000, 3, dtype=np.uint8), synth.random_dna(100_000, seed=55)]), 6),
+}
+
+
+@pytest.mark.parametrize("levels", ["1", "2"])
+@pytest.mark.parametrize("parts", [1, 3])
+@pytest.mark.parametrize("case", sorted(TILE_CASES))
+def test_tile_path_forced(case, parts, levels, monkeypatch):
+    """The staged-partition + shared-memory tile sorter, forced on small inputs (one and two partition
+    levels), including buckets it must hand over to the global sorters and the refinement path."""
+    monkeypatch.setenv("GTB200_TILE", "2")
+    monkeypatch.setenv("GTB200_TILE_LEVELS", levels)
+    enc, pl = TILE_CASES[case]()
+    want = oracle.build(enc, 4, pl)
+    got = sfx.suffixerator(enc, "dna", parts=parts, prefixlength=want["prefixlength"])
+    _compare(got, want, f"tile/{case}/parts{parts}/levels{levels}")
+
+
 def test_config2_ecoli_size_full_parity():
     """BASELINE.json configs[1]: 4.6 Mbp random DNA, single sequence, seed 42, pl = 8."""
     enc = synth.random_dna(4_600_000, seed=42)
