@@ -470,6 +470,8 @@ __global__ void __launch_bounds__(256) k_kmers(Text<BITS> T, CodeParams cp, uint
       const uint64_t code = prefix_value<BITS>(win, pl, cp);
       if (MODE == 0) {
         atomicAdd(&table[code], 1u);
+      } else if (MODE == 2) {
+        if (code >= mincode && code <= maxcode) atomicAdd(&table[code], 1u);
       } else if (code >= mincode && code <= maxcode) {
         const uint32_t slot = atomicAdd(&table[code], 1u);
         sa[slot - partoffset] = (uint32_t)(p0 + i);
@@ -481,6 +483,8 @@ __global__ void __launch_bounds__(256) k_kmers(Text<BITS> T, CodeParams cp, uint
       const uint64_t code = prefix_value<BITS>(T.window(p0 + i), pl, cp);
       if (MODE == 0) {
         atomicAdd(&table[code], 1u);
+      } else if (MODE == 2) {
+        if (code >= mincode && code <= maxcode) atomicAdd(&table[code], 1u);
       } else if (code >= mincode && code <= maxcode) {
         const uint32_t slot = atomicAdd(&table[code], 1u);
         sa[slot - partoffset] = (uint32_t)(p0 + i);
@@ -1640,8 +1644,19 @@ static int count_impl(gtb200_ctx *c) {
   CK(cudaMemsetAsync(c->d_lb, 0, tablewords * 4, c->stream));
   CK(cudaMemsetAsync(c->d_stats, 0, sizeof(PartStats), c->stream));
   if (n) {
-    ProfScope ps(c, KC_COUNT);
-    k_kmers<BITS, 0><<<grid_for((n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, n, c->d_lb, nullptr, 0, 0, 0);
+    // A table larger than L2 is filled slice by slice (64 MB of counters per pass over the text), so
+    // that the RED.ADDs always hit L2-resident lines; the text scan itself is cheap (n/4 bytes).
+    const uint64_t slice = 1ull << 24;
+    if (c->numcodes * 4 <= (96ull << 20)) {
+      ProfScope ps(c, KC_COUNT);
+      k_kmers<BITS, 0><<<grid_for((n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, n, c->d_lb, nullptr, 0, 0, 0);
+    } else {
+      for (uint64_t lo = 0; lo < c->numcodes; lo += slice) {
+        const uint64_t hi = lo + slice - 1 < c->numcodes - 1 ? lo + slice - 1 : c->numcodes - 1;
+        ProfScope ps(c, KC_COUNT);
+        k_kmers<BITS, 2><<<grid_for((n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, n, c->d_lb, nullptr, lo, hi, 0);
+      }
+    }
   }
   // special-padded suffixes
   if (small) {

@@ -115,13 +115,23 @@ __global__ void __launch_bounds__(256) k_stage_partition(Text<BITS> T, CodeParam
     rcnt = send - rbeg < SP_CHUNK ? send - rbeg : SP_CHUNK;
     binbase = (uint64_t)parent << (parent_shift - shift);
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      const uint32_t j = i * 256 + threadIdx.x;
-      if (j < rcnt) {
-        const uint64_t r = rec_in[rbeg + j];
-        const uint32_t bin = (uint32_t)(((rec_code(r, recL) - mincode) >> shift) - binbase);
-        const uint32_t q = atomicAdd(&h[bin], 1u);
-        rk[i >> 1] |= q << ((i & 1) * 16);
+    for (int g8 = 0; g8 < 4; ++g8) {           // eight loads in flight per thread, not thirty-two
+      uint64_t r8[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const uint32_t j = (g8 * 8 + k) * 256 + threadIdx.x;
+        r8[k] = j < rcnt ? rec_in[rbeg + j] : 0;
+      }
+      asm volatile("" ::: "memory");
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int i = g8 * 8 + k;
+        const uint32_t j = i * 256 + threadIdx.x;
+        if (j < rcnt) {
+          const uint32_t bin = (uint32_t)(((rec_code(r8[k], recL) - mincode) >> shift) - binbase);
+          const uint32_t q = atomicAdd(&h[bin], 1u);
+          rk[i >> 1] |= q << ((i & 1) * 16);
+        }
       }
     }
   }
@@ -160,13 +170,23 @@ __global__ void __launch_bounds__(256) k_stage_partition(Text<BITS> T, CodeParam
     }
   } else {
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      const uint32_t j = i * 256 + threadIdx.x;
-      if (j < rcnt) {
-        const uint64_t r = rec_in[rbeg + j];
-        const uint32_t bin = (uint32_t)(((rec_code(r, recL) - mincode) >> shift) - binbase);
-        const uint32_t q = (rk[i >> 1] >> ((i & 1) * 16)) & 0xffffu;
-        stage[lstart[bin] + q] = r;
+    for (int g8 = 0; g8 < 4; ++g8) {
+      uint64_t r8[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const uint32_t j = (g8 * 8 + k) * 256 + threadIdx.x;
+        r8[k] = j < rcnt ? __ldcs(rec_in + rbeg + j) : 0;   // second and last read of the chunk (L2 hit)
+      }
+      asm volatile("" ::: "memory");
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int i = g8 * 8 + k;
+        const uint32_t j = i * 256 + threadIdx.x;
+        if (j < rcnt) {
+          const uint32_t bin = (uint32_t)(((rec_code(r8[k], recL) - mincode) >> shift) - binbase);
+          const uint32_t q = (rk[i >> 1] >> ((i & 1) * 16)) & 0xffffu;
+          stage[lstart[bin] + q] = r8[k];
+        }
       }
     }
   }
