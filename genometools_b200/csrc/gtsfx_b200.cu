@@ -95,6 +95,7 @@ struct gtb200_ctx {
   uint32_t *d_cursor;        // [numcodes]
   uint32_t *d_csc, *d_dist;
   uint64_t padcap, npadded;
+  unsigned long long *d_persist;   // [0] number of special-padded suffixes, [1] largest bucket, [2] sum of counts
   uint64_t *d_padkey;        // (code << 6) | (pl - reallen), sorted
   uint32_t *d_padpos;
   uint32_t *d_padcnt;
@@ -755,10 +756,11 @@ __device__ __forceinline__ void emit_large(const PartOut &o, uint32_t r, uint32_
 // padded list is sorted by (code, pl-L) with ascending positions inside equal keys: entry i of
 // code c goes to the right end of bucket c (reference order: src/match/sfx-suffixer.c:476-516)
 __global__ void k_place_padded(const uint64_t *__restrict__ padkey, const uint32_t *__restrict__ padpos,
-                               uint64_t npadded, const uint32_t *__restrict__ lb, const uint32_t *__restrict__ csc,
+                               const unsigned long long *__restrict__ npadded_dev, const uint32_t *__restrict__ lb,
+                               const uint32_t *__restrict__ csc,
                                unsigned sigma, unsigned pl, uint64_t mincode, uint64_t maxcode, PartOut out) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= npadded) return;
+  if (i >= *npadded_dev) return;
   const uint64_t key = padkey[i];
   const uint64_t code = key >> 6;
   if (code < mincode || code > maxcode) return;
@@ -1274,24 +1276,48 @@ __global__ void k_llv_gather(const gtb200_largelcp *__restrict__ src, const uint
 // lcp of the first entry of every non-empty bucket with its left neighbour in the suffix array
 // (src/match/sfx-lcpvalues.c:91-111,591-693 compute the same value from codes and prefix indices)
 template <int BITS>
-__global__ void k_boundary(Text<BITS> T, PartOut out, const uint32_t *__restrict__ lb, uint64_t mincode,
-                           uint64_t maxcode, unsigned pl) {
+__global__ void k_boundary(Text<BITS> T, CodeParams cp, PartOut out, const uint32_t *__restrict__ lb,
+                           const uint32_t *__restrict__ csc, uint64_t mincode, uint64_t maxcode) {
   const uint64_t c = mincode + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned pl = cp.pl;
   unsigned long long sum = 0;
   uint32_t mx = 0;
   if (c <= maxcode) {
-    const uint32_t b0 = lb[c];
+    const uint32_t b0 = lb[c], b1 = lb[c + 1];
     const uint32_t r = b0 - out.partoffset;
-    if (lb[c + 1] != b0 && r != 0) {          // non-empty and not the first entry of the part (k_part_first)
-      const uint32_t a = out.sa[r - 1], b = out.sa[r];
-      const unsigned la = T.reallen(a), lbn = T.reallen(b);
-      const uint64_t x = T.window(a) ^ T.window(b);
-      const unsigned common = x ? (unsigned)__clzll((long long)x) / BITS : 64u / BITS;
-      unsigned l = common < la ? common : la;
-      l = l < lbn ? l : lbn;
-      if (l > pl) l = pl;                     // cannot happen for different buckets; defensive
+    if (b1 != b0 && r != 0) {                 // non-empty and not the first entry of the part (k_part_first)
+      uint64_t cprev = c - 1;                 // previous non-empty bucket; exists inside the part because r > 0
+      while (lb[cprev] == b0) --cprev;
+      const uint32_t padc = (c % cp.sigma == cp.sigma - 1) ? csc[(c - (cp.sigma - 1)) / cp.sigma] : 0u;
+      const uint32_t padp = (cprev % cp.sigma == cp.sigma - 1) ? csc[(cprev - (cp.sigma - 1)) / cp.sigma] : 0u;
+      unsigned l;
+      bool regular;
+      if (padp == 0 && b1 - b0 > padc) {
+        // both neighbours have >= pl real symbols: the value is the common prefix of the two codes
+        regular = true;
+        if (cp.pow2) {
+          const uint64_t x = cprev ^ c;
+          l = pl - 1 - (unsigned)(63 - __clzll((long long)x)) / BITS;
+        } else {
+          l = 0;
+          for (unsigned i = 0; i < pl; ++i) {
+            if ((cprev / cp.pw[pl - 1 - i]) % cp.sigma != (c / cp.pw[pl - 1 - i]) % cp.sigma) break;
+            ++l;
+          }
+        }
+      } else {
+        // a special-padded suffix is involved: compare the two suffixes themselves
+        const uint32_t a = out.sa[r - 1], b = out.sa[r];
+        const unsigned la = T.reallen(a), lbn = T.reallen(b);
+        const uint64_t x = T.window(a) ^ T.window(b);
+        const unsigned common = x ? (unsigned)__clzll((long long)x) / BITS : 64u / BITS;
+        l = common < la ? common : la;
+        l = l < lbn ? l : lbn;
+        if (l > pl) l = pl;
+        regular = lbn >= pl;
+      }
       out.lcp[r] = (uint8_t)l;
-      if (lbn >= pl) sum = l;                 // special-padded entries do not enter lcptabsum
+      if (regular) sum = l;                   // special-padded entries do not enter lcptabsum
       mx = l;
     }
   }
@@ -1311,7 +1337,8 @@ __global__ void k_boundary(Text<BITS> T, PartOut out, const uint32_t *__restrict
 template <int BITS>
 __global__ void k_part_first(Text<BITS> T, CodeParams cp, PartOut out, const uint32_t *__restrict__ lb,
                              uint64_t numcodes, const uint32_t *__restrict__ csc,
-                             const uint64_t *__restrict__ padkey, uint64_t npadded) {
+                             const uint64_t *__restrict__ padkey, const unsigned long long *__restrict__ npadded_dev) {
+  const uint64_t npadded = *npadded_dev;
   if (blockIdx.x || threadIdx.x) return;
   const uint32_t po = out.partoffset;
   // cprev = max{x : lb[x] < po}; ccur = max{x : lb[x] <= po, x < numcodes}
@@ -1624,7 +1651,7 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
 }
 
 template <int BITS>
-static int count_impl(gtb200_ctx *c) {
+static int count_impl(gtb200_ctx *c, bool need_host_values) {
   const Text<BITS> T = text_of<BITS>(c);
   const uint64_t n = c->n;
   const uint64_t nr1 = c->nranges + 1;
@@ -1638,7 +1665,9 @@ static int count_impl(gtb200_ctx *c) {
     CK(dmalloc(c, &c->d_padcnt, (nr1 + 1) * 4));
     CK(dmalloc(c, &c->d_padkey, c->padcap * 8));
     CK(dmalloc(c, &c->d_padpos, c->padcap * 4));
+    CK(dmalloc(c, &c->d_persist, 64));
   }
+  CK(cudaMemsetAsync(c->d_persist, 0, 64, c->stream));
   const bool small = nr1 <= PADSMALL_CAP && c->padcap <= PADSMALL_CAP;
   uint32_t *cntoff = c->d_padcnt;
   CK(cudaMemsetAsync(c->d_lb, 0, tablewords * 4, c->stream));
@@ -1662,14 +1691,14 @@ static int count_impl(gtb200_ctx *c) {
   if (small) {
     ProfScope ps(c, KC_PADDED);
     k_padded_small<BITS><<<1, 256, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, c->d_lb, c->d_csc, c->d_dist,
-                                                   c->d_padkey, c->d_padpos, &c->d_stats->scan_total);
+                                                   c->d_padkey, c->d_padpos, c->d_persist);
   } else {
     {
       ProfScope ps(c, KC_PADDED);
       k_padded<BITS, 0><<<grid_for(nr1, 128), 128, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, cntoff, nullptr,
                                                                    nullptr, nullptr, nullptr, nullptr);
     }
-    if (device_scan(c, cntoff, cntoff, nr1, 0, &c->d_stats->scan_total, KC_PADDED)) return -1;
+    if (device_scan(c, cntoff, cntoff, nr1, 0, c->d_persist, KC_PADDED)) return -1;
     {
       ProfScope ps(c, KC_PADDED);
       k_padded<BITS, 1><<<grid_for(nr1, 128), 128, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, cntoff, c->d_lb,
@@ -1678,15 +1707,21 @@ static int count_impl(gtb200_ctx *c) {
   }
   {
     ProfScope ps(c, KC_COUNT);
-    k_max_u32<<<592, 256, 0, c->stream>>>(c->d_lb, c->numcodes, &c->d_stats->largest);
+    k_max_u32<<<592, 256, 0, c->stream>>>(c->d_lb, c->numcodes, (unsigned int *)(c->d_persist + 1));
   }
-  if (device_scan(c, c->d_lb, c->d_lb, c->numcodes, 1, &c->d_stats->scan_total2)) return -1;
-  if (sync_stats(c)) return -1;
-  c->npadded = c->h_stats->scan_total;
-  c->largestbucket = c->h_stats->largest;
-  if (c->h_stats->scan_total2 != c->nsort)
-    return set_error("internal: bucket counts sum to %llu, expected %llu", c->h_stats->scan_total2,
-                     (unsigned long long)c->nsort);
+  if (device_scan(c, c->d_lb, c->d_lb, c->numcodes, 1, c->d_persist + 2)) return -1;
+  c->counted = true;
+  if (small && !need_host_values) {           // nothing the host needs: stay asynchronous
+    CK(cudaGetLastError());
+    return 0;
+  }
+  unsigned long long *hp = (unsigned long long *)((char *)c->h_stats + 128);
+  CK(cudaMemcpyAsync(hp, c->d_persist, 24, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  c->npadded = hp[0];
+  c->largestbucket = (uint32_t)hp[1];
+  if (hp[2] != c->nsort)
+    return set_error("internal: bucket counts sum to %llu, expected %llu", hp[2], (unsigned long long)c->nsort);
   // large lists: sort by (code, pl-L); stable, so positions stay ascending
   if (!small && c->npadded > 1) {
     const uint32_t np = (uint32_t)c->npadded;
@@ -1716,7 +1751,8 @@ extern "C" int gtb200_count(gtb200_ctx *c, uint32_t *leftborder, uint32_t *count
   if (!c) return set_error("gtb200_count: null context");
   CK(cudaSetDevice(c->device));
   {                                           // recomputed on every call (the tables are reused)
-    const int rc = c->bits == 2 ? count_impl<2>(c) : count_impl<8>(c);
+    const bool need = leftborder || countspecialcodes || distpfxidx || info;
+    const int rc = c->bits == 2 ? count_impl<2>(c, need) : count_impl<8>(c, need);
     if (rc) return rc;
   }
   if (leftborder) CK(cudaMemcpyAsync(leftborder, c->d_lb, (c->numcodes + 1) * 4, cudaMemcpyDeviceToHost, c->stream));
@@ -1724,7 +1760,7 @@ extern "C" int gtb200_count(gtb200_ctx *c, uint32_t *leftborder, uint32_t *count
     CK(cudaMemcpyAsync(countspecialcodes, c->d_csc, c->numspecialcodes * 4, cudaMemcpyDeviceToHost, c->stream));
   if (distpfxidx && c->numdist)
     CK(cudaMemcpyAsync(distpfxidx, c->d_dist, c->numdist * 4, cudaMemcpyDeviceToHost, c->stream));
-  CK(cudaStreamSynchronize(c->stream));
+  if (leftborder || countspecialcodes || distpfxidx || info) CK(cudaStreamSynchronize(c->stream));
   if (info) {
     info->numofallcodes = c->numcodes;
     info->numofspecialcodes = c->numspecialcodes;
@@ -2026,9 +2062,9 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
                                                                      (uint32_t)partoffset);
     }
   }
-  if (c->npadded) {
+  if (c->padcap > 1) {
     ProfScope ps(c, KC_PADDED);
-    k_place_padded<<<grid_for(c->npadded, 256), 256, 0, c->stream>>>(c->d_padkey, c->d_padpos, c->npadded, c->d_lb,
+    k_place_padded<<<grid_for(c->padcap, 256), 256, 0, c->stream>>>(c->d_padkey, c->d_padpos, c->d_persist, c->d_lb,
                                                                      c->d_csc, c->cp.sigma, c->cp.pl, mincode, maxcode, out);
   }
   {
@@ -2052,9 +2088,9 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
   for (int pass = 0; pass < 2; ++pass) {
     {
       ProfScope ps(c, KC_BOUNDARY, partoffset > 0 ? 2 : 1);
-      k_boundary<BITS><<<grid_for(ncodes, 256), 256, 0, c->stream>>>(T, out, c->d_lb, mincode, maxcode, c->cp.pl);
+      k_boundary<BITS><<<grid_for(ncodes, 256), 256, 0, c->stream>>>(T, c->cp, out, c->d_lb, c->d_csc, mincode, maxcode);
       if (partoffset > 0)
-        k_part_first<BITS><<<1, 32, 0, c->stream>>>(T, c->cp, out, c->d_lb, c->numcodes, c->d_csc, c->d_padkey, c->npadded);
+        k_part_first<BITS><<<1, 32, 0, c->stream>>>(T, c->cp, out, c->d_lb, c->numcodes, c->d_csc, c->d_padkey, c->d_persist);
     }
     {
       ProfScope ps(c, KC_WIDEN);
