@@ -376,12 +376,23 @@ def main():
         bits = 2 if alphabet == "dna" else 8
         text_bytes = n * bits / 8 + n / 8                       # packed text + special bitmap, read once
         m = width
+        ncodes_part = maxcode - mincode + 1
+        tile = alphabet == "dna" and m >= (1 << 24) and ncodes_part >= 1024    # the library's own rule
+        levels = 1
+        if tile:                                    # same arithmetic as sort_part_impl
+            sh = 0
+            while sh < 10 and ((m << (sh + 1)) // ncodes_part) <= 4608 and (ncodes_part >> (sh + 1)) >= 1:
+                sh += 1
+            levels = 2 if ((ncodes_part - 1) >> sh) + 1 > 1024 else 1
         algo = {   # algorithmic bytes per step and kernel class (DESIGN.md "Kernels")
             "count": text_bytes + 4 * numcodes,
             "scan": 8 * numcodes,
-            "scatter": text_bytes + 4 * m,
-            "sort_lcp": (4 + 8 + 4 + 1) * m,                    # pos in, 8-byte text window, pos out, lcp out
-            "boundary": 8 * (maxcode - mincode + 1),
+            # direct: text read + one 4-byte store; tile path: text read + 8-byte records written once per level
+            # and re-read once between levels
+            "scatter": text_bytes + (4 * m if not tile else 8 * m + (levels - 1) * 16 * m),
+            # direct: pos in, 8-byte text window, pos out, lcp out; tile path reads an 8-byte record instead of pos
+            "sort_lcp": ((4 if not tile else 8) + 8 + 4 + 1) * m,
+            "boundary": 8 * ncodes_part,
             "widen": 12 * m,
         }
         kern = {k: v for k, v in prof.items() if v[1] > 0}
@@ -401,7 +412,9 @@ def main():
                        "totallength": n, "prefixlength": it.prefixlength, "suffixes": n + 1,
                        "sharding": f"{world} bucket ranges (-parts split), text broadcast over NCCL",
                        "l2": "flushed (256 MiB write) before every timed step",
-                       "fallback_suffixes": int(pinfo.fallback_suffixes)},
+                       "fallback_suffixes": int(pinfo.fallback_suffixes),
+                       "insertion": ("tile path: staged partition x%d + shared-memory tile sort" % levels) if tile
+                                    else "direct scatter + warp bucket sort"},
             "e2e": {"value": (n + 1) / e2e_s, "unit": "suffixes/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "steps": e2e_steps},
             "gpu_launches": int(sum(v[1] for v in kern.values())),

@@ -452,45 +452,47 @@ __global__ void k_range_lengths(const gtb200_range *__restrict__ ranges, uint64_
 // One thread per 32 consecutive positions.  Counts suffixes whose first pl symbols are all real.
 // MODE 0: histogram (hist[code]++).  MODE 1: scatter (sa[cursor[code]++ - partoffset] = pos) for
 // codes in [mincode,maxcode].
+#define KM_PPT 8     // positions per thread: four threads share one 32-base word (the loads hit L1), which gives
+                     // small genomes enough threads to cover the latency of the returning atomics
 template <int BITS, int MODE>
 __global__ void __launch_bounds__(256) k_kmers(Text<BITS> T, CodeParams cp, uint64_t n, uint32_t *__restrict__ table,
                                                 uint32_t *__restrict__ sa, uint64_t mincode, uint64_t maxcode,
                                                 uint32_t partoffset) {
   const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const uint64_t p0 = t << 5;
+  const uint64_t p0 = t * KM_PPT;
   if (p0 >= n) return;
   const unsigned pl = cp.pl;
   const uint64_t mw = T.maskwin(p0);
   const uint64_t plmask = (pl >= 64) ? ~0ull : ((1ull << pl) - 1ull);
-  if (BITS == 2) {
-    const uint64_t hi = __ldg(T.w + t), lo = __ldg(T.w + t + 1);
-#pragma unroll 8
-    for (int i = 0; i < 32; ++i) {
-      if (((mw >> i) & plmask) != 0) continue;
-      const uint64_t win = i ? (hi << (2 * i)) | (lo >> (64 - 2 * i)) : hi;
+  uint64_t hi = 0, lo = 0;
+  const int i0 = (int)(p0 & 31);
+  if (BITS == 2) { hi = __ldg(T.w + (p0 >> 5)); lo = __ldg(T.w + (p0 >> 5) + 1); }
+  uint32_t slot[KM_PPT];
+  bool ok[KM_PPT];
+#pragma unroll
+  for (int k = 0; k < KM_PPT; ++k) {
+    ok[k] = ((mw >> k) & plmask) == 0;
+    slot[k] = 0;
+    if (ok[k]) {
+      uint64_t win;
+      const int i = i0 + k;
+      if (BITS == 2) win = i ? (hi << (2 * i)) | (lo >> (64 - 2 * i)) : hi;
+      else win = T.window(p0 + k);
       const uint64_t code = prefix_value<BITS>(win, pl, cp);
       if (MODE == 0) {
         atomicAdd(&table[code], 1u);
       } else if (MODE == 2) {
         if (code >= mincode && code <= maxcode) atomicAdd(&table[code], 1u);
-      } else if (code >= mincode && code <= maxcode) {
-        const uint32_t slot = atomicAdd(&table[code], 1u);
-        sa[slot - partoffset] = (uint32_t)(p0 + i);
-      }
+      } else {
+        ok[k] = code >= mincode && code <= maxcode;
+        if (ok[k]) slot[k] = atomicAdd(&table[code], 1u);      // all atomics of the thread are issued before
+      }                                                        // the first dependent store below
     }
-  } else {
-    for (int i = 0; i < 32; ++i) {
-      if (((mw >> i) & plmask) != 0) continue;
-      const uint64_t code = prefix_value<BITS>(T.window(p0 + i), pl, cp);
-      if (MODE == 0) {
-        atomicAdd(&table[code], 1u);
-      } else if (MODE == 2) {
-        if (code >= mincode && code <= maxcode) atomicAdd(&table[code], 1u);
-      } else if (code >= mincode && code <= maxcode) {
-        const uint32_t slot = atomicAdd(&table[code], 1u);
-        sa[slot - partoffset] = (uint32_t)(p0 + i);
-      }
-    }
+  }
+  if (MODE == 1) {
+#pragma unroll
+    for (int k = 0; k < KM_PPT; ++k)
+      if (ok[k]) sa[slot[k] - partoffset] = (uint32_t)(p0 + k);
   }
 }
 
@@ -1678,12 +1680,12 @@ static int count_impl(gtb200_ctx *c, bool need_host_values) {
     const uint64_t slice = 1ull << 24;
     if (c->numcodes * 4 <= (96ull << 20)) {
       ProfScope ps(c, KC_COUNT);
-      k_kmers<BITS, 0><<<grid_for((n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, n, c->d_lb, nullptr, 0, 0, 0);
+      k_kmers<BITS, 0><<<grid_for((n + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, n, c->d_lb, nullptr, 0, 0, 0);
     } else {
       for (uint64_t lo = 0; lo < c->numcodes; lo += slice) {
         const uint64_t hi = lo + slice - 1 < c->numcodes - 1 ? lo + slice - 1 : c->numcodes - 1;
         ProfScope ps(c, KC_COUNT);
-        k_kmers<BITS, 2><<<grid_for((n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, n, c->d_lb, nullptr, lo, hi, 0);
+        k_kmers<BITS, 2><<<grid_for((n + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, n, c->d_lb, nullptr, lo, hi, 0);
       }
     }
   }
@@ -2035,7 +2037,7 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
     ProfScope ps(c, KC_SCATTER, 2);
     k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, fbwords,
                                                               c->d_stats, c->d_lcp);
-    k_kmers<BITS, 1><<<grid_for((c->n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, c->n, c->d_cursor, c->d_sa, mincode,
+    k_kmers<BITS, 1><<<grid_for((c->n + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, c->n, c->d_cursor, c->d_sa, mincode,
                                                                             maxcode, (uint32_t)partoffset);
   } else {
     int shift = 0;
