@@ -39,6 +39,7 @@ WORKLOADS = {
     "chr1": (250_000_000, "configs[2]: synthetic 250 Mbp DNA, 24 sequences, N-runs (seed 250)"),
     "human": (3_100_000_000, "configs[3]: synthetic 3.1 Gbp multi-FASTA DNA (seed 31)"),
     "protein": (1_000_000_000, "configs[4]: synthetic 1 G-residue protein set (seed 5)"),
+    "genomelike": (50_000_000, "stress (not in BASELINE.json): 50 Mbp with repeat families, segmental duplications, N-runs"),
 }
 
 
@@ -54,6 +55,8 @@ def make_workload(name: str, scale: int):
         return synth.multi_dna_with_nruns(total, nseq=24, seed=250), "dna"
     if name == "human":
         return synth.multi_dna_with_nruns(total, nseq=24, seed=31), "dna"
+    if name == "genomelike":
+        return synth.genome_like_dna(total, seed=77), "dna"
     return synth.random_protein(max(1, total // 334), seed=5), "protein"
 
 

@@ -84,3 +84,41 @@ def repeat_rich_dna(unit: int = 700, copies: int = 6, seed: int = 7, mutate: flo
     pieces.append(np.full(600, 3, dtype=np.uint8))          # poly-T
     pieces.append(np.tile(np.array([0, 1], dtype=np.uint8), 400))  # (AC)n
     return np.concatenate(pieces)
+
+
+def genome_like_dna(total: int, seed: int = 77, repeat_fraction: float = 0.35, nseq: int = 6) -> np.ndarray:
+    """Stress case closer to a real genome than i.i.d. bases: interspersed repeat families (300 bp
+    to 6 kb consensus sequences copied with 0-15 % divergence), a few recent exact segmental
+    duplications (10-50 kb), microsatellites, N-runs and several sequences.  Produces many buckets
+    with ties beyond pl+28 bases and LCP values in the thousands."""
+    rng = np.random.default_rng(seed)
+    out = rng.integers(0, 4, size=total, dtype=np.uint8)
+    fams = [rng.integers(0, 4, size=int(L), dtype=np.uint8) for L in rng.choice([300, 300, 300, 1200, 6000], size=12)]
+    budget = int(total * repeat_fraction)
+    while budget > 0:
+        f = fams[int(rng.integers(0, len(fams)))]
+        div = float(rng.choice([0.0, 0.01, 0.05, 0.15]))
+        c = f.copy()
+        if div > 0:
+            m = rng.random(c.shape[0]) < div
+            c[m] = rng.integers(0, 4, size=int(m.sum()), dtype=np.uint8)
+        a = int(rng.integers(0, max(1, total - c.shape[0])))
+        out[a:a + c.shape[0]] = c[: total - a]
+        budget -= c.shape[0]
+    for _ in range(4):                                   # segmental duplications (exact)
+        L = int(rng.integers(10_000, 50_000))
+        if total > 4 * L:
+            a, b = int(rng.integers(0, total - L)), int(rng.integers(0, total - L))
+            out[b:b + L] = out[a:a + L]
+    for _ in range(max(1, total // 200_000)):            # microsatellites
+        unit = rng.integers(0, 4, size=int(rng.integers(1, 5)), dtype=np.uint8)
+        L = int(rng.integers(40, 400))
+        a = int(rng.integers(0, max(1, total - L)))
+        out[a:a + L] = np.resize(unit, L)[: total - a]
+    for _ in range(max(1, total // 1_000_000)):          # N-runs
+        L = int(rng.integers(1, 5000))
+        a = int(rng.integers(0, max(1, total - L)))
+        out[a:a + L] = WILDCARD
+    cuts = np.sort(rng.choice(np.arange(1, total - 1), size=nseq - 1, replace=False))
+    out[cuts] = SEPARATOR
+    return out
