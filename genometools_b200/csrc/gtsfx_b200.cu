@@ -845,6 +845,7 @@ __device__ __forceinline__ bool warp_sort_bucket(const Text<BITS> &T, const Part
   }
   WarpSorter<E>::sort(k, v, lane);
   uint32_t l[E];
+  bool tp[E];                      // tied with the predecessor on all pl+W symbols: order and lcp still open
   bool tie = false;
 #pragma unroll
   for (int e = 0; e < E; ++e) {
@@ -853,25 +854,28 @@ __device__ __forceinline__ bool warp_sort_bucket(const Text<BITS> &T, const Part
     if (lane == 0) pk = last;
     const uint32_t i = e * 32 + lane;
     l[e] = 0;
+    tp[e] = false;
     if (i >= 1 && i < cnt) {
-      if (pk == k[e] && (k[e] & 0xff) == 0) tie = true;
+      tp[e] = pk == k[e] && (k[e] & 0xff) == 0;
+      tie |= tp[e];
       l[e] = pl + key_common<BITS>(pk, k[e]);
     }
   }
-  if (__any_sync(GTB_FULL, tie)) return false;
 #pragma unroll
   for (int e = 0; e < E; ++e) {
     const uint32_t i = e * 32 + lane;
     if (i < cnt) {
       __stcs(out.sa + start + i, v[e]);
       if (i >= 1) {
-        __stcs(out.lcp + start + i, (uint8_t)l[e]);
-        sum += l[e];
-        mx = max(mx, l[e]);
+        __stcs(out.lcp + start + i, (uint8_t)l[e]);      // provisional for tied pairs, rewritten by refinement
+        if (!tp[e]) {
+          sum += l[e];
+          mx = max(mx, l[e]);
+        }
       }
     }
   }
-  return true;
+  return !__any_sync(GTB_FULL, tie);   // false: sorted on pl+W symbols, tie groups go to the refinement path
 }
 
 // 32-bit variant: keys are (12 leading bases of the window << 8) | slot; min/max network
@@ -986,7 +990,7 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
                                                       const uint32_t *__restrict__ cursor, uint64_t mincode,
                                                       uint64_t maxcode, unsigned pl, uint32_t *__restrict__ fbbits,
                                                       uint32_t maxbucket, uint32_t *__restrict__ medlist,
-                                                      uint32_t medmax, int only_leftovers) {
+                                                      uint32_t medmax, int only_leftovers, uint64_t tieoff) {
   if (only_leftovers && out.stats->tile_leftover == 0) return;   // the tile sorter finished every bucket
   __shared__ uint64_t s_key[SORT_WARPS][SORT_MAXBUCKET];
   __shared__ uint32_t s_pos[SORT_WARPS][SORT_MAXBUCKET];
@@ -1017,7 +1021,9 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
     else if (cnt <= 128) ok = warp_sort_any<BITS, 4>(T, out, out.sa + start, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
     if (!ok && lane == 0) {
       const uint64_t rel = c - mincode;
-      atomicOr(&fbbits[rel >> 5], 1u << (rel & 31));
+      // cnt <= maxbucket: sorted, only its tie groups are refined; otherwise the whole bucket is
+      uint32_t *bits = cnt <= maxbucket ? fbbits + tieoff : fbbits;
+      atomicOr(&bits[rel >> 5], 1u << (rel & 31));
       atomicAdd(&out.stats->fb_elems, (unsigned long long)cnt);
       atomicAdd(&out.stats->fb_buckets, 1u);
     }
@@ -1042,7 +1048,7 @@ template <int BITS>
 __global__ void __launch_bounds__(256) k_sort_medium(Text<BITS> T, PartOut out, const uint32_t *__restrict__ lb,
                                                      const uint32_t *__restrict__ cursor,
                                                      const uint32_t *__restrict__ medlist, uint64_t mincode,
-                                                     unsigned pl, uint32_t *__restrict__ fbbits) {
+                                                     unsigned pl, uint32_t *__restrict__ fbbits, uint64_t tieoff) {
   extern __shared__ __align__(16) unsigned char sm_raw[];
   uint64_t *skey = (uint64_t *)sm_raw;
   uint32_t *spos = (uint32_t *)(skey + MED_MAX);
@@ -1083,19 +1089,18 @@ __global__ void __launch_bounds__(256) k_sort_medium(Text<BITS> T, PartOut out, 
     for (uint32_t i = threadIdx.x + 1; i < cnt; i += 256)
       if (skey[i - 1] == skey[i] && (skey[i] & 0xff) == 0) s_tie = 1;
     __syncthreads();
-    if (s_tie) {
-      if (threadIdx.x == 0) {
-        const uint64_t rel = c - mincode;
-        atomicOr(&fbbits[rel >> 5], 1u << (rel & 31));
-        atomicAdd(&out.stats->fb_elems, (unsigned long long)cnt);
-        atomicAdd(&out.stats->fb_buckets, 1u);
-      }
-    } else {
-      for (uint32_t i = threadIdx.x; i < cnt; i += 256) {
-        out.sa[start + i] = spos[i];
-        if (i >= 1) {
-          const uint32_t l = pl + key_common<BITS>(skey[i - 1], skey[i]);
-          out.lcp[start + i] = (uint8_t)l;
+    if (s_tie && threadIdx.x == 0) {                    // sorted on pl+W symbols; tie groups are refined
+      const uint64_t rel = c - mincode;
+      atomicOr(&fbbits[tieoff + (rel >> 5)], 1u << (rel & 31));
+      atomicAdd(&out.stats->fb_elems, (unsigned long long)cnt);
+      atomicAdd(&out.stats->fb_buckets, 1u);
+    }
+    for (uint32_t i = threadIdx.x; i < cnt; i += 256) {
+      out.sa[start + i] = spos[i];
+      if (i >= 1) {
+        const uint32_t l = pl + key_common<BITS>(skey[i - 1], skey[i]);
+        out.lcp[start + i] = (uint8_t)l;
+        if (!(skey[i - 1] == skey[i] && (skey[i] & 0xff) == 0)) {
           sum += l;
           mx = max(mx, l);
         }
@@ -1117,43 +1122,90 @@ __global__ void __launch_bounds__(256) k_sort_medium(Text<BITS> T, PartOut out, 
 // ---------------------------------------------------------------------------------------------
 // refinement path (buckets > MED_MAX or still tied after pl+W symbols)
 // ---------------------------------------------------------------------------------------------
-__global__ void k_fb_popc(const uint32_t *__restrict__ fbbits, uint64_t nwords, uint32_t *cnt) {
+__global__ void k_fb_popc(const uint32_t *__restrict__ fbbits, const uint32_t *__restrict__ tiebits, uint64_t nwords,
+                          uint32_t *cnt) {
   const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < nwords) cnt[t] = __popc(fbbits[t]);
+  if (t < nwords) cnt[t] = __popc(fbbits[t] | tiebits[t]);
 }
 
-__global__ void k_fb_codes(const uint32_t *__restrict__ fbbits, uint64_t nwords, const uint32_t *__restrict__ off,
-                           uint64_t mincode, const uint32_t *__restrict__ lb, const uint32_t *__restrict__ cursor,
-                           uint32_t *codes, uint32_t *sizes) {
+// flagged buckets in code order; kind 0 = never sorted (whole bucket, depth pl), 1 = sorted, has tie groups
+__global__ void k_fb_codes(const uint32_t *__restrict__ fbbits, const uint32_t *__restrict__ tiebits, uint64_t nwords,
+                           const uint32_t *__restrict__ off, uint64_t mincode, uint32_t *codes, uint32_t *kind) {
   const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= nwords) return;
-  uint32_t bits = fbbits[t];
+  const uint32_t fb = fbbits[t];
+  uint32_t bits = fb | tiebits[t];
   uint32_t o = off[t];
   while (bits) {
     const int b = __ffs(bits) - 1;
     bits &= bits - 1;
-    const uint64_t c = mincode + (t << 5) + b;
-    codes[o] = (uint32_t)c;
-    sizes[o] = cursor[c] - lb[c];
+    codes[o] = (uint32_t)(mincode + (t << 5) + b);
+    kind[o] = (fb >> b) & 1u ? 0u : 1u;
     o++;
   }
 }
 
-// one warp per flagged bucket: list entries in ascending suffix-array index
-__global__ void k_fb_fill(const uint32_t *__restrict__ codes, const uint32_t *__restrict__ eoff, uint32_t nb,
-                          const uint32_t *__restrict__ lb, const uint32_t *__restrict__ cursor, uint32_t partoffset,
-                          unsigned pl, uint32_t *idx, uint32_t *gs, uint32_t *dep) {
+__device__ __forceinline__ uint32_t regular_count(const uint32_t *__restrict__ lb, const uint32_t *__restrict__ csc,
+                                                  uint32_t c, unsigned sigma) {
+  const uint32_t npad = (c % sigma == sigma - 1) ? csc[(c - (sigma - 1)) / sigma] : 0u;
+  return lb[c + 1] - lb[c] - npad;
+}
+
+// One warp per flagged bucket.  FILL = false: sizes[b] = number of list entries the bucket contributes
+// (all regular suffixes of a never-sorted bucket; the members of tie groups of a sorted one).
+// FILL = true: writes the entries (ascending suffix-array index) at eoff[b].
+template <int BITS, bool FILL>
+__global__ void k_fb_list(Text<BITS> T, const uint32_t *__restrict__ sa, const uint32_t *__restrict__ codes,
+                          const uint32_t *__restrict__ kind, uint32_t nb, const uint32_t *__restrict__ lb,
+                          const uint32_t *__restrict__ csc, unsigned sigma, uint32_t partoffset, unsigned pl,
+                          uint32_t *sizes, const uint32_t *__restrict__ eoff, uint32_t *idx, uint32_t *gs, uint32_t *dep) {
+  constexpr int W = Text<BITS>::W;
   const uint64_t gw = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const uint64_t nw = ((uint64_t)gridDim.x * blockDim.x) >> 5;
   const int lane = threadIdx.x & 31;
   for (uint64_t b = gw; b < nb; b += nw) {
     const uint32_t c = codes[b];
-    const uint32_t start = lb[c] - partoffset, cnt = cursor[c] - lb[c], o = eoff[b];
-    for (uint32_t i = lane; i < cnt; i += 32) {
-      idx[o + i] = start + i;
-      gs[o + i] = start;
-      dep[o + i] = pl;
+    const uint32_t start = lb[c] - partoffset, cnt = regular_count(lb, csc, c, sigma);
+    if (kind[b] == 0) {
+      if (!FILL) {
+        if (lane == 0) sizes[b] = cnt;
+      } else {
+        const uint32_t o = eoff[b];
+        for (uint32_t i = lane; i < cnt; i += 32) { idx[o + i] = start + i; gs[o + i] = start; dep[o + i] = pl; }
+      }
+      continue;
     }
+    uint32_t total = 0, carry_head = 0;        // carry_head: run start inherited from the previous 32-chunk
+    for (uint32_t base = 0; base < cnt; base += 32) {
+      const uint32_t i = base + lane;
+      uint64_t kp = 1, kc = 0, kn = 1;
+      if (i < cnt) {
+        kc = make_key<BITS>(T, (uint64_t)sa[start + i] + pl);
+        if (i >= 1) kp = make_key<BITS>(T, (uint64_t)sa[start + i - 1] + pl);
+        if (i + 1 < cnt) kn = make_key<BITS>(T, (uint64_t)sa[start + i + 1] + pl);
+      }
+      const bool open_key = i < cnt && (kc & 0xff) == 0;
+      const bool tp = open_key && i >= 1 && kp == kc;          // tied with predecessor
+      const bool tn = open_key && i + 1 < cnt && kn == kc;     // tied with successor
+      const bool member = tp || tn;
+      const unsigned mm = __ballot_sync(GTB_FULL, member);
+      if (FILL) {
+        // run start = index of the latest member that is not tied with its predecessor
+        const bool hd = member && !tp;
+        const unsigned hm = __ballot_sync(GTB_FULL, hd);
+        const unsigned below = hm & ((2u << lane) - 1u);       // heads at lanes <= mine
+        const uint32_t rs = below ? base + (31 - __clz(below)) : carry_head;
+        if (member) {
+          const uint32_t o = eoff[b] + total + __popc(mm & ((1u << lane) - 1u));
+          idx[o] = start + i;
+          gs[o] = start + rs;
+          dep[o] = pl + W;
+        }
+        if (hm) carry_head = base + (31 - __clz(hm));
+      }
+      total += __popc(mm);
+    }
+    if (!FILL && lane == 0) sizes[b] = total;
   }
 }
 
@@ -1787,7 +1839,7 @@ static int ensure_part_buffers(gtb200_ctx *c, uint64_t width, uint64_t ncodes_in
     CK(dmalloc(c, &c->d_medlist, (width / (SORT_MAXBUCKET + 1) + 2) * 4));
     c->cap_width = width;
   }
-  const uint64_t fbwords = (ncodes_in_part + 31) / 32 + 1;
+  const uint64_t fbwords = 2 * ((ncodes_in_part + 31) / 32) + 2;   // unsorted-bucket bitmap, then tied-bucket bitmap
   if (fbwords > c->cap_fbwords) {
     dfree(c, c->d_fbbits);
     c->d_fbbits = nullptr; c->cap_fbwords = 0;
@@ -1819,6 +1871,7 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   size_t need = 0;
   auto take = [&](size_t bytes) { size_t o = need; need += (bytes + 255) & ~(size_t)255; return o; };
   const size_t o_wcnt = take((fbwords + 1) * 4), o_codes = take(((size_t)nb + 1) * 4), o_sizes = take(((size_t)nb + 1) * 4);
+  const size_t o_kind = take(((size_t)nb + 1) * 4);
   const size_t a4 = ((size_t)A0 + 1) * 4, a8 = ((size_t)A0 + 1) * 8;
   const size_t o_idx0 = take(a4), o_idx1 = take(a4), o_gs0 = take(a4), o_gs1 = take(a4), o_dep0 = take(a4), o_dep1 = take(a4);
   const size_t o_keys = take(a8), o_kA = take(a8), o_kB = take(a8), o_vals = take(a4), o_vA = take(a4), o_vB = take(a4);
@@ -1828,6 +1881,8 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   if (ensure_scratch(c, need)) return -1;
   char *S = (char *)c->d_scratch;
   uint32_t *wcnt = (uint32_t *)(S + o_wcnt), *codes = (uint32_t *)(S + o_codes), *sizes = (uint32_t *)(S + o_sizes);
+  uint32_t *kind = (uint32_t *)(S + o_kind);
+  const uint32_t *tiebits = c->d_fbbits + fbwords;
   uint32_t *idx[2] = {(uint32_t *)(S + o_idx0), (uint32_t *)(S + o_idx1)};
   uint32_t *gs[2] = {(uint32_t *)(S + o_gs0), (uint32_t *)(S + o_gs1)};
   uint32_t *dep[2] = {(uint32_t *)(S + o_dep0), (uint32_t *)(S + o_dep1)};
@@ -1839,25 +1894,31 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   gtb200_largelcp *llvtmp = (gtb200_largelcp *)(S + o_llvtmp);
   out.llv = llvtmp;
 
-  // expand the flagged-bucket bitmap into the ordered element list
+  // expand the two flagged-bucket bitmaps into the ordered element list
   {
     ProfScope ps(c, KC_REFINE, 1);
-    k_fb_popc<<<grid_for(fbwords, 256), 256, 0, c->stream>>>(c->d_fbbits, fbwords, wcnt);
+    k_fb_popc<<<grid_for(fbwords, 256), 256, 0, c->stream>>>(c->d_fbbits, tiebits, fbwords, wcnt);
   }
   if (device_scan(c, wcnt, wcnt, fbwords, 0, nullptr, KC_REFINE)) return -1;
   {
-    ProfScope ps(c, KC_REFINE, 1);
-    k_fb_codes<<<grid_for(fbwords, 256), 256, 0, c->stream>>>(c->d_fbbits, fbwords, wcnt, mincode, c->d_lb, c->d_cursor,
-                                                              codes, sizes);
+    ProfScope ps(c, KC_REFINE, 2);
+    k_fb_codes<<<grid_for(fbwords, 256), 256, 0, c->stream>>>(c->d_fbbits, tiebits, fbwords, wcnt, mincode, codes, kind);
+    k_fb_list<BITS, false><<<grid_for((uint64_t)nb * 32, 256), 256, 0, c->stream>>>(
+        T, out.sa, codes, kind, nb, c->d_lb, c->d_csc, c->cp.sigma, out.partoffset, c->cp.pl, sizes, nullptr, nullptr,
+        nullptr, nullptr);
   }
-  if (device_scan(c, sizes, sizes, nb, 0, nullptr, KC_REFINE)) return -1;
+  if (device_scan(c, sizes, sizes, nb, 0, &c->d_stats->scan_total2, KC_REFINE)) return -1;
   {
     ProfScope ps(c, KC_REFINE, 1);
-    k_fb_fill<<<grid_for((uint64_t)nb * 32, 256), 256, 0, c->stream>>>(codes, sizes, nb, c->d_lb, c->d_cursor,
-                                                                       out.partoffset, c->cp.pl, idx[0], gs[0], dep[0]);
+    k_fb_list<BITS, true><<<grid_for((uint64_t)nb * 32, 256), 256, 0, c->stream>>>(
+        T, out.sa, codes, kind, nb, c->d_lb, c->d_csc, c->cp.sigma, out.partoffset, c->cp.pl, nullptr, sizes, idx[0], gs[0],
+        dep[0]);
   }
   CK(cudaGetLastError());
-  uint32_t A = A0;
+  if (sync_stats(c)) return -1;
+  const uint32_t A1 = (uint32_t)c->h_stats->scan_total2;     // suffixes that really need refinement
+  info->fallback_suffixes = A1;
+  uint32_t A = A1;
   int cur = 0;
   uint64_t rounds = 0;
   const int gsbits = ((bits_for(width) + 7) / 8) * 8;
@@ -2002,7 +2063,7 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
     const int recL = (c->numcodes <= (1ull << 26) && c->cp.pl + Text<BITS>::W <= 63) ? 1 : 0;
     {
       ProfScope ps(c, KC_SCATTER, nb1 ? 6 : 3);
-      k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, fbwords,
+      k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, 2 * fbwords,
                                                                 c->d_stats, c->d_lcp);
       k_bins_init<<<grid_for(nbinsF, 256), 256, 0, c->stream>>>(c->d_lb, mincode, shiftF, nbinsF, (uint32_t)partoffset, gcurF,
                                                                 nullptr);
@@ -2026,7 +2087,7 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
       ProfScope ps(c, KC_SORT);
       const unsigned tb = nbinsF < 148u * 5 ? nbinsF : 148u * 5;
       k_tile_sort<BITS><<<tb, 256, 0, c->stream>>>(T, out, c->d_lb, c->d_cursor, c->d_suf64, gcurF, mincode, maxcode, shiftF,
-                                                   nbinsF, c->cp.pl, recL);
+                                                   nbinsF, c->cp.pl, recL, c->d_fbbits, fbwords);
     }
     CK(cudaGetLastError());
   }
@@ -2035,7 +2096,7 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
     // insertion already done
   } else if (!twolevel) {
     ProfScope ps(c, KC_SCATTER, 2);
-    k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, fbwords,
+    k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, 2 * fbwords,
                                                               c->d_stats, c->d_lcp);
     k_kmers<BITS, 1><<<grid_for((c->n + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, c->n, c->d_cursor, c->d_sa, mincode,
                                                                             maxcode, (uint32_t)partoffset);
@@ -2046,7 +2107,7 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
     if (ensure_tilesums(c, PT_MAXBINS)) return -1;          // reused as the bins' record cursors
     uint32_t *gcursor = c->d_tilesums;
     ProfScope ps(c, KC_SCATTER, 4);
-    k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, fbwords,
+    k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, 2 * fbwords,
                                                               c->d_stats, c->d_lcp);
     k_partition_init<<<grid_for(nbins, 256), 256, 0, c->stream>>>(c->d_lb, mincode, shift, nbins, (uint32_t)partoffset, gcursor);
     k_partition<BITS><<<grid_for((c->n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, c->n, mincode, maxcode, shift, nbins,
@@ -2075,14 +2136,14 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
     const uint32_t medmax = c->sort_maxbucket == SORT_MAXBUCKET ? MED_MAX : 0;   // testing knob disables both
     k_sort_buckets<BITS><<<grid_for(warps * 32, 256), 256, 0, c->stream>>>(T, out, c->d_lb, c->d_cursor, mincode, maxcode,
                                                                           c->cp.pl, c->d_fbbits, c->sort_maxbucket,
-                                                                          c->d_medlist, medmax, tile ? 1 : 0);
+                                                                          c->d_medlist, medmax, tile ? 1 : 0, fbwords);
   }
   if (c->sort_maxbucket == SORT_MAXBUCKET && width > SORT_MAXBUCKET) {
     ProfScope ps(c, KC_SORT);
     const size_t smem = (size_t)MED_MAX * 12;
     CK(cudaFuncSetAttribute(k_sort_medium<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_sort_medium<BITS><<<148 * 4, 256, smem, c->stream>>>(T, out, c->d_lb, c->d_cursor, c->d_medlist, mincode, c->cp.pl,
-                                                          c->d_fbbits);
+                                                          c->d_fbbits, fbwords);
   }
   // Bucket borders and the 64-bit image are launched right away: in the common case (no bucket
   // needs refinement) the part is finished with a single host round trip.  If refinement was

@@ -235,7 +235,8 @@ template <int BITS>
 __global__ void __launch_bounds__(256) k_tile_sort(Text<BITS> T, PartOut out, const uint32_t *__restrict__ lb,
                                                    uint32_t *__restrict__ cursor, const uint64_t *__restrict__ rec,
                                                    const uint32_t *__restrict__ gcursor, uint64_t mincode,
-                                                   uint64_t maxcode, int shift, uint32_t nbins, unsigned pl, int recL) {
+                                                   uint64_t maxcode, int shift, uint32_t nbins, unsigned pl, int recL,
+                                                   uint32_t *__restrict__ fbbits, uint64_t tieoff) {
   __shared__ uint8_t s_len[TILE_CAP];
   __shared__ uint32_t s_lb[TILE_MAXCODES + 1];
   __shared__ uint32_t s_cur[TILE_MAXCODES];
@@ -289,14 +290,20 @@ __global__ void __launch_bounds__(256) k_tile_sort(Text<BITS> T, PartOut out, co
       } else if (cf > 1) {
         uint32_t *src = s_pos + ls;
         const uint8_t *srcL = recL ? s_len + ls : nullptr;
-        bool ok = false;
-        if (cf <= 32) ok = warp_sort_any<BITS, 1>(T, out, src, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
-        else if (cf <= 64) ok = warp_sort_any<BITS, 2>(T, out, src, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
-        else if (cf <= SORT_MAXBUCKET) ok = warp_sort_any<BITS, 4>(T, out, src, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
-        if (!ok) {                                      // leave it to the global sorters
+        bool clean = true;                              // sorted and free of ties
+        if (cf <= 32) clean = warp_sort_any<BITS, 1>(T, out, src, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
+        else if (cf <= 64) clean = warp_sort_any<BITS, 2>(T, out, src, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
+        else if (cf <= SORT_MAXBUCKET) clean = warp_sort_any<BITS, 4>(T, out, src, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
+        else {                                          // too large for a warp: leave it to the global sorters
           for (uint32_t i = lane; i < cf; i += 32) out.sa[start + i] = src[i];
           done = false;
           if (lane == 0) atomicAdd(&out.stats->tile_leftover, 1u);
+        }
+        if (!clean && lane == 0) {                      // sorted on pl+W symbols, tie groups go to refinement
+          const uint64_t rel = c0 + f - mincode;
+          atomicOr(&fbbits[tieoff + (rel >> 5)], 1u << (rel & 31));
+          atomicAdd(&out.stats->fb_elems, (unsigned long long)cf);
+          atomicAdd(&out.stats->fb_buckets, 1u);
         }
       }
       if (lane == 0) cursor[c0 + f] = done ? base + ls : base + ls + cf;
