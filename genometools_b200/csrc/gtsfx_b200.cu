@@ -74,6 +74,8 @@ struct PartStats {          // lives in device memory, mirrored to pinned host m
   unsigned int bmax;             // bucket-boundary part of maxdepth
   unsigned int med_count;        // buckets queued for the block-level sorter
   unsigned int tile_leftover;    // buckets the tile sorter handed to the global sorters
+  unsigned int fb_unsorted;      // buckets that reach refinement without having been sorted at all
+  unsigned int pad2_;
 };
 
 struct ProfEvent { int cls; cudaEvent_t a, b; };
@@ -107,6 +109,9 @@ struct gtb200_ctx {
   int tile_mode;             // 0 off, 1 automatic, 2 forced (GTB200_TILE, testing knob)
   int tile_levels;           // 0 automatic, 1/2 forced (GTB200_TILE_LEVELS, testing knob)
   uint64_t *d_recB;          // second record buffer of the tile path (two partition levels)
+  uint32_t *d_isa;           // rank array of the prefix-doubling refinement (n+1 entries)
+  uint64_t cap_isa;
+  int doubling;              // 1 = prefix doubling when the part is the whole array (GTB200_DOUBLING, testing knob)
   uint32_t *d_bins;          // bin cursors / starts / chunk table of the tile path
   uint64_t cap_recB, cap_bins;
   // per part
@@ -1024,6 +1029,7 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
       // cnt <= maxbucket: sorted, only its tie groups are refined; otherwise the whole bucket is
       uint32_t *bits = cnt <= maxbucket ? fbbits + tieoff : fbbits;
       atomicOr(&bits[rel >> 5], 1u << (rel & 31));
+      if (cnt > maxbucket) atomicAdd(&out.stats->fb_unsorted, 1u);
       atomicAdd(&out.stats->fb_elems, (unsigned long long)cnt);
       atomicAdd(&out.stats->fb_buckets, 1u);
     }
@@ -1310,6 +1316,126 @@ __global__ void k_fb_compact(const uint32_t *__restrict__ keep, const uint32_t *
   idx2[o] = idx[j];
   gs2[o] = newgs[j];
   dep2[o] = newdep[j];
+}
+
+// ---------------------------------------------------------------------------------------------
+// Prefix doubling (Larsson-Sadakane style) for parts that cover the whole suffix array: the rank
+// array ISA (group start index of every suffix; final index for resolved ones, tail suffixes
+// included) lets a group tied on h symbols be split by the rank of the suffix h positions further
+// on, so a repeat of length L costs log2(L/h) rounds instead of L/28.
+// ---------------------------------------------------------------------------------------------
+__global__ void k_isa_from_sa(const uint32_t *__restrict__ sa, uint64_t width, uint32_t *__restrict__ isa) {
+  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < width) isa[sa[r]] = (uint32_t)r;
+}
+
+// suffixes that start with a special symbol (and the empty suffix n): rank = their place in the tail
+__global__ void k_isa_tail(const gtb200_range *__restrict__ ranges, const uint32_t *__restrict__ rangeoff,
+                           uint64_t nranges, uint64_t specialchars, uint64_t n, uint64_t nsort, uint32_t *isa) {
+  const uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e > specialchars) return;
+  if (e == specialchars) { isa[n] = (uint32_t)(nsort + e); return; }
+  uint64_t lo = 0, hi = nranges;
+  while (hi - lo > 1) {
+    const uint64_t mid = (lo + hi) >> 1;
+    if (rangeoff[mid] <= e) lo = mid; else hi = mid;
+  }
+  isa[ranges[lo].start + (e - rangeoff[lo])] = (uint32_t)(nsort + e);
+}
+
+__global__ void k_isa_groups(const uint32_t *__restrict__ idx, const uint32_t *__restrict__ gs,
+                             const uint32_t *__restrict__ sa, uint32_t A, uint32_t *isa) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < A) isa[sa[idx[j]]] = gs[j];
+}
+
+__global__ void k_dbl_keys(const uint32_t *__restrict__ sa, const uint32_t *__restrict__ idx,
+                           const uint32_t *__restrict__ gs, uint32_t A, uint64_t h, const uint32_t *__restrict__ isa,
+                           uint64_t *keys, uint32_t *posbuf, uint32_t *vals) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= A) return;
+  const uint32_t p = sa[idx[j]];
+  posbuf[j] = p;
+  keys[j] = ((uint64_t)gs[j] << 32) | (uint64_t)isa[(uint64_t)p + h];
+  vals[j] = j;
+}
+
+// sorted by (group, rank of the suffix h further on): new order, heads of the new groups
+__global__ void k_dbl_regroup(uint32_t *__restrict__ sa, const uint64_t *__restrict__ skeys,
+                              const uint32_t *__restrict__ svals, const uint32_t *__restrict__ idx,
+                              const uint32_t *__restrict__ posbuf, uint32_t A, uint32_t *head) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= A) return;
+  sa[idx[j]] = posbuf[svals[j]];
+  head[j] = (j == 0 || skeys[j] != skeys[j - 1]) ? 1u : 0u;
+}
+
+__global__ void k_dbl_update_isa(const uint32_t *__restrict__ sa, const uint32_t *__restrict__ idx,
+                                 const uint32_t *__restrict__ newgs, uint32_t A, uint32_t *isa) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < A) isa[sa[idx[j]]] = newgs[j];
+}
+
+// entries whose lcp the fast path could not determine: everything in the initial list but group heads
+__global__ void k_phi_flags(const uint32_t *__restrict__ idx0, const uint32_t *__restrict__ gs0, uint32_t A,
+                            uint32_t *flag) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < A) flag[j] = idx0[j] != gs0[j] ? 1u : 0u;
+}
+
+__global__ void k_phi_build(const uint32_t *__restrict__ idx0, const uint32_t *__restrict__ flag,
+                            const uint32_t *__restrict__ fscan, const uint32_t *__restrict__ sa, uint32_t A,
+                            uint64_t *keys, uint32_t *vals) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= A || !flag[j]) return;
+  const uint32_t o = fscan[j], r = idx0[j];
+  keys[o] = sa[r];          // text position: the Kasai order
+  vals[o] = r;
+}
+
+// Phi / Kasai over the open entries in text order: lcp(i, Phi(i)) >= lcp(i-1, Phi(i-1)) - 1, so a thread
+// that walks consecutive text positions re-compares only what is new.  One thread per PHI_CHUNK entries;
+// a chunk start (or a gap in the positions) restarts from the prefix length shared inside a bucket.
+#define PHI_CHUNK 32
+template <int BITS>
+__global__ void k_phi_lcp(Text<BITS> T, PartOut out, const uint64_t *__restrict__ skeys,
+                          const uint32_t *__restrict__ svals, uint32_t U, unsigned pl) {
+  constexpr int SPW = Text<BITS>::SPW;
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long sum = 0;
+  uint32_t mx = 0;
+  const uint64_t e0 = (uint64_t)t * PHI_CHUNK;
+  uint64_t l = 0, previ = ~0ull - 1;
+  for (uint64_t e = e0; e < e0 + PHI_CHUNK && e < U; ++e) {
+    const uint64_t i = skeys[e];
+    const uint32_t r = svals[e];
+    const uint64_t phi = out.sa[r - 1];
+    l = (i == previ + 1 && l > 0) ? l - 1 : 0;
+    if (l < pl) l = pl;                       // neighbours inside a bucket share the prefix
+    for (;;) {
+      const uint64_t x = T.window(i + l) ^ T.window(phi + l);
+      unsigned step = x ? (unsigned)__clzll((long long)x) / BITS : (unsigned)SPW;
+      const unsigned ra = T.reallen(i + l), rb = T.reallen(phi + l);
+      step = step < ra ? step : ra;
+      step = step < rb ? step : rb;
+      l += step;
+      if (step < (unsigned)SPW) break;
+    }
+    out.lcp[r] = (uint8_t)(l < 255 ? l : 255);
+    if (l >= 255) emit_large(out, r, (uint32_t)l);
+    sum += l;
+    mx = max(mx, (uint32_t)l);
+    previ = i;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sum += __shfl_xor_sync(GTB_FULL, sum, o);
+    mx = max(mx, __shfl_xor_sync(GTB_FULL, mx, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (sum) atomicAdd(&out.stats->lcpsum, sum);
+    if (mx) atomicMax(&out.stats->maxdepth, mx);
+  }
 }
 
 __global__ void k_llv_keys(const gtb200_largelcp *__restrict__ llv, uint32_t nl, uint64_t *keys, uint32_t *vals) {
@@ -1694,6 +1820,8 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
     const long v = atol(e2);
     if (v >= 0 && v < SORT_MAXBUCKET) c->sort_maxbucket = (uint32_t)v;
   }
+  c->doubling = 1;
+  if (const char *e6 = getenv("GTB200_DOUBLING")) c->doubling = atoi(e6);
   c->tile_mode = 1;
   if (const char *e4 = getenv("GTB200_TILE")) c->tile_mode = atoi(e4);
   if (const char *e5 = getenv("GTB200_TILE_LEVELS")) c->tile_levels = atoi(e5);
@@ -1878,6 +2006,7 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   const size_t o_pos = take(a4), o_head = take(a4), o_hscan = take(a4), o_headpos = take(a4 + 4), o_keep = take(a4);
   const size_t o_kscan = take(a4), o_newgs = take(a4), o_newdep = take(a4), o_hist = take((256ull * nblocks + 1) * 4);
   const size_t o_llvtmp = take(((size_t)A0 + 1) * sizeof(gtb200_largelcp));
+  const size_t o_idx00 = take(a4), o_gs00 = take(a4);
   if (ensure_scratch(c, need)) return -1;
   char *S = (char *)c->d_scratch;
   uint32_t *wcnt = (uint32_t *)(S + o_wcnt), *codes = (uint32_t *)(S + o_codes), *sizes = (uint32_t *)(S + o_sizes);
@@ -1892,6 +2021,7 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   uint32_t *headpos = (uint32_t *)(S + o_headpos), *keep = (uint32_t *)(S + o_keep), *kscan = (uint32_t *)(S + o_kscan);
   uint32_t *newgs = (uint32_t *)(S + o_newgs), *newdep = (uint32_t *)(S + o_newdep), *hist = (uint32_t *)(S + o_hist);
   gtb200_largelcp *llvtmp = (gtb200_largelcp *)(S + o_llvtmp);
+  uint32_t *idx00 = (uint32_t *)(S + o_idx00), *gs00 = (uint32_t *)(S + o_gs00);
   out.llv = llvtmp;
 
   // expand the two flagged-bucket bitmaps into the ordered element list
@@ -1922,6 +2052,87 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   int cur = 0;
   uint64_t rounds = 0;
   const int gsbits = ((bits_for(width) + 7) / 8) * 8;
+  const bool whole = mincode == 0 && maxcode == c->numcodes - 1 && out.partoffset == 0;
+  if (whole && c->doubling && A > 0) {
+    // ---- prefix doubling on ranks, then LCP of the refined entries by Phi/Kasai in text order ----
+    if (c->n + 2 > c->cap_isa) {
+      dfree(c, c->d_isa);
+      CK(dmalloc(c, &c->d_isa, (c->n + 2) * 4));
+      c->cap_isa = c->n + 2;
+    }
+    uint32_t *isa = c->d_isa;
+    CK(cudaMemcpyAsync(idx00, idx[0], (size_t)A * 4, cudaMemcpyDeviceToDevice, c->stream));
+    CK(cudaMemcpyAsync(gs00, gs[0], (size_t)A * 4, cudaMemcpyDeviceToDevice, c->stream));
+    {
+      ProfScope ps(c, KC_REFINE, 3);
+      k_isa_from_sa<<<grid_for(width, 256), 256, 0, c->stream>>>(out.sa, width, isa);
+      k_isa_tail<<<grid_for(c->specialchars + 1, 256), 256, 0, c->stream>>>(c->d_ranges, c->d_rangeoff, c->nranges,
+                                                                            c->specialchars, c->n, c->nsort, isa);
+      k_isa_groups<<<grid_for(A, 256), 256, 0, c->stream>>>(idx[0], gs[0], out.sa, A, isa);
+    }
+    uint64_t h = c->h_stats->fb_unsorted ? c->cp.pl : c->cp.pl + Text<BITS>::W;   // every open group is tied >= h
+    const int rbits = ((bits_for(c->n + 1) + 7) / 8) * 8;
+    while (A > 0) {
+      rounds++;
+      const unsigned g = grid_for(A, 256);
+      {
+        ProfScope ps(c, KC_REFINE, 1);
+        k_dbl_keys<<<g, 256, 0, c->stream>>>(out.sa, idx[cur], gs[cur], A, h, isa, keys, posbuf, vals);
+      }
+      const uint64_t *ko, *ko2;
+      const uint32_t *vo, *vo2;
+      if (device_radix_sort(c, keys, vals, kA, vA, kB, vB, hist, A, 0, rbits, &ko, &vo)) return -1;
+      if (ko == kA) { if (device_radix_sort(c, ko, vo, kB, vB, kA, vA, hist, A, 32, 32 + gsbits, &ko2, &vo2)) return -1; }
+      else          { if (device_radix_sort(c, ko, vo, kA, vA, kB, vB, hist, A, 32, 32 + gsbits, &ko2, &vo2)) return -1; }
+      {
+        ProfScope ps(c, KC_REFINE, 1);
+        k_dbl_regroup<<<g, 256, 0, c->stream>>>(out.sa, ko2, vo2, idx[cur], posbuf, A, head);
+      }
+      if (device_scan(c, head, hscan, A, 0, &c->d_stats->scan_total, KC_REFINE)) return -1;
+      {
+        ProfScope ps(c, KC_REFINE, 3);
+        k_fb_headpos<<<g, 256, 0, c->stream>>>(head, hscan, A, headpos, &c->d_stats->scan_total);
+        k_fb_finalize<<<g, 256, 0, c->stream>>>(head, hscan, headpos, idx[cur], A, keep, newgs);
+        k_dbl_update_isa<<<g, 256, 0, c->stream>>>(out.sa, idx[cur], newgs, A, isa);
+      }
+      if (device_scan(c, keep, kscan, A, 0, &c->d_stats->scan_total2, KC_REFINE)) return -1;
+      {
+        ProfScope ps(c, KC_REFINE, 1);
+        k_fb_compact<<<g, 256, 0, c->stream>>>(keep, kscan, idx[cur], newgs, dep[cur], A, idx[cur ^ 1], gs[cur ^ 1],
+                                               dep[cur ^ 1]);
+      }
+      CK(cudaGetLastError());
+      if (sync_stats(c)) return -1;
+      A = (uint32_t)c->h_stats->scan_total2;
+      cur ^= 1;
+      h = h * 2 < c->n ? h * 2 : c->n;
+      if (rounds > 70) return set_error("internal: prefix doubling does not converge");
+    }
+    // LCP of every entry that was not a group head when refinement started
+    {
+      ProfScope ps(c, KC_REFINE, 1);
+      k_phi_flags<<<grid_for(A1, 256), 256, 0, c->stream>>>(idx00, gs00, A1, head);
+    }
+    if (device_scan(c, head, hscan, A1, 0, &c->d_stats->scan_total, KC_REFINE)) return -1;
+    if (sync_stats(c)) return -1;
+    const uint32_t U = (uint32_t)c->h_stats->scan_total;
+    if (U) {
+      {
+        ProfScope ps(c, KC_REFINE, 1);
+        k_phi_build<<<grid_for(A1, 256), 256, 0, c->stream>>>(idx00, head, hscan, out.sa, A1, keys, vals);
+      }
+      const uint64_t *ko;
+      const uint32_t *vo;
+      if (device_radix_sort(c, keys, vals, kA, vA, kB, vB, hist, U, 0, rbits, &ko, &vo)) return -1;
+      {
+        ProfScope ps(c, KC_REFINE, 1);
+        k_phi_lcp<BITS><<<grid_for(((uint64_t)U + PHI_CHUNK - 1) / PHI_CHUNK, 128), 128, 0, c->stream>>>(T, out, ko, vo, U,
+                                                                                                    c->cp.pl);
+      }
+      CK(cudaGetLastError());
+      if (sync_stats(c)) return -1;
+    }
+  }
   while (A > 0) {
     rounds++;
     const unsigned g = grid_for(A, 256);

@@ -12,6 +12,12 @@ from oracle import oracle
 pytestmark = pytest.mark.gpu
 
 
+def load_golden_by_name(name):
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name + ".npz"))
+    return {"enc": z["enc"], "prefixlength": int(z["prefixlength"])}
+
+
 def _compare(got, want, label):
     for ext in ("bck", "suf", "lcp", "llv"):
         if got[ext] != want[ext]:
@@ -112,6 +118,31 @@ def test_tile_path_forced(case, parts, levels, monkeypatch):
     want = oracle.build(enc, 4, pl)
     got = sfx.suffixerator(enc, "dna", parts=parts, prefixlength=want["prefixlength"])
     _compare(got, want, f"tile/{case}/parts{parts}/levels{levels}")
+
+
+@pytest.mark.parametrize("doubling", ["0", "1"])
+@pytest.mark.parametrize("case", ["repeat_rich", "duplicate", "genome_like", "polyT", "maxbucket0"])
+def test_refinement_modes(case, doubling, monkeypatch):
+    """Deep repeats through both refinement strategies: prefix doubling on ranks + Phi/Kasai LCP (whole-array
+    parts) and text-window rounds (what sharded parts use)."""
+    monkeypatch.setenv("GTB200_DOUBLING", doubling)
+    if case == "repeat_rich":
+        enc, pl = synth.repeat_rich_dna(unit=6000, copies=9, seed=61), None
+    elif case == "duplicate":
+        g = load_golden_by_name("duplicate")
+        enc, pl = g["enc"], g["prefixlength"]
+    elif case == "genome_like":
+        enc, pl = synth.genome_like_dna(600_000, seed=62), None
+    elif case == "polyT":
+        enc, pl = np.concatenate([np.full(9000, 3, dtype=np.uint8), synth.random_dna(5000, seed=63),
+                                  np.full(7000, 3, dtype=np.uint8)]), 5
+    else:
+        monkeypatch.setenv("GTB200_MAXBUCKET", "0")     # every bucket reaches refinement unsorted
+        enc, pl = synth.genome_like_dna(200_000, seed=64), None
+    want = oracle.build(enc, 4, pl)
+    got = sfx.suffixerator(enc, "dna", prefixlength=want["prefixlength"])
+    _compare(got, want, f"refine/{case}/doubling{doubling}")
+    assert got["fallback_suffixes"] > 0
 
 
 def test_config2_ecoli_size_full_parity():
