@@ -1,0 +1,391 @@
+/*
+ * integration/sfx_suffixer_b200.c -- the B200 build of GenomeTools' Sfxiterator.
+ *
+ * A from-scratch implementation of the interface declared in src/match/sfx-suffixer.h:33-71
+ * (gt_Sfxiterator_new_withadditionalvalues / _new / _next / _longest / _bcktab2file / _delete)
+ * that is compiled INSTEAD of src/match/sfx-suffixer.c when libgenometools is built for B200.
+ * Everything around it is the unmodified reference: option parser, GtEncseq, GtSuffixsortspace,
+ * the .suf/.lcp/.llv/.bck/.prj writers.  The CPU loops of the original (k-mer counting, bucket
+ * insertion, gt_sortallbuckets and every sorter below it, the LCP bookkeeping) are replaced by
+ * calls into the C ABI of include/gtsfx_b200.h; there is no CPU fallback.
+ *
+ * integration/Makefile links it, together with the unmodified reference objects, into
+ * oracle/_ref/gt_b200 (test infrastructure: the drop-in check of tests/test_gpu_dropin.py).
+ * Only reference HEADERS are included; no reference source is copied.
+ */
+#include <limits.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "core/alphabet_api.h"
+#include "core/encseq.h"
+#include "core/error_api.h"
+#include "core/fa_api.h"
+#include "core/intbits.h"
+#include "core/logger_api.h"
+#include "core/ma_api.h"
+#include "core/timer_api.h"
+#include "core/unused_api.h"
+#include "core/xansi_api.h"
+#include "match/sfx-lcpvalues.h"
+#include "match/sfx-strategy.h"
+#include "match/sfx-suffixer.h"
+#include "match/sfx-suffixgetset.h"
+
+#include "gtsfx_b200.h"
+
+/* added to the B200 build of src/match/sfx-lcpvalues.c (integration/sfx_lcpvalues_b200.c) */
+void gt_Outlcpinfo_b200_writepart(GtOutlcpinfo *outlcpinfo, const uint8_t *lcp, GtUword width,
+                                  const void *llv, GtUword nllv, double lcptabsum, GtUword maxbranchdepth);
+
+struct Sfxiterator
+{
+  gtb200_ctx *dev;
+  const GtEncseq *encseq;          /* borrowed */
+  GtOutlcpinfo *outlcpinfo;        /* borrowed, may be NULL */
+  FILE *outfpbcktab;               /* written in _delete when parts > 1, like the reference */
+  GtSuffixsortspace *suffixsortspace;
+  GtTimer *sfxprogress;
+  GtLogger *logger;
+  bool suftabuint, bck_written;
+  unsigned int prefixlength;
+  uint32_t *leftborder, *countspecialcodes, *distpfxidx;
+  gtb200_countinfo ci;
+  uint64_t *mincodes, *maxcodes, *widths;
+  int numofparts, part;
+  GtUword totallength, bufentries, tail_done, longest;
+  bool longest_defined;
+  uint8_t *lcpbuf;
+  gtb200_largelcp *llvbuf;
+  GtUword llvcap;
+};
+
+static int b200_device(void)
+{
+  const char *env = getenv("GTB200_DEVICE");
+  return env != NULL ? atoi(env) : 0;
+}
+
+static void *b200_rawptr(Sfxiterator *sfi)
+{
+  /* partoffset and bucketleftidx stay 0, so index 0 is the start of the buffer that
+     gt_suffixsortspace_to_file (src/match/sfx-suffixgetset.c:462-478) writes from */
+  if (sfi->suftabuint)
+  {
+    return (void *) gt_suffixsortspace_getptr_uint32(sfi->suffixsortspace, 0);
+  }
+  return (void *) gt_suffixsortspace_getptr_ulong(sfi->suffixsortspace, 0);
+}
+
+static void b200_write_padded(FILE *fp, const void *ptr, size_t bytes)
+{
+  /* gt_mapspec_write: every table is followed by zero bytes up to a multiple of 8
+     (src/core/mapspec.c:350-365) */
+  static const char zeros[8] = {0};
+  if (bytes > 0)
+  {
+    gt_xfwrite(ptr, (size_t) 1, bytes, fp);
+  }
+  if (bytes % 8 != 0)
+  {
+    gt_xfwrite(zeros, (size_t) 1, 8 - bytes % 8, fp);
+  }
+}
+
+static void b200_bcktab_to_file(Sfxiterator *sfi, FILE *fp)
+{
+  /* table order of assignbcktabmapspecification (src/match/bcktab.c:519-570) */
+  b200_write_padded(fp, sfi->leftborder, sizeof (uint32_t) * (size_t) (sfi->ci.numofallcodes + 1));
+  b200_write_padded(fp, sfi->countspecialcodes, sizeof (uint32_t) * (size_t) sfi->ci.numofspecialcodes);
+  if (sfi->prefixlength > 2U)
+  {
+    b200_write_padded(fp, sfi->distpfxidx, sizeof (uint32_t) * (size_t) sfi->ci.numofdistpfxidx);
+  }
+  sfi->bck_written = true;
+}
+
+int gt_Sfxiterator_delete(Sfxiterator *sfi, GT_UNUSED GtError *err)
+{
+  if (sfi == NULL)
+  {
+    return 0;
+  }
+  if (sfi->outfpbcktab != NULL && !sfi->bck_written && sfi->leftborder != NULL)
+  {
+    /* parts > 1: the reference writes .bck here (src/match/sfx-suffixer.c:560-577) */
+    b200_bcktab_to_file(sfi, sfi->outfpbcktab);
+    gt_fa_fclose(sfi->outfpbcktab);
+  }
+  if (sfi->dev != NULL)
+  {
+    gtb200_close(sfi->dev);
+  }
+  if (sfi->suffixsortspace != NULL)
+  {
+    gt_suffixsortspace_delete(sfi->suffixsortspace, false);
+  }
+  gt_free(sfi->leftborder);
+  gt_free(sfi->countspecialcodes);
+  gt_free(sfi->distpfxidx);
+  gt_free(sfi->mincodes);
+  gt_free(sfi->maxcodes);
+  gt_free(sfi->widths);
+  gt_free(sfi->lcpbuf);
+  gt_free(sfi->llvbuf);
+  gt_free(sfi);
+  return 0;
+}
+
+Sfxiterator *gt_Sfxiterator_new_withadditionalvalues(const GtEncseq *encseq,
+                                                     GtReadmode readmode,
+                                                     unsigned int prefixlength,
+                                                     unsigned int numofparts,
+                                                     GtUword maximumspace,
+                                                     void *voidoutlcpinfo,
+                                                     FILE *outfpbcktab,
+                                                     const Sfxstrategy *sfxstrategy,
+                                                     GtTimer *sfxprogress,
+                                                     GT_UNUSED bool withprogressbar,
+                                                     GtLogger *logger,
+                                                     GtError *err)
+{
+  Sfxiterator *sfi;
+  gtb200_seqdesc seq;
+  gtb200_range *ranges = NULL;
+  GtUchar *encoded = NULL;
+  GtUword largest = 0;
+  unsigned int i;
+  int p;
+
+  gt_error_check(err);
+  if (readmode != GT_READMODE_FORWARD)
+  {
+    gt_error_set(err, "the B200 build of the suffixerator supports option -dir fwd only");
+    return NULL;
+  }
+  if (sfxstrategy != NULL && (sfxstrategy->spmopt_minlength > 0 || sfxstrategy->compressedoutput))
+  {
+    gt_error_set(err, "the B200 build of the suffixerator supports neither -spmopt nor -compressedoutput");
+    return NULL;
+  }
+  sfi = gt_calloc((size_t) 1, sizeof *sfi);
+  sfi->encseq = encseq;
+  sfi->outlcpinfo = (GtOutlcpinfo *) voidoutlcpinfo;
+  sfi->outfpbcktab = outfpbcktab;
+  sfi->sfxprogress = sfxprogress;
+  sfi->logger = logger;
+  sfi->prefixlength = prefixlength;
+  sfi->suftabuint = sfxstrategy != NULL && sfxstrategy->suftabuint;
+  sfi->totallength = gt_encseq_total_length(encseq);
+  if (sfi->suftabuint && sfi->totallength > (GtUword) UINT_MAX)
+  {
+    sfi->suftabuint = false;
+  }
+  memset(&seq, 0, sizeof seq);
+  seq.numofchars = gt_alphabet_num_of_chars(gt_encseq_alphabet(encseq));
+  seq.totallength = sfi->totallength;
+  seq.memory = GTB200_MEM_HOST;
+  if (seq.numofchars == 4U && gt_encseq_has_twobitencoding(encseq))
+  {
+    GtUword k = 0, nr = gt_encseq_realspecialranges(encseq);
+    seq.twobitencoding = (const uint64_t *) gt_encseq_twobitencoding_export(encseq);
+    seq.numofwords = gt_unitsoftwobitencoding(sfi->totallength);
+    ranges = gt_malloc(sizeof *ranges * (size_t) (nr + 1));
+    if (gt_encseq_has_specialranges(encseq))
+    {
+      GtRange range;
+      GtSpecialrangeiterator *sri = gt_specialrangeiterator_new(encseq, true);
+      while (gt_specialrangeiterator_next(sri, &range))
+      {
+        if (k > 0 && ranges[k-1].end == range.start)   /* iterator may split a run at page borders */
+        {
+          ranges[k-1].end = range.end;
+        } else
+        {
+          gt_assert(k <= nr);
+          ranges[k].start = range.start;
+          ranges[k++].end = range.end;
+        }
+      }
+      gt_specialrangeiterator_delete(sri);
+    }
+    seq.specialranges = ranges;
+    seq.numofspecialranges = k;
+  } else
+  {
+    encoded = gt_malloc(sizeof *encoded * (size_t) (sfi->totallength + 1));
+    if (sfi->totallength > 0)
+    {
+      gt_encseq_extract_encoded(encseq, encoded, 0, sfi->totallength - 1);
+    }
+    seq.encoded = encoded;
+  }
+  if (sfxprogress != NULL)
+  {
+    gt_timer_show_progress(sfxprogress, "counting prefix distribution", stdout);
+  }
+  if (gtb200_open(&sfi->dev, b200_device(), &seq, prefixlength) != 0)
+  {
+    gt_error_set(err, "%s", gtb200_last_error());
+    gt_free(ranges);
+    gt_free(encoded);
+    (void) gt_Sfxiterator_delete(sfi, NULL);
+    return NULL;
+  }
+  gt_free(ranges);
+  gt_free(encoded);
+  /* numofallcodes = sigma^pl, numofspecialcodes = sigma^(pl-1), distpfxidx = sum_{i=1}^{pl-2} sigma^i */
+  {
+    uint64_t allcodes = 1, speccodes = 1, d = 0, q = 1;
+    for (i = 0; i < prefixlength; i++) allcodes *= seq.numofchars;
+    for (i = 0; i + 1 < prefixlength; i++) speccodes *= seq.numofchars;
+    for (i = 1; i + 1 < prefixlength; i++) { q *= seq.numofchars; d += q; }
+    sfi->leftborder = gt_malloc(sizeof (uint32_t) * (size_t) (allcodes + 1));
+    sfi->countspecialcodes = gt_malloc(sizeof (uint32_t) * (size_t) speccodes);
+    sfi->distpfxidx = gt_malloc(sizeof (uint32_t) * (size_t) (d + 1));
+  }
+  if (gtb200_count(sfi->dev, sfi->leftborder, sfi->countspecialcodes, sfi->distpfxidx, &sfi->ci) != 0)
+  {
+    gt_error_set(err, "%s", gtb200_last_error());
+    (void) gt_Sfxiterator_delete(sfi, NULL);
+    return NULL;
+  }
+  gt_logger_log(logger, "largest bucket size=" GT_WU, (GtUword) sfi->ci.largestbucket);
+  if (maximumspace > 0)
+  {
+    gt_logger_log(logger, "B200 build: -memlimit is ignored, the index is built in %u part(s)", numofparts);
+  }
+  if (numofparts == 0)
+  {
+    numofparts = 1U;
+  }
+  sfi->mincodes = gt_malloc(sizeof (uint64_t) * numofparts);
+  sfi->maxcodes = gt_malloc(sizeof (uint64_t) * numofparts);
+  sfi->widths = gt_malloc(sizeof (uint64_t) * numofparts);
+  sfi->numofparts = gtb200_suftabparts(numofparts, sfi->leftborder, sfi->ci.numofallcodes, prefixlength,
+                                       sfi->mincodes, sfi->maxcodes, sfi->widths);
+  for (p = 0; p < sfi->numofparts; p++)
+  {
+    gt_logger_log(logger, "widthofpart[%d]=" GT_WU, p, (GtUword) sfi->widths[p]);
+    if (largest < (GtUword) sfi->widths[p])
+    {
+      largest = (GtUword) sfi->widths[p];
+    }
+  }
+  sfi->bufentries = largest;
+  if (sfi->bufentries < 1024 && sfi->bufentries < sfi->ci.specialcharacters + 1)
+  {
+    sfi->bufentries = sfi->ci.specialcharacters + 1 < 1024 ? sfi->ci.specialcharacters + 1 : 1024;
+  }
+  if (sfi->bufentries == 0)
+  {
+    sfi->bufentries = 1;
+  }
+  sfi->suffixsortspace = gt_suffixsortspace_new(sfi->bufentries, sfi->totallength, sfi->suftabuint, logger);
+  if (sfi->outlcpinfo != NULL)
+  {
+    gt_Outlcpinfo_numsuffixes2output_set(sfi->outlcpinfo, sfi->totallength + 1);
+    sfi->lcpbuf = gt_malloc(sizeof (uint8_t) * (size_t) (largest + 1));
+    sfi->llvcap = largest + 1;
+    sfi->llvbuf = gt_malloc(sizeof (gtb200_largelcp) * (size_t) sfi->llvcap);
+  }
+  return sfi;
+}
+
+Sfxiterator *gt_Sfxiterator_new(const GtEncseq *encseq,
+                                GtReadmode readmode,
+                                unsigned int prefixlength,
+                                unsigned int numofparts,
+                                GtUword maximumspace,
+                                const Sfxstrategy *sfxstrategy,
+                                GtTimer *sfxprogress,
+                                bool withprogressbar,
+                                GtLogger *logger,
+                                GtError *err)
+{
+  return gt_Sfxiterator_new_withadditionalvalues(encseq, readmode, prefixlength, numofparts, maximumspace,
+                                                 NULL, NULL, sfxstrategy, sfxprogress, withprogressbar,
+                                                 logger, err);
+}
+
+const GtSuffixsortspace *gt_Sfxiterator_next(GtUword *numberofsuffixes, bool *specialsuffixes, Sfxiterator *sfi)
+{
+  if (sfi->part < sfi->numofparts)
+  {
+    gtb200_partinfo pi;
+    const int p = sfi->part++;
+
+    if (sfi->sfxprogress != NULL)
+    {
+      gt_timer_show_progress(sfi->sfxprogress, "sorting the buckets", stdout);
+    }
+    if (gtb200_sort_part(sfi->dev, sfi->mincodes[p], sfi->maxcodes[p], b200_rawptr(sfi), sfi->suftabuint ? 1 : 0,
+                         sfi->lcpbuf, sfi->llvbuf, (uint64_t) sfi->llvcap, &pi) != 0)
+    {
+      fprintf(stderr, "gt suffixerator (B200): %s\n", gtb200_last_error());
+      exit(EXIT_FAILURE);         /* gt_Sfxiterator_next has no error channel (sfx-suffixer.h:60-62) */
+    }
+    if (pi.longest != UINT64_MAX)
+    {
+      sfi->longest = (GtUword) pi.longest;
+      sfi->longest_defined = true;
+    }
+    if (sfi->outlcpinfo != NULL)
+    {
+      gt_Outlcpinfo_b200_writepart(sfi->outlcpinfo, sfi->lcpbuf, (GtUword) pi.width, sfi->llvbuf,
+                                   (GtUword) pi.numoflargelcpvalues, pi.lcptabsum, (GtUword) pi.maxbranchdepth);
+    }
+    *numberofsuffixes = (GtUword) pi.width;
+    if (specialsuffixes != NULL)
+    {
+      *specialsuffixes = false;
+    }
+    return sfi->suffixsortspace;
+  }
+  if (sfi->tail_done < sfi->ci.specialcharacters + 1)
+  {
+    /* replaces gt_SSSPbuf_fillspecialnextpage: positions of the specials in ascending order, then n */
+    GtUword page = sfi->ci.specialcharacters + 1 - sfi->tail_done;
+    if (page > sfi->bufentries)
+    {
+      page = sfi->bufentries;
+    }
+    if (gtb200_tail(sfi->dev, sfi->tail_done, page, b200_rawptr(sfi), sfi->suftabuint ? 1 : 0) != 0)
+    {
+      fprintf(stderr, "gt suffixerator (B200): %s\n", gtb200_last_error());
+      exit(EXIT_FAILURE);
+    }
+    if (!sfi->longest_defined && sfi->tail_done == 0 && sfi->totallength > 0)
+    {
+      /* position 0 holds a special: it is the first entry of the tail */
+      sfi->longest = (GtUword) sfi->ci.numofsuffixestosort;
+      sfi->longest_defined = true;
+    }
+    sfi->tail_done += page;
+    *numberofsuffixes = page;
+    if (specialsuffixes != NULL)
+    {
+      *specialsuffixes = true;
+    }
+    return sfi->suffixsortspace;
+  }
+  return NULL;
+}
+
+int gt_Sfxiterator_bcktab2file(FILE *fp, Sfxiterator *sfi, GtError *err)
+{
+  gt_error_check(err);
+  if (sfi->numofparts <= 1)
+  {
+    b200_bcktab_to_file(sfi, fp);
+    gt_fa_fclose(fp);
+  }
+  return 0;
+}
+
+GtUword gt_Sfxiterator_longest(const Sfxiterator *sfi)
+{
+  return sfi->longest_defined ? sfi->longest : 0;
+}

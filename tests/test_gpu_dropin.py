@@ -1,0 +1,62 @@
+"""The drop-in itself: oracle/_ref/gt_b200 is the reference's `gt suffixerator` with ONLY the Sfxiterator
+translation unit replaced (integration/sfx_suffixer_b200.c over the C ABI) - option parser, GtEncseq, file
+writers and .prj code are the unmodified reference.  Its index files must be byte-identical to those of the
+unmodified binary oracle/_ref/gt_ref, and the reference's own checker (`gt dev sfxmap`) must accept them."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from genometools_b200 import encseq, synth
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GT_REF = os.path.join(ROOT, "oracle", "_ref", "gt_ref")
+GT_B200 = os.path.join(ROOT, "oracle", "_ref", "gt_b200")
+needs_binaries = pytest.mark.skipif(not (os.path.exists(GT_REF) and os.path.exists(GT_B200)),
+                                    reason="oracle/_ref/gt_ref or gt_b200 not built (make -C oracle; make -C integration)")
+
+CASES = {
+    "dna_nruns": (lambda: synth.multi_dna_with_nruns(300_000, nseq=6, seed=81), "dna", []),
+    "dna_nruns_parts3": (lambda: synth.multi_dna_with_nruns(300_000, nseq=6, seed=82), "dna", ["-parts", "3"]),
+    "dna_repeats_pl5": (lambda: synth.genome_like_dna(250_000, seed=83), "dna", ["-pl", "5"]),
+    "dna_suftabuint": (lambda: synth.random_dna(100_000, seed=84), "dna", ["-suftabuint"]),
+    "protein_parts2": (lambda: synth.random_protein(400, seed=85), "protein", ["-parts", "2"]),
+}
+
+
+def _run(binary, args, cwd):
+    p = subprocess.run([binary] + args, cwd=cwd, capture_output=True, text=True)
+    assert p.returncode == 0, f"{os.path.basename(binary)} {' '.join(args)} failed:\n{p.stdout}\n{p.stderr}"
+    return p.stdout
+
+
+@needs_binaries
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_gt_suffixerator_dropin_is_byte_identical(case, tmp_path):
+    gen, alphabet, extra = CASES[case]
+    enc = gen()
+    fasta = str(tmp_path / "in.fna")
+    encseq.write_fasta(fasta, encseq.decode_to_fasta_bytes(enc, alphabet))
+    common = ["suffixerator", "-" + alphabet, "-suf", "-lcp", "-bck", "-tis", "-des", "-sds", "-ssp"] + extra
+    _run(GT_REF, common + ["-indexname", "ref", "-db", fasta], str(tmp_path))
+    _run(GT_B200, common + ["-indexname", "b200", "-db", fasta], str(tmp_path))
+    for ext in ("suf", "lcp", "llv", "bck", "esq", "prj"):
+        a = open(tmp_path / f"ref.{ext}", "rb").read()
+        b = open(tmp_path / f"b200.{ext}", "rb").read()
+        assert a == b, f".{ext} differs between the reference and the B200 drop-in ({len(a)} vs {len(b)} bytes)"
+    if "-suftabuint" not in extra:
+        # the reference's own checker on the drop-in's index
+        _run(GT_REF, ["sfxmap", "-tis", "-suf", "-lcp", "-bck", "-esa", "b200"], str(tmp_path))
+
+
+@needs_binaries
+def test_dropin_reports_device_errors_through_gterror(tmp_path):
+    fasta = str(tmp_path / "in.fna")
+    encseq.write_fasta(fasta, encseq.decode_to_fasta_bytes(synth.random_dna(2000, seed=86), "dna"))
+    env = dict(os.environ, GTB200_DEVICE="99")
+    p = subprocess.run([GT_B200, "suffixerator", "-dna", "-suf", "-indexname", "x", "-db", fasta], cwd=str(tmp_path),
+                       capture_output=True, text=True, env=env)
+    assert p.returncode != 0 and "device 99 out of range" in p.stderr
