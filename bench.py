@@ -60,6 +60,14 @@ def make_workload(name: str, scale: int):
     return synth.random_protein(max(1, total // 334), seed=5), "protein"
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from one `ncu --set full`
+# capture of this same command (profiles/r1_ncu_full_ecoli.txt, profiles/r1_ncu_full_chr1.txt)
+NCU_TRAFFIC = {
+    ("ecoli", "sort_lcp"): 20.73e6,            # k_sort_buckets: 20.7 MB read, 0 written (outputs stay in L2)
+    ("chr1", "sort_lcp"): 3.265e9 + 1.200e9,   # k_tile_sort
+}
+
+
 def peak_hbm():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
@@ -423,7 +431,9 @@ def main():
             "gpu_launches": int(sum(v[1] for v in kern.values())),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak,
+                         "traffic": NCU_TRAFFIC.get((args.workload, dominant)) if world == 1 and SHRINK == 1 else None,
+                         "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": algo[dominant] / launches_per_step,
                          "avg_launch_ms": per_launch_s * 1e3,
                          "share_of_step": d_ms / total_ms if total_ms else None,
