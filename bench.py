@@ -206,6 +206,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=None)
     ap.add_argument("--skip-e2e", action="store_true", help="exploratory runs only: leaves e2e out of the line")
+    ap.add_argument("--verify", action="store_true", help="N > 1: compare every rank's part with a single-context run on rank 0")
     ap.add_argument("--shrink", type=int, default=1, help="exploratory: run on 1/D of the named workload size")
     args = ap.parse_args()
     global SHRINK
@@ -285,8 +286,33 @@ def main():
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
     info = sfx.CountInfo()
 
+    class _DevArray:       # lets torch wrap the library's counter tables for the NCCL all-reduce
+        def __init__(self, ptr, nwords):
+            self.__cuda_array_interface__ = {"shape": (nwords,), "typestr": "<i4", "data": (ptr, False), "version": 3}
+
+    shard = (n // world + 63) // 64 * 64
+    pos_lo, pos_hi = min(n, rank * shard), (n if rank == world - 1 else min(n, (rank + 1) * shard))
+    tables = {}
+    # The all-reduce costs ~0.25 ms of launch + NCCL latency (measured at N = 2): it pays only when a replicated
+    # count of the whole genome is more expensive than that, i.e. for genomes of chr1 size and up.
+    sharded_count = world > 1 and n >= 64_000_000
+
+    def count_step(ctx):
+        """Counting phase: replicated at N = 1; position-sharded + one all-reduce of the sigma^pl tables at N > 1."""
+        if not sharded_count:
+            sfx._check(L.gtb200_count(ctx, None, None, None, None))   # tables stay on the device
+            return
+        ptr, nw = C.c_void_p(), C.c_uint64()
+        sfx._check(L.gtb200_count_shard(ctx, pos_lo, pos_hi, 1 if rank == 0 else 0, C.byref(ptr), C.byref(nw)))
+        key = (ptr.value, nw.value)
+        if key not in tables:
+            tables[key] = torch.as_tensor(_DevArray(ptr.value, nw.value), device=dev)
+        dist.all_reduce(tables[key])                                  # ordered after the counting kernels on this stream
+        sfx._check(L.gtb200_count_finish(ctx, None, None, None, None))
+
     def device_step():
-        sfx._check(L.gtb200_count(it.ctx, None, None, None, None))   # tables stay on the device
+        with torch.cuda.stream(stream):
+            count_step(it.ctx)
         pinfo = it.sort_part_device(mincode, maxcode)
         if rank == world - 1:
             sfx._check(L.gtb200_tail(it.ctx, 0, it.specialcharacters + 1, None, 0))
@@ -343,7 +369,14 @@ def main():
     def e2e_step():
         upload_and_broadcast()                                  # pinned H2D (rank 0) + NVLink broadcast
         it2 = open_iter_raw()
-        sfx._check(L.gtb200_count(it2, lb_h.data_ptr(), csc_h.data_ptr(), dist_h.data_ptr(), C.byref(info)))
+        if not sharded_count:
+            sfx._check(L.gtb200_count(it2, lb_h.data_ptr(), csc_h.data_ptr(), dist_h.data_ptr(), C.byref(info)))
+        else:
+            with torch.cuda.stream(torch.cuda.ExternalStream(int(L.gtb200_stream(it2)), device=dev)):
+                ptr, nw = C.c_void_p(), C.c_uint64()
+                sfx._check(L.gtb200_count_shard(it2, pos_lo, pos_hi, 1 if rank == 0 else 0, C.byref(ptr), C.byref(nw)))
+                dist.all_reduce(torch.as_tensor(_DevArray(ptr.value, nw.value), device=dev))
+            sfx._check(L.gtb200_count_finish(it2, lb_h.data_ptr(), csc_h.data_ptr(), dist_h.data_ptr(), C.byref(info)))
         pi = sfx.PartInfo()
         sfx._check(L.gtb200_sort_part(it2, mincode, maxcode, suf_np.ctypes.data, 0, lcp_np.ctypes.data, None, 0,
                                       C.byref(pi)))
@@ -421,7 +454,8 @@ def main():
             "config": {"workload": WORKLOADS[args.workload][1] + (f" x{world} (genome grows with N)" if world > 1 else "")
                        + (f" SHRUNK 1/{SHRINK}" if SHRINK > 1 else ""),
                        "totallength": n, "prefixlength": it.prefixlength, "suffixes": n + 1,
-                       "sharding": f"{world} bucket ranges (-parts split), text broadcast over NCCL",
+                       "sharding": f"{world} bucket ranges (-parts split), text broadcast over NCCL, count "
+                                   + ("position-sharded + all-reduce" if sharded_count else "replicated"),
                        "l2": "flushed (256 MiB write) before every timed step",
                        "fallback_suffixes": int(pinfo.fallback_suffixes),
                        "insertion": ("tile path: staged partition x%d + shared-memory tile sort" % levels) if tile
@@ -445,6 +479,28 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(enc, alphabet)
         print(json.dumps(line))
+    if args.verify and world > 1:
+        import hashlib
+        itv = open_iter()
+        with torch.cuda.stream(torch.cuda.ExternalStream(itv.stream_handle(), device=dev)):
+            count_step(itv.ctx)
+        pv = sfx.PartInfo()
+        sufv = np.empty(width, dtype=np.uint64)
+        lcpv = np.empty(width, dtype=np.uint8)
+        sfx._check(L.gtb200_sort_part(itv.ctx, mincode, maxcode, sufv.ctypes.data, 0, lcpv.ctypes.data, None, 0, C.byref(pv)))
+        mine = (int(pv.partoffset), width, hashlib.sha256(sufv.tobytes()).hexdigest(), hashlib.sha256(lcpv.tobytes()).hexdigest())
+        itv.delete()
+        allparts = [None] * world
+        dist.all_gather_object(allparts, mine)
+        if rank == 0:
+            full = sfx.suffixerator(enc, alphabet, parts=1, device=local)
+            ok = True
+            for off, w, hs, hl in allparts:
+                ok &= hashlib.sha256(full["suf"][off * 8:(off + w) * 8]).hexdigest() == hs
+                ok &= hashlib.sha256(full["lcp"][off:off + w]).hexdigest() == hl
+            print("VERIFY multi-GPU parts vs single context:", "PASS" if ok else "FAIL", file=sys.stderr)
+            if not ok:
+                raise SystemExit("multi-GPU verification failed")
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

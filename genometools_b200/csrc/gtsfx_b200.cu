@@ -460,11 +460,13 @@ __global__ void k_range_lengths(const gtb200_range *__restrict__ ranges, uint64_
 #define KM_PPT 8     // positions per thread: four threads share one 32-base word (the loads hit L1), which gives
                      // small genomes enough threads to cover the latency of the returning atomics
 template <int BITS, int MODE>
-__global__ void __launch_bounds__(256) k_kmers(Text<BITS> T, CodeParams cp, uint64_t n, uint32_t *__restrict__ table,
-                                                uint32_t *__restrict__ sa, uint64_t mincode, uint64_t maxcode,
-                                                uint32_t partoffset) {
+__global__ void __launch_bounds__(256) k_kmers(Text<BITS> T, CodeParams cp, uint64_t pbase, uint64_t n,
+                                                uint32_t *__restrict__ table, uint32_t *__restrict__ sa,
+                                                uint64_t mincode, uint64_t maxcode, uint32_t partoffset) {
+  // positions [pbase, n): pbase is a multiple of 32; n is the end of the text or of this rank's position shard
+  // (a shard end is a multiple of 64, so no thread straddles it)
   const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const uint64_t p0 = t * KM_PPT;
+  const uint64_t p0 = pbase + t * KM_PPT;
   if (p0 >= n) return;
   const unsigned pl = cp.pl;
   const uint64_t mw = T.maskwin(p0);
@@ -643,12 +645,14 @@ __global__ void k_padded(Text<BITS> T, CodeParams cp, uint64_t n, const gtb200_r
     const uint64_t pv = prefix_value<BITS>(T.window(p), j, cp);
     const uint64_t fill = cp.pw[pl - j] - 1;    // pl-j digits of value sigma-1
     const uint64_t code = pv * (fill + 1) + fill;
-    atomicAdd(&hist[code], 1u);
-    atomicAdd(&csc[(code - (cp.sigma - 1)) / cp.sigma], 1u);
-    if (j + 1 < pl) {
-      uint64_t doff = 0;
-      for (unsigned i = 1; i < j; ++i) doff += cp.pw[i];
-      atomicAdd(&dist[doff + pv], 1u);
+    if (hist) {
+      atomicAdd(&hist[code], 1u);
+      atomicAdd(&csc[(code - (cp.sigma - 1)) / cp.sigma], 1u);
+      if (j + 1 < pl) {
+        uint64_t doff = 0;
+        for (unsigned i = 1; i < j; ++i) doff += cp.pw[i];
+        atomicAdd(&dist[doff + pv], 1u);
+      }
     }
     padkey[off + (cnt - j)] = (code << 6) | (uint64_t)(pl - j);
     padpos[off + (cnt - j)] = (uint32_t)p;
@@ -686,12 +690,14 @@ __global__ void __launch_bounds__(256) k_padded_small(Text<BITS> T, CodeParams c
       const uint64_t pv = prefix_value<BITS>(T.window(p), j, cp);
       const uint64_t fill = cp.pw[pl - j] - 1;
       const uint64_t code = pv * (fill + 1) + fill;
-      atomicAdd(&hist[code], 1u);
-      atomicAdd(&csc[(code - (cp.sigma - 1)) / cp.sigma], 1u);
-      if (j + 1 < pl) {
-        uint64_t doff = 0;
-        for (unsigned i = 1; i < j; ++i) doff += cp.pw[i];
-        atomicAdd(&dist[doff + pv], 1u);
+      if (hist) {                              // null on ranks that only need the list (sharded counting)
+        atomicAdd(&hist[code], 1u);
+        atomicAdd(&csc[(code - (cp.sigma - 1)) / cp.sigma], 1u);
+        if (j + 1 < pl) {
+          uint64_t doff = 0;
+          for (unsigned i = 1; i < j; ++i) doff += cp.pw[i];
+          atomicAdd(&dist[doff + pv], 1u);
+        }
       }
       skey[off + (cnt - j)] = (code << 6) | (uint64_t)(pl - j);
       spos[off + (cnt - j)] = (uint32_t)p;
@@ -1833,7 +1839,8 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
 }
 
 template <int BITS>
-static int count_impl(gtb200_ctx *c, bool need_host_values) {
+static int count_impl(gtb200_ctx *c, bool need_host_values, uint64_t pos_lo, uint64_t pos_hi, bool padded_counts,
+                      int phase /* 0 = everything, 1 = counting only, 2 = finish only */) {
   const Text<BITS> T = text_of<BITS>(c);
   const uint64_t n = c->n;
   const uint64_t nr1 = c->nranges + 1;
@@ -1849,30 +1856,32 @@ static int count_impl(gtb200_ctx *c, bool need_host_values) {
     CK(dmalloc(c, &c->d_padpos, c->padcap * 4));
     CK(dmalloc(c, &c->d_persist, 64));
   }
-  CK(cudaMemsetAsync(c->d_persist, 0, 64, c->stream));
   const bool small = nr1 <= PADSMALL_CAP && c->padcap <= PADSMALL_CAP;
   uint32_t *cntoff = c->d_padcnt;
+  uint32_t *hist_or_null = padded_counts ? c->d_lb : nullptr;
+  if (phase != 2) {
+  CK(cudaMemsetAsync(c->d_persist, 0, 64, c->stream));
   CK(cudaMemsetAsync(c->d_lb, 0, tablewords * 4, c->stream));
   CK(cudaMemsetAsync(c->d_stats, 0, sizeof(PartStats), c->stream));
-  if (n) {
+  if (pos_hi > pos_lo) {
     // A table larger than L2 is filled slice by slice (64 MB of counters per pass over the text), so
     // that the RED.ADDs always hit L2-resident lines; the text scan itself is cheap (n/4 bytes).
     const uint64_t slice = 1ull << 24;
     if (c->numcodes * 4 <= (96ull << 20)) {
       ProfScope ps(c, KC_COUNT);
-      k_kmers<BITS, 0><<<grid_for((n + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, n, c->d_lb, nullptr, 0, 0, 0);
+      k_kmers<BITS, 0><<<grid_for((pos_hi - pos_lo + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, pos_lo, pos_hi, c->d_lb, nullptr, 0, 0, 0);
     } else {
       for (uint64_t lo = 0; lo < c->numcodes; lo += slice) {
         const uint64_t hi = lo + slice - 1 < c->numcodes - 1 ? lo + slice - 1 : c->numcodes - 1;
         ProfScope ps(c, KC_COUNT);
-        k_kmers<BITS, 2><<<grid_for((n + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, n, c->d_lb, nullptr, lo, hi, 0);
+        k_kmers<BITS, 2><<<grid_for((pos_hi - pos_lo + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, pos_lo, pos_hi, c->d_lb, nullptr, lo, hi, 0);
       }
     }
   }
   // special-padded suffixes
   if (small) {
     ProfScope ps(c, KC_PADDED);
-    k_padded_small<BITS><<<1, 256, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, c->d_lb, c->d_csc, c->d_dist,
+    k_padded_small<BITS><<<1, 256, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, hist_or_null, c->d_csc, c->d_dist,
                                                    c->d_padkey, c->d_padpos, c->d_persist);
   } else {
     {
@@ -1883,9 +1892,14 @@ static int count_impl(gtb200_ctx *c, bool need_host_values) {
     if (device_scan(c, cntoff, cntoff, nr1, 0, c->d_persist, KC_PADDED)) return -1;
     {
       ProfScope ps(c, KC_PADDED);
-      k_padded<BITS, 1><<<grid_for(nr1, 128), 128, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, cntoff, c->d_lb,
-                                                                   c->d_csc, c->d_dist, c->d_padkey, c->d_padpos);
+      k_padded<BITS, 1><<<grid_for(nr1, 128), 128, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, cntoff,
+                                                                   hist_or_null, c->d_csc, c->d_dist, c->d_padkey, c->d_padpos);
     }
+  }
+  }   // phase != 2
+  if (phase == 1) {
+    CK(cudaGetLastError());
+    return 0;
   }
   {
     ProfScope ps(c, KC_COUNT);
@@ -1934,7 +1948,7 @@ extern "C" int gtb200_count(gtb200_ctx *c, uint32_t *leftborder, uint32_t *count
   CK(cudaSetDevice(c->device));
   {                                           // recomputed on every call (the tables are reused)
     const bool need = leftborder || countspecialcodes || distpfxidx || info;
-    const int rc = c->bits == 2 ? count_impl<2>(c, need) : count_impl<8>(c, need);
+    const int rc = c->bits == 2 ? count_impl<2>(c, need, 0, c->n, true, 0) : count_impl<8>(c, need, 0, c->n, true, 0);
     if (rc) return rc;
   }
   if (leftborder) CK(cudaMemcpyAsync(leftborder, c->d_lb, (c->numcodes + 1) * 4, cudaMemcpyDeviceToHost, c->stream));
@@ -1943,6 +1957,47 @@ extern "C" int gtb200_count(gtb200_ctx *c, uint32_t *leftborder, uint32_t *count
   if (distpfxidx && c->numdist)
     CK(cudaMemcpyAsync(distpfxidx, c->d_dist, c->numdist * 4, cudaMemcpyDeviceToHost, c->stream));
   if (leftborder || countspecialcodes || distpfxidx || info) CK(cudaStreamSynchronize(c->stream));
+  if (info) {
+    info->numofallcodes = c->numcodes;
+    info->numofspecialcodes = c->numspecialcodes;
+    info->numofdistpfxidx = c->numdist;
+    info->numofsuffixestosort = c->nsort;
+    info->specialcharacters = c->specialchars;
+    info->largestbucket = c->largestbucket;
+  }
+  return 0;
+}
+
+extern "C" int gtb200_count_shard(gtb200_ctx *c, uint64_t pos_lo, uint64_t pos_hi, int with_padded_counts,
+                                  void **tables_dev, uint64_t *ntablewords) {
+  if (!c) return set_error("gtb200_count_shard: null context");
+  if (pos_hi > c->n) pos_hi = c->n;
+  if (pos_lo > pos_hi || (pos_lo & 63) || (pos_hi != c->n && (pos_hi & 63)))
+    return set_error("gtb200_count_shard: [%llu,%llu) must be 64-aligned inside the sequence",
+                     (unsigned long long)pos_lo, (unsigned long long)pos_hi);
+  CK(cudaSetDevice(c->device));
+  const int rc = c->bits == 2 ? count_impl<2>(c, false, pos_lo, pos_hi, with_padded_counts != 0, 1)
+                              : count_impl<8>(c, false, pos_lo, pos_hi, with_padded_counts != 0, 1);
+  if (rc) return rc;
+  if (tables_dev) *tables_dev = c->d_lb;
+  if (ntablewords) *ntablewords = (c->numcodes + 2) + (c->numspecialcodes + 1) + (c->numdist + 1);
+  return 0;
+}
+
+extern "C" int gtb200_count_finish(gtb200_ctx *c, uint32_t *leftborder, uint32_t *countspecialcodes,
+                                   uint32_t *distpfxidx, gtb200_countinfo *info) {
+  if (!c) return set_error("gtb200_count_finish: null context");
+  if (!c->d_lb) return set_error("gtb200_count_finish: call gtb200_count_shard first");
+  CK(cudaSetDevice(c->device));
+  const bool need = leftborder || countspecialcodes || distpfxidx || info;
+  const int rc = c->bits == 2 ? count_impl<2>(c, need, 0, 0, true, 2) : count_impl<8>(c, need, 0, 0, true, 2);
+  if (rc) return rc;
+  if (leftborder) CK(cudaMemcpyAsync(leftborder, c->d_lb, (c->numcodes + 1) * 4, cudaMemcpyDeviceToHost, c->stream));
+  if (countspecialcodes)
+    CK(cudaMemcpyAsync(countspecialcodes, c->d_csc, c->numspecialcodes * 4, cudaMemcpyDeviceToHost, c->stream));
+  if (distpfxidx && c->numdist)
+    CK(cudaMemcpyAsync(distpfxidx, c->d_dist, c->numdist * 4, cudaMemcpyDeviceToHost, c->stream));
+  if (need) CK(cudaStreamSynchronize(c->stream));
   if (info) {
     info->numofallcodes = c->numcodes;
     info->numofspecialcodes = c->numspecialcodes;
@@ -2309,7 +2364,7 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
     ProfScope ps(c, KC_SCATTER, 2);
     k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, 2 * fbwords,
                                                               c->d_stats, c->d_lcp);
-    k_kmers<BITS, 1><<<grid_for((c->n + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, c->n, c->d_cursor, c->d_sa, mincode,
+    k_kmers<BITS, 1><<<grid_for((c->n + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, 0, c->n, c->d_cursor, c->d_sa, mincode,
                                                                             maxcode, (uint32_t)partoffset);
   } else {
     int shift = 0;

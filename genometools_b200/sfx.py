@@ -69,6 +69,7 @@ EXPORTS = [
     "gtb200_sort_part", "gtb200_tail", "gtb200_recommendedprefixlength", "gtb200_suftabparts",
     "gtb200_profile_enable", "gtb200_profile_read", "gtb200_profile_reset",
     "gtb200_leftborder_partialsums_noalloc", "gtb200_release_cached_memory",
+    "gtb200_count_shard", "gtb200_count_finish",
 ]
 
 
@@ -103,6 +104,9 @@ def load_library() -> C.CDLL:
                                       C.POINTER(C.c_uint64), C.c_int]
     L.gtb200_profile_reset.argtypes = [C.c_void_p]
     L.gtb200_profile_reset.restype = None
+    L.gtb200_count_shard.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_void_p),
+                                     C.POINTER(C.c_uint64)]
+    L.gtb200_count_finish.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(CountInfo)]
     L.gtb200_leftborder_partialsums_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
                                                         C.c_char_p, C.c_size_t]
     _lib = L

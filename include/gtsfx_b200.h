@@ -128,6 +128,22 @@ void *gtb200_stream(gtb200_ctx *ctx);
 int gtb200_count(gtb200_ctx *ctx, uint32_t *leftborder, uint32_t *countspecialcodes,
                  uint32_t *distpfxidx, gtb200_countinfo *info);
 
+/*
+ * Multi-GPU form of the counting phase ("counting position-sharded + all-reduce of
+ * the sigma^pl histogram").  gtb200_count_shard counts only the suffixes that START in [pos_lo, pos_hi)
+ * (pos_lo and pos_hi multiples of 64, pos_hi may be totallength) and leaves the raw counters - leftborder
+ * counts, countspecialcodes, distpfxidx, contiguous uint32_t[*ntablewords] at *tables_dev (device) - on the
+ * device; exactly one rank passes with_padded_counts = 1 (the special-padded suffixes come from the range
+ * table, which every rank holds).  The caller sums the tables over all ranks (ncclAllReduce on the
+ * context's stream), then every rank calls gtb200_count_finish, which performs the prefix sums and
+ * delivers what gtb200_count delivers.  One rank with [0, totallength) and with_padded_counts = 1 followed
+ * by gtb200_count_finish is identical to gtb200_count.
+ */
+int gtb200_count_shard(gtb200_ctx *ctx, uint64_t pos_lo, uint64_t pos_hi, int with_padded_counts,
+                       void **tables_dev, uint64_t *ntablewords);
+int gtb200_count_finish(gtb200_ctx *ctx, uint32_t *leftborder, uint32_t *countspecialcodes,
+                        uint32_t *distpfxidx, gtb200_countinfo *info);
+
 /* -- phase 2+3: insert, sort and LCP-annotate one part --------------------------------------- */
 
 /*
