@@ -246,6 +246,55 @@ def test_medium_buckets_block_sorter():
     _compare(got, want, "medium/protein")
 
 
+def test_sharded_count_equals_replicated_count():
+    """gtb200_count_shard on two position shards (as two ranks would run it) + summed tables + gtb200_count_finish
+    gives the bucket tables of gtb200_count; the sort that follows is unchanged."""
+    import ctypes as C
+    import torch
+
+    class DevArray:
+        def __init__(self, ptr, nwords):
+            self.__cuda_array_interface__ = {"shape": (nwords,), "typestr": "<i4", "data": (ptr, False), "version": 3}
+
+    enc = synth.multi_dna_with_nruns(700_000, nseq=5, seed=91)
+    want = oracle.build(enc, 4)
+    n = enc.shape[0]
+    L = sfx.load_library()
+    its = [sfx.Sfxiterator(4, n, None, 1, twobit=encseq.twobit_pack(enc), ranges=encseq.special_ranges(enc)) for _ in range(2)]
+    cut = (n // 2 + 63) // 64 * 64
+    tabs = []
+    for r, (lo, hi) in enumerate([(0, cut), (cut, n)]):
+        ptr, nw = C.c_void_p(), C.c_uint64()
+        sfx._check(L.gtb200_count_shard(its[r].ctx, lo, hi, 1 if r == 0 else 0, C.byref(ptr), C.byref(nw)))
+        tabs.append(torch.as_tensor(DevArray(ptr.value, nw.value), device="cuda"))
+    torch.cuda.synchronize()
+    total = tabs[0] + tabs[1]                  # what the all-reduce leaves on every rank
+    for r in range(2):
+        tabs[r].copy_(total)
+    torch.cuda.synchronize()
+    for r in range(2):
+        lb = np.zeros(want["leftborder"].shape[0], dtype=np.uint32)
+        csc = np.zeros(want["countspecialcodes"].shape[0], dtype=np.uint32)
+        dst = np.zeros(max(1, want["distpfxidx"].shape[0]), dtype=np.uint32)
+        info = sfx.CountInfo()
+        sfx._check(L.gtb200_count_finish(its[r].ctx, lb.ctypes.data, csc.ctypes.data, dst.ctypes.data, C.byref(info)))
+        assert np.array_equal(lb, want["leftborder"]) and np.array_equal(csc, want["countspecialcodes"])
+        assert np.array_equal(dst[:want["distpfxidx"].shape[0]], want["distpfxidx"])
+        assert info.numofsuffixestosort == want["nonspecial"]
+    # rank 1's context sorts the second half of the buckets from the summed tables
+    parts = sfx.suftabparts(2, want["leftborder"], want["prefixlength"])
+    lo, hi, width = parts[1]
+    pi = sfx.PartInfo()
+    suf = np.empty(width, dtype=np.uint64)
+    lcp = np.empty(width, dtype=np.uint8)
+    sfx._check(L.gtb200_sort_part(its[1].ctx, lo, hi, suf.ctypes.data, 0, lcp.ctypes.data, None, 0, C.byref(pi)))
+    off = int(pi.partoffset)
+    assert np.array_equal(suf, want["suf_array"][off:off + width])
+    assert lcp.tobytes() == want["lcp"][off:off + width]
+    for it in its:
+        it.delete()
+
+
 def test_suftabuint_and_tail_paging():
     enc = synth.multi_dna_with_nruns(100_000, nseq=5, seed=21)
     want = oracle.build(enc, 4)
