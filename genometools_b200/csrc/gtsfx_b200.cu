@@ -75,7 +75,7 @@ struct PartStats {          // lives in device memory, mirrored to pinned host m
   unsigned int med_count;        // buckets queued for the block-level sorter
   unsigned int tile_leftover;    // buckets the tile sorter handed to the global sorters
   unsigned int fb_unsorted;      // buckets that reach refinement without having been sorted at all
-  unsigned int pad2_;
+  unsigned int posmode_kept;     // open suffixes whose group is cut by a special (next round orders them by position)
 };
 
 struct ProfEvent { int cls; cudaEvent_t a, b; };
@@ -1315,14 +1315,17 @@ __global__ void k_fb_finalize(const uint32_t *__restrict__ head, const uint32_t 
 __global__ void k_fb_compact(const uint32_t *__restrict__ keep, const uint32_t *__restrict__ kscan,
                              const uint32_t *__restrict__ idx, const uint32_t *__restrict__ newgs,
                              const uint32_t *__restrict__ newdep, uint32_t A, uint32_t *idx2, uint32_t *gs2,
-                             uint32_t *dep2) {
+                             uint32_t *dep2, PartStats *stats) {
   const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= A || !keep[j]) return;
   const uint32_t o = kscan[j];
   idx2[o] = idx[j];
   gs2[o] = newgs[j];
   dep2[o] = newdep[j];
+  if (stats && newdep[j] == GTB_POSMODE) atomicAdd(&stats->posmode_kept, 1u);
 }
+
+__global__ void k_reset_posmode(PartStats *stats) { stats->posmode_kept = 0; }
 
 // ---------------------------------------------------------------------------------------------
 // Prefix doubling (Larsson-Sadakane style) for parts that cover the whole suffix array: the rank
@@ -2108,87 +2111,13 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   uint64_t rounds = 0;
   const int gsbits = ((bits_for(width) + 7) / 8) * 8;
   const bool whole = mincode == 0 && maxcode == c->numcodes - 1 && out.partoffset == 0;
-  if (whole && c->doubling && A > 0) {
-    // ---- prefix doubling on ranks, then LCP of the refined entries by Phi/Kasai in text order ----
-    if (c->n + 2 > c->cap_isa) {
-      dfree(c, c->d_isa);
-      CK(dmalloc(c, &c->d_isa, (c->n + 2) * 4));
-      c->cap_isa = c->n + 2;
-    }
-    uint32_t *isa = c->d_isa;
-    CK(cudaMemcpyAsync(idx00, idx[0], (size_t)A * 4, cudaMemcpyDeviceToDevice, c->stream));
-    CK(cudaMemcpyAsync(gs00, gs[0], (size_t)A * 4, cudaMemcpyDeviceToDevice, c->stream));
-    {
-      ProfScope ps(c, KC_REFINE, 3);
-      k_isa_from_sa<<<grid_for(width, 256), 256, 0, c->stream>>>(out.sa, width, isa);
-      k_isa_tail<<<grid_for(c->specialchars + 1, 256), 256, 0, c->stream>>>(c->d_ranges, c->d_rangeoff, c->nranges,
-                                                                            c->specialchars, c->n, c->nsort, isa);
-      k_isa_groups<<<grid_for(A, 256), 256, 0, c->stream>>>(idx[0], gs[0], out.sa, A, isa);
-    }
-    uint64_t h = c->h_stats->fb_unsorted ? c->cp.pl : c->cp.pl + Text<BITS>::W;   // every open group is tied >= h
-    const int rbits = ((bits_for(c->n + 1) + 7) / 8) * 8;
-    while (A > 0) {
-      rounds++;
-      const unsigned g = grid_for(A, 256);
-      {
-        ProfScope ps(c, KC_REFINE, 1);
-        k_dbl_keys<<<g, 256, 0, c->stream>>>(out.sa, idx[cur], gs[cur], A, h, isa, keys, posbuf, vals);
-      }
-      const uint64_t *ko, *ko2;
-      const uint32_t *vo, *vo2;
-      if (device_radix_sort(c, keys, vals, kA, vA, kB, vB, hist, A, 0, rbits, &ko, &vo)) return -1;
-      if (ko == kA) { if (device_radix_sort(c, ko, vo, kB, vB, kA, vA, hist, A, 32, 32 + gsbits, &ko2, &vo2)) return -1; }
-      else          { if (device_radix_sort(c, ko, vo, kA, vA, kB, vB, hist, A, 32, 32 + gsbits, &ko2, &vo2)) return -1; }
-      {
-        ProfScope ps(c, KC_REFINE, 1);
-        k_dbl_regroup<<<g, 256, 0, c->stream>>>(out.sa, ko2, vo2, idx[cur], posbuf, A, head);
-      }
-      if (device_scan(c, head, hscan, A, 0, &c->d_stats->scan_total, KC_REFINE)) return -1;
-      {
-        ProfScope ps(c, KC_REFINE, 3);
-        k_fb_headpos<<<g, 256, 0, c->stream>>>(head, hscan, A, headpos, &c->d_stats->scan_total);
-        k_fb_finalize<<<g, 256, 0, c->stream>>>(head, hscan, headpos, idx[cur], A, keep, newgs);
-        k_dbl_update_isa<<<g, 256, 0, c->stream>>>(out.sa, idx[cur], newgs, A, isa);
-      }
-      if (device_scan(c, keep, kscan, A, 0, &c->d_stats->scan_total2, KC_REFINE)) return -1;
-      {
-        ProfScope ps(c, KC_REFINE, 1);
-        k_fb_compact<<<g, 256, 0, c->stream>>>(keep, kscan, idx[cur], newgs, dep[cur], A, idx[cur ^ 1], gs[cur ^ 1],
-                                               dep[cur ^ 1]);
-      }
-      CK(cudaGetLastError());
-      if (sync_stats(c)) return -1;
-      A = (uint32_t)c->h_stats->scan_total2;
-      cur ^= 1;
-      h = h * 2 < c->n ? h * 2 : c->n;
-      if (rounds > 70) return set_error("internal: prefix doubling does not converge");
-    }
-    // LCP of every entry that was not a group head when refinement started
-    {
-      ProfScope ps(c, KC_REFINE, 1);
-      k_phi_flags<<<grid_for(A1, 256), 256, 0, c->stream>>>(idx00, gs00, A1, head);
-    }
-    if (device_scan(c, head, hscan, A1, 0, &c->d_stats->scan_total, KC_REFINE)) return -1;
-    if (sync_stats(c)) return -1;
-    const uint32_t U = (uint32_t)c->h_stats->scan_total;
-    if (U) {
-      {
-        ProfScope ps(c, KC_REFINE, 1);
-        k_phi_build<<<grid_for(A1, 256), 256, 0, c->stream>>>(idx00, head, hscan, out.sa, A1, keys, vals);
-      }
-      const uint64_t *ko;
-      const uint32_t *vo;
-      if (device_radix_sort(c, keys, vals, kA, vA, kB, vB, hist, U, 0, rbits, &ko, &vo)) return -1;
-      {
-        ProfScope ps(c, KC_REFINE, 1);
-        k_phi_lcp<BITS><<<grid_for(((uint64_t)U + PHI_CHUNK - 1) / PHI_CHUNK, 128), 128, 0, c->stream>>>(T, out, ko, vo, U,
-                                                                                                    c->cp.pl);
-      }
-      CK(cudaGetLastError());
-      if (sync_stats(c)) return -1;
-    }
-  }
-  while (A > 0) {
+  // Text-window rounds: the only strategy for sharded parts; for whole-array parts they run first when few
+  // suffixes are open (building the rank array costs a pass over the whole suffix array), and as long as a
+  // group cut by a special still has to be ordered by position.
+  const bool can_double = whole && c->doubling;
+  const uint64_t text_limit = !can_double ? ~0ull : ((uint64_t)A1 * 256 < c->n ? 6 : 0);
+  bool posmode_open = false;
+  while (A > 0 && (rounds < text_limit || posmode_open)) {
     rounds++;
     const unsigned g = grid_for(A, 256);
     {
@@ -2227,13 +2156,97 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
     {
       // newdep is indexed by sorted position j, like idx; gather of dep happened in regroup
       ProfScope ps(c, KC_REFINE, 1);
-      k_fb_compact<<<g, 256, 0, c->stream>>>(keep, kscan, idx[cur], newgs, newdep, A, idx[cur ^ 1], gs[cur ^ 1], dep[cur ^ 1]);
+      k_reset_posmode<<<1, 1, 0, c->stream>>>(c->d_stats);
+      k_fb_compact<<<g, 256, 0, c->stream>>>(keep, kscan, idx[cur], newgs, newdep, A, idx[cur ^ 1], gs[cur ^ 1], dep[cur ^ 1],
+                                             c->d_stats);
     }
     CK(cudaGetLastError());
     if (sync_stats(c)) return -1;
     A = (uint32_t)c->h_stats->scan_total2;
+    posmode_open = c->h_stats->posmode_kept > 0;
     cur ^= 1;
     if (rounds > (c->n / Text<BITS>::W) + 8) return set_error("internal: refinement does not converge");
+  }
+  if (A > 0) {                                 // what text rounds left open (or everything): prefix doubling
+    const uint32_t AD = A;                       // list size when doubling starts
+    // ---- prefix doubling on ranks, then LCP of the refined entries by Phi/Kasai in text order ----
+    if (c->n + 2 > c->cap_isa) {
+      dfree(c, c->d_isa);
+      CK(dmalloc(c, &c->d_isa, (c->n + 2) * 4));
+      c->cap_isa = c->n + 2;
+    }
+    uint32_t *isa = c->d_isa;
+    CK(cudaMemcpyAsync(idx00, idx[cur], (size_t)A * 4, cudaMemcpyDeviceToDevice, c->stream));
+    CK(cudaMemcpyAsync(gs00, gs[cur], (size_t)A * 4, cudaMemcpyDeviceToDevice, c->stream));
+    {
+      ProfScope ps(c, KC_REFINE, 3);
+      k_isa_from_sa<<<grid_for(width, 256), 256, 0, c->stream>>>(out.sa, width, isa);
+      k_isa_tail<<<grid_for(c->specialchars + 1, 256), 256, 0, c->stream>>>(c->d_ranges, c->d_rangeoff, c->nranges,
+                                                                            c->specialchars, c->n, c->nsort, isa);
+      k_isa_groups<<<grid_for(A, 256), 256, 0, c->stream>>>(idx[cur], gs[cur], out.sa, A, isa);
+    }
+    uint64_t h = c->h_stats->fb_unsorted ? c->cp.pl : c->cp.pl + Text<BITS>::W;   // every open group is tied >= h
+    const int rbits = ((bits_for(c->n + 1) + 7) / 8) * 8;
+    while (A > 0) {
+      rounds++;
+      const unsigned g = grid_for(A, 256);
+      {
+        ProfScope ps(c, KC_REFINE, 1);
+        k_dbl_keys<<<g, 256, 0, c->stream>>>(out.sa, idx[cur], gs[cur], A, h, isa, keys, posbuf, vals);
+      }
+      const uint64_t *ko, *ko2;
+      const uint32_t *vo, *vo2;
+      if (device_radix_sort(c, keys, vals, kA, vA, kB, vB, hist, A, 0, rbits, &ko, &vo)) return -1;
+      if (ko == kA) { if (device_radix_sort(c, ko, vo, kB, vB, kA, vA, hist, A, 32, 32 + gsbits, &ko2, &vo2)) return -1; }
+      else          { if (device_radix_sort(c, ko, vo, kA, vA, kB, vB, hist, A, 32, 32 + gsbits, &ko2, &vo2)) return -1; }
+      {
+        ProfScope ps(c, KC_REFINE, 1);
+        k_dbl_regroup<<<g, 256, 0, c->stream>>>(out.sa, ko2, vo2, idx[cur], posbuf, A, head);
+      }
+      if (device_scan(c, head, hscan, A, 0, &c->d_stats->scan_total, KC_REFINE)) return -1;
+      {
+        ProfScope ps(c, KC_REFINE, 3);
+        k_fb_headpos<<<g, 256, 0, c->stream>>>(head, hscan, A, headpos, &c->d_stats->scan_total);
+        k_fb_finalize<<<g, 256, 0, c->stream>>>(head, hscan, headpos, idx[cur], A, keep, newgs);
+        k_dbl_update_isa<<<g, 256, 0, c->stream>>>(out.sa, idx[cur], newgs, A, isa);
+      }
+      if (device_scan(c, keep, kscan, A, 0, &c->d_stats->scan_total2, KC_REFINE)) return -1;
+      {
+        ProfScope ps(c, KC_REFINE, 1);
+        k_fb_compact<<<g, 256, 0, c->stream>>>(keep, kscan, idx[cur], newgs, dep[cur], A, idx[cur ^ 1], gs[cur ^ 1],
+                                               dep[cur ^ 1], nullptr);
+      }
+      CK(cudaGetLastError());
+      if (sync_stats(c)) return -1;
+      A = (uint32_t)c->h_stats->scan_total2;
+      cur ^= 1;
+      h = h * 2 < c->n ? h * 2 : c->n;
+      if (rounds > 70) return set_error("internal: prefix doubling does not converge");
+    }
+    // LCP of every entry that was not a group head when refinement started
+    {
+      ProfScope ps(c, KC_REFINE, 1);
+      k_phi_flags<<<grid_for(AD, 256), 256, 0, c->stream>>>(idx00, gs00, AD, head);
+    }
+    if (device_scan(c, head, hscan, AD, 0, &c->d_stats->scan_total, KC_REFINE)) return -1;
+    if (sync_stats(c)) return -1;
+    const uint32_t U = (uint32_t)c->h_stats->scan_total;
+    if (U) {
+      {
+        ProfScope ps(c, KC_REFINE, 1);
+        k_phi_build<<<grid_for(AD, 256), 256, 0, c->stream>>>(idx00, head, hscan, out.sa, AD, keys, vals);
+      }
+      const uint64_t *ko;
+      const uint32_t *vo;
+      if (device_radix_sort(c, keys, vals, kA, vA, kB, vB, hist, U, 0, rbits, &ko, &vo)) return -1;
+      {
+        ProfScope ps(c, KC_REFINE, 1);
+        k_phi_lcp<BITS><<<grid_for(((uint64_t)U + PHI_CHUNK - 1) / PHI_CHUNK, 128), 128, 0, c->stream>>>(T, out, ko, vo, U,
+                                                                                                    c->cp.pl);
+      }
+      CK(cudaGetLastError());
+      if (sync_stats(c)) return -1;
+    }
   }
   info->fallback_rounds = rounds;
   // order the large-lcp records by suffix-array index
