@@ -106,6 +106,9 @@ struct gtb200_ctx {
   uint32_t sort_maxbucket;   // buckets above this size take the refinement path (testing knob)
   uint64_t twolevel_bytes;   // parts whose 4-byte suffix array exceeds this use the two-level insertion
   bool l2_window;            // persisting-L2 window set on the stream
+  int pipeline;              // 1 = overlap D2H of finished slices with the sort of the next (GTB200_PIPELINE, testing knob)
+  cudaStream_t copy_stream;
+  cudaEvent_t slice_ev[8];
   int tile_mode;             // 0 off, 1 automatic, 2 forced (GTB200_TILE, testing knob)
   int tile_levels;           // 0 automatic, 1/2 forced (GTB200_TILE_LEVELS, testing knob)
   uint64_t *d_recB;          // second record buffer of the tile path (two partition levels)
@@ -195,6 +198,8 @@ struct ProfScope {
 static std::mutex g_pool_mu;
 static std::vector<PoolBlock> g_pool[64];
 static std::vector<void *> g_pinned_pool;
+struct StreamSet { cudaStream_t main, copy; cudaEvent_t ev[8]; };
+static std::vector<StreamSet> g_stream_pool[64];   // streams and events of closed contexts, reused by the next open
 
 static void pool_release_device(int dev) {   // caller holds g_pool_mu
   for (auto &b : g_pool[dev]) cudaFree(b.p);
@@ -262,6 +267,13 @@ extern "C" void gtb200_release_cached_memory(void) {
     }
   for (void *h : g_pinned_pool) cudaFreeHost(h);
   g_pinned_pool.clear();
+  for (int d = 0; d < 64; ++d) {
+    for (auto &ss : g_stream_pool[d]) {
+      cudaStreamDestroy(ss.main);
+      if (ss.copy) { for (int k = 0; k < 8; ++k) cudaEventDestroy(ss.ev[k]); cudaStreamDestroy(ss.copy); }
+    }
+    g_stream_pool[d].clear();
+  }
   cudaSetDevice(cur);
 }
 
@@ -921,6 +933,7 @@ struct WarpSorter32 {
   }
 };
 
+#define GTB_MAXSLICES 8
 #define SORT_MAXBUCKET 128   // warp path: 4 elements per lane keep the kernel at 64 registers (32 warps/SM)
 #define SORT_WARPS 8
 
@@ -1588,6 +1601,8 @@ __global__ void k_part_init(const uint32_t *__restrict__ lb, uint32_t *__restric
   }
 }
 
+__global__ void k_reset_medcount(PartStats *stats) { stats->med_count = 0; }
+
 __global__ void k_reset_boundary_stats(PartStats *stats) {
   stats->bsum = 0;
   stats->bmax = 0;
@@ -1630,6 +1645,7 @@ static void free_ctx(gtb200_ctx *c) {
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->l2_window) cudaCtxResetPersistingL2Cache();
+  if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
   {
     std::lock_guard<std::mutex> lock(g_pool_mu);
     for (auto &b : c->blocks) g_pool[c->device].push_back(b);
@@ -1638,7 +1654,19 @@ static void free_ctx(gtb200_ctx *c) {
   }
   for (auto &p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
   for (auto e : c->evpool) cudaEventDestroy(e);
-  if (c->stream) cudaStreamDestroy(c->stream);
+  if (c->stream) {
+    if (c->l2_window) {
+      cudaStreamDestroy(c->stream);               // carries an access-policy attribute: not reusable
+      if (c->copy_stream) { for (int k = 0; k < 8; ++k) cudaEventDestroy(c->slice_ev[k]); cudaStreamDestroy(c->copy_stream); }
+    } else {
+      StreamSet ss;
+      ss.main = c->stream;
+      ss.copy = c->copy_stream;
+      for (int k = 0; k < 8; ++k) ss.ev[k] = c->slice_ev[k];
+      std::lock_guard<std::mutex> lock(g_pool_mu);
+      g_stream_pool[c->device].push_back(ss);
+    }
+  }
   delete c;
 }
 
@@ -1820,7 +1848,17 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
   c->numspecialcodes = c->cp.pw[prefixlength - 1];
   c->numdist = 0;
   for (unsigned i = 1; i + 1 < prefixlength; ++i) c->numdist += c->cp.pw[i];
-  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+  {
+    std::lock_guard<std::mutex> lock(g_pool_mu);
+    if (!g_stream_pool[device].empty()) {
+      const StreamSet ss = g_stream_pool[device].back();
+      g_stream_pool[device].pop_back();
+      c->stream = ss.main;
+      c->copy_stream = ss.copy;
+      for (int k = 0; k < 8; ++k) c->slice_ev[k] = ss.ev[k];
+    }
+  }
+  if (!c->stream && cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
     delete c;
     return set_error("gtb200_open: cudaStreamCreate failed");
   }
@@ -1829,6 +1867,8 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
     const long v = atol(e2);
     if (v >= 0 && v < SORT_MAXBUCKET) c->sort_maxbucket = (uint32_t)v;
   }
+  c->pipeline = 1;
+  if (const char *e7 = getenv("GTB200_PIPELINE")) c->pipeline = atoi(e7);
   c->doubling = 1;
   if (const char *e6 = getenv("GTB200_DOUBLING")) c->doubling = atoi(e6);
   c->tile_mode = 1;
@@ -2270,8 +2310,155 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   return 0;
 }
 
+// Everything that can be enqueued for the code range [lo,hi] of the current part without a host round trip:
+// insertion, special-padded suffixes, the sorters, bucket borders and the 64-bit image of the slice
+// [roff, roff+rwidth) of the part's buffers.  (lo - part mincode) is a multiple of 32.
 template <int BITS>
-static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb200_partinfo *info) {
+static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out, uint64_t pmin, uint64_t lo, uint64_t hi,
+                         uint64_t roff, uint64_t rwidth, uint64_t fbwords, bool first_of_part) {
+  const uint64_t rcodes = hi - lo + 1;
+  uint32_t *fbb = c->d_fbbits + ((lo - pmin) >> 5);
+  if (rwidth == 0) return 0;
+  {
+    ProfScope ps(c, KC_SORT);
+    k_reset_medcount<<<1, 1, 0, c->stream>>>(c->d_stats);
+  }
+  // ---- tile path (DNA): staged partition into shared-memory sized bins, then sort inside the tile ----
+  bool tile = BITS == 2 && c->tile_mode != 0 && rcodes >= 2 && (c->tile_mode == 2 || (rwidth >= (1u << 24) && rcodes >= 1024));
+  int shiftF = 0, shift1 = 0;
+  uint32_t nbinsF = 0, nb1 = 0;
+  if (tile) {
+    if (rwidth / rcodes > 4096) tile = false;                      // buckets alone exceed a tile
+    while (tile && shiftF < 10 && (((uint64_t)rwidth << (shiftF + 1)) / rcodes) <= 4608 && (rcodes >> (shiftF + 1)) >= 1) ++shiftF;
+    const uint64_t nf = ((rcodes - 1) >> shiftF) + 1;
+    bool two = nf > SP_MAXBINS;
+    if (c->tile_levels == 2 && nf >= 4) two = true;
+    if (c->tile_levels == 1 && nf <= SP_MAXBINS) two = false;
+    if (nf > (1ull << 20)) tile = false;
+    nbinsF = (uint32_t)nf;
+    if (tile && two) {
+      int lg = 0;
+      while ((1ull << lg) < nf) ++lg;
+      shift1 = shiftF + (lg + 1) / 2;
+      while ((((rcodes - 1) >> shift1) + 1) > SP_MAXBINS) ++shift1;
+      if (shift1 - shiftF > 10) tile = false;
+      nb1 = (uint32_t)(((rcodes - 1) >> shift1) + 1);
+    }
+  }
+  if (tile) {
+    const uint64_t binwords = (uint64_t)nbinsF + 3 * SP_MAXBINS + 64;
+    if (binwords > c->cap_bins) {
+      dfree(c, c->d_bins);
+      CK(dmalloc(c, &c->d_bins, binwords * 4));
+      c->cap_bins = binwords;
+    }
+    if (nb1 && c->part_width > c->cap_recB) {
+      dfree(c, c->d_recB);
+      CK(dmalloc(c, &c->d_recB, (c->part_width + 1) * 8));
+      c->cap_recB = c->part_width;
+    }
+    uint32_t *gcurF = c->d_bins, *gcur1 = gcurF + nbinsF, *start1 = gcur1 + SP_MAXBINS, *blkfirst = start1 + SP_MAXBINS;
+    CK(cudaFuncSetAttribute(k_stage_partition<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SP_SMEM));
+    CK(cudaFuncSetAttribute(k_stage_partition<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SP_SMEM));
+    const unsigned textblocks = grid_for(c->n, SP_CHUNK);
+    // records carry min(real length, 63) in their top 6 bits when the code leaves room for it
+    const int recL = (c->numcodes <= (1ull << 26) && c->cp.pl + Text<BITS>::W <= 63) ? 1 : 0;
+    {
+      ProfScope ps(c, KC_SCATTER, nb1 ? 5 : 2);
+      k_bins_init<<<grid_for(nbinsF, 256), 256, 0, c->stream>>>(c->d_lb, lo, shiftF, nbinsF, out.partoffset, gcurF,
+                                                                nullptr);
+      if (!nb1) {
+        k_stage_partition<BITS, true><<<textblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, lo, hi, shiftF, nbinsF,
+                                                                               nullptr, nullptr, nullptr, nullptr, 0, 0, gcurF,
+                                                                               c->d_suf64, recL);
+      } else {
+        k_bins_init<<<grid_for(nb1, 256), 256, 0, c->stream>>>(c->d_lb, lo, shift1, nb1, out.partoffset, gcur1, start1);
+        k_stage_partition<BITS, true><<<textblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, lo, hi, shift1, nb1,
+                                                                               nullptr, nullptr, nullptr, nullptr, 0, 0, gcur1,
+                                                                               c->d_recB, recL);
+        k_chunk_table<<<1, 256, 0, c->stream>>>(start1, gcur1, nb1, blkfirst);
+        const unsigned recblocks = (unsigned)(rwidth / SP_CHUNK + nb1 + 1);
+        k_stage_partition<BITS, false><<<recblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, lo, hi, shiftF,
+                                                                               1u << (shift1 - shiftF), c->d_recB, start1, gcur1,
+                                                                               blkfirst, nb1, shift1, gcurF, c->d_suf64, recL);
+      }
+    }
+    {
+      ProfScope ps(c, KC_SORT);
+      const unsigned tb = nbinsF < 148u * 5 ? nbinsF : 148u * 5;
+      k_tile_sort<BITS><<<tb, 256, 0, c->stream>>>(T, out, c->d_lb, c->d_cursor, c->d_suf64, gcurF, lo, hi, shiftF,
+                                                   nbinsF, c->cp.pl, recL, fbb, fbwords);
+    }
+    CK(cudaGetLastError());
+  }
+  const bool twolevel = !tile && rwidth * 4 > c->twolevel_bytes && rcodes >= 4096;
+  if (tile) {
+    // insertion already done
+  } else if (!twolevel) {
+    ProfScope ps(c, KC_SCATTER, 1);
+    k_kmers<BITS, 1><<<grid_for((c->n + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, 0, c->n, c->d_cursor, c->d_sa, lo,
+                                                                            hi, out.partoffset);
+  } else {
+    int shift = 0;
+    while (((rcodes - 1) >> shift) + 1 > PT_MAXBINS) ++shift;
+    const uint32_t nbins = (uint32_t)(((rcodes - 1) >> shift) + 1);
+    if (ensure_tilesums(c, PT_MAXBINS)) return -1;          // reused as the bins' record cursors
+    uint32_t *gcursor = c->d_tilesums;
+    ProfScope ps(c, KC_SCATTER, 3);
+    k_partition_init<<<grid_for(nbins, 256), 256, 0, c->stream>>>(c->d_lb, lo, shift, nbins, out.partoffset, gcursor);
+    k_partition<BITS><<<grid_for((c->n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, c->n, lo, hi, shift, nbins,
+                                                                             gcursor, c->d_suf64);
+    const size_t smem = ((size_t)4 << shift);
+    if (smem <= 160 * 1024) {
+      if (smem > 48 * 1024)
+        CK(cudaFuncSetAttribute(k_scatter_bins, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      k_scatter_bins<<<nbins, 1024, smem, c->stream>>>(c->d_suf64, gcursor, c->d_lb, c->d_cursor, c->d_sa, lo, hi,
+                                                       shift, out.partoffset);
+    } else {
+      k_partition_gaps<<<grid_for((uint64_t)nbins * 32, 256), 256, 0, c->stream>>>(gcursor, c->d_lb, lo, hi, shift,
+                                                                                  nbins, out.partoffset, c->d_suf64);
+      k_scatter_records<<<grid_for(rwidth, 256), 256, 0, c->stream>>>(c->d_suf64 + roff, rwidth, c->d_cursor, c->d_sa,
+                                                                     out.partoffset);
+    }
+  }
+  if (c->padcap > 1) {
+    ProfScope ps(c, KC_PADDED);
+    k_place_padded<<<grid_for(c->padcap, 256), 256, 0, c->stream>>>(c->d_padkey, c->d_padpos, c->d_persist, c->d_lb,
+                                                                     c->d_csc, c->cp.sigma, c->cp.pl, lo, hi, out);
+  }
+  {
+    ProfScope ps(c, KC_SORT);
+    uint64_t warps = rcodes < 148ull * 64 ? rcodes : 148ull * 64;   // 8 blocks of 8 warps per SM
+    const uint32_t medmax = c->sort_maxbucket == SORT_MAXBUCKET ? MED_MAX : 0;   // testing knob disables both
+    k_sort_buckets<BITS><<<grid_for(warps * 32, 256), 256, 0, c->stream>>>(T, out, c->d_lb, c->d_cursor, lo, hi,
+                                                                          c->cp.pl, fbb, c->sort_maxbucket,
+                                                                          c->d_medlist, medmax, tile ? 1 : 0, fbwords);
+  }
+  if (c->sort_maxbucket == SORT_MAXBUCKET && rwidth > SORT_MAXBUCKET) {
+    ProfScope ps(c, KC_SORT);
+    const size_t smem = (size_t)MED_MAX * 12;
+    CK(cudaFuncSetAttribute(k_sort_medium<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_sort_medium<BITS><<<148 * 4, 256, smem, c->stream>>>(T, out, c->d_lb, c->d_cursor, c->d_medlist, lo, c->cp.pl,
+                                                          fbb, fbwords);
+  }
+  {
+    ProfScope ps(c, KC_BOUNDARY, first_of_part && out.partoffset > 0 ? 2 : 1);
+    k_boundary<BITS><<<grid_for(rcodes, 256), 256, 0, c->stream>>>(T, c->cp, out, c->d_lb, c->d_csc, lo, hi);
+    if (first_of_part && out.partoffset > 0)
+      k_part_first<BITS><<<1, 32, 0, c->stream>>>(T, c->cp, out, c->d_lb, c->numcodes, c->d_csc, c->d_padkey, c->d_persist);
+  }
+  {
+    ProfScope ps(c, KC_WIDEN);
+    k_widen<<<grid_for(rwidth, 256), 256, 0, c->stream>>>(c->d_sa + roff, rwidth, c->d_suf64 + roff, (uint64_t)out.partoffset + roff,
+                                                         c->d_stats);
+  }
+  CK(cudaGetLastError());
+  return 0;
+}
+
+template <int BITS>
+static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb200_partinfo *info, void *h_suf,
+                          int h_suf_u32, uint8_t *h_lcp) {
   const Text<BITS> T = text_of<BITS>(c);
   // part geometry from the bucket table (known without a round trip when the part is everything)
   uint64_t partoffset = 0, width = c->nsort;
@@ -2300,136 +2487,60 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
   out.llv = nullptr;
   out.stats = c->d_stats;
   out.partoffset = (uint32_t)partoffset;
-  // ---- tile path (DNA): staged partition into shared-memory sized bins, then sort inside the tile ----
-  bool tile = BITS == 2 && c->tile_mode != 0 && ncodes >= 2 && (c->tile_mode == 2 || (width >= (1u << 24) && ncodes >= 1024));
-  int shiftF = 0, shift1 = 0;
-  uint32_t nbinsF = 0, nb1 = 0;
-  if (tile) {
-    if (width / ncodes > 4096) tile = false;                      // buckets alone exceed a tile
-    while (tile && shiftF < 10 && (((uint64_t)width << (shiftF + 1)) / ncodes) <= 4608 && (ncodes >> (shiftF + 1)) >= 1) ++shiftF;
-    const uint64_t nf = ((ncodes - 1) >> shiftF) + 1;
-    bool two = nf > SP_MAXBINS;
-    if (c->tile_levels == 2 && nf >= 4) two = true;
-    if (c->tile_levels == 1 && nf <= SP_MAXBINS) two = false;
-    if (nf > (1ull << 20)) tile = false;
-    nbinsF = (uint32_t)nf;
-    if (tile && two) {
-      int lg = 0;
-      while ((1ull << lg) < nf) ++lg;
-      shift1 = shiftF + (lg + 1) / 2;
-      while ((((ncodes - 1) >> shift1) + 1) > SP_MAXBINS) ++shift1;
-      if (shift1 - shiftF > 10) tile = false;
-      nb1 = (uint32_t)(((ncodes - 1) >> shift1) + 1);
-    }
+  // With host buffers to fill, the part is cut into up to 8 code ranges: while range k+1 is inserted and sorted
+  // on the compute stream, the finished slice of range k already crosses PCIe on the copy stream.
+  const bool to_host = h_suf != nullptr || h_lcp != nullptr;
+  int S = 1;
+  if (to_host && c->pipeline && width >= (2u << 20) && ncodes >= 4096) {
+    S = width >= (64u << 20) ? GTB_MAXSLICES : width >= (16u << 20) ? 4 : 2;
   }
-  if (tile) {
-    const uint64_t binwords = (uint64_t)nbinsF + 3 * SP_MAXBINS + 64;
-    if (binwords > c->cap_bins) {
-      dfree(c, c->d_bins);
-      CK(dmalloc(c, &c->d_bins, binwords * 4));
-      c->cap_bins = binwords;
+  uint64_t blo[GTB_MAXSLICES + 1], boff[GTB_MAXSLICES + 1];
+  blo[0] = mincode; boff[0] = 0;
+  blo[S] = maxcode + 1; boff[S] = width;
+  if (S > 1) {
+    uint32_t *hb = (uint32_t *)((char *)c->h_stats + 160);
+    for (int k = 1; k < S; ++k) {
+      blo[k] = mincode + ((ncodes * (uint64_t)k / S) & ~31ull);
+      CK(cudaMemcpyAsync(hb + k, c->d_lb + blo[k], 4, cudaMemcpyDeviceToHost, c->stream));
     }
-    if (nb1 && width > c->cap_recB) {
-      dfree(c, c->d_recB);
-      CK(dmalloc(c, &c->d_recB, (width + 1) * 8));
-      c->cap_recB = width;
+    CK(cudaStreamSynchronize(c->stream));
+    for (int k = 1; k < S; ++k) boff[k] = (uint64_t)hb[k] - partoffset;
+    if (!c->copy_stream) {
+      CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+      for (int k = 0; k < GTB_MAXSLICES; ++k) CK(cudaEventCreateWithFlags(&c->slice_ev[k], cudaEventDisableTiming));
     }
-    uint32_t *gcurF = c->d_bins, *gcur1 = gcurF + nbinsF, *start1 = gcur1 + SP_MAXBINS, *blkfirst = start1 + SP_MAXBINS;
-    CK(cudaFuncSetAttribute(k_stage_partition<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SP_SMEM));
-    CK(cudaFuncSetAttribute(k_stage_partition<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SP_SMEM));
-    const unsigned textblocks = grid_for(c->n, SP_CHUNK);
-    // records carry min(real length, 63) in their top 6 bits when the code leaves room for it
-    const int recL = (c->numcodes <= (1ull << 26) && c->cp.pl + Text<BITS>::W <= 63) ? 1 : 0;
-    {
-      ProfScope ps(c, KC_SCATTER, nb1 ? 6 : 3);
-      k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, 2 * fbwords,
-                                                                c->d_stats, c->d_lcp);
-      k_bins_init<<<grid_for(nbinsF, 256), 256, 0, c->stream>>>(c->d_lb, mincode, shiftF, nbinsF, (uint32_t)partoffset, gcurF,
-                                                                nullptr);
-      if (!nb1) {
-        k_stage_partition<BITS, true><<<textblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, mincode, maxcode, shiftF, nbinsF,
-                                                                               nullptr, nullptr, nullptr, nullptr, 0, 0, gcurF,
-                                                                               c->d_suf64, recL);
-      } else {
-        k_bins_init<<<grid_for(nb1, 256), 256, 0, c->stream>>>(c->d_lb, mincode, shift1, nb1, (uint32_t)partoffset, gcur1, start1);
-        k_stage_partition<BITS, true><<<textblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, mincode, maxcode, shift1, nb1,
-                                                                               nullptr, nullptr, nullptr, nullptr, 0, 0, gcur1,
-                                                                               c->d_recB, recL);
-        k_chunk_table<<<1, 256, 0, c->stream>>>(start1, gcur1, nb1, blkfirst);
-        const unsigned recblocks = (unsigned)(width / SP_CHUNK + nb1 + 1);
-        k_stage_partition<BITS, false><<<recblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, mincode, maxcode, shiftF,
-                                                                               1u << (shift1 - shiftF), c->d_recB, start1, gcur1,
-                                                                               blkfirst, nb1, shift1, gcurF, c->d_suf64, recL);
-      }
-    }
-    {
-      ProfScope ps(c, KC_SORT);
-      const unsigned tb = nbinsF < 148u * 5 ? nbinsF : 148u * 5;
-      k_tile_sort<BITS><<<tb, 256, 0, c->stream>>>(T, out, c->d_lb, c->d_cursor, c->d_suf64, gcurF, mincode, maxcode, shiftF,
-                                                   nbinsF, c->cp.pl, recL, c->d_fbbits, fbwords);
-    }
-    CK(cudaGetLastError());
-  }
-  const bool twolevel = !tile && width * 4 > c->twolevel_bytes && ncodes >= 4096;
-  if (tile) {
-    // insertion already done
-  } else if (!twolevel) {
-    ProfScope ps(c, KC_SCATTER, 2);
-    k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, 2 * fbwords,
-                                                              c->d_stats, c->d_lcp);
-    k_kmers<BITS, 1><<<grid_for((c->n + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, 0, c->n, c->d_cursor, c->d_sa, mincode,
-                                                                            maxcode, (uint32_t)partoffset);
-  } else {
-    int shift = 0;
-    while (((ncodes - 1) >> shift) + 1 > PT_MAXBINS) ++shift;
-    const uint32_t nbins = (uint32_t)(((ncodes - 1) >> shift) + 1);
-    if (ensure_tilesums(c, PT_MAXBINS)) return -1;          // reused as the bins' record cursors
-    uint32_t *gcursor = c->d_tilesums;
-    ProfScope ps(c, KC_SCATTER, 4);
-    k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, 2 * fbwords,
-                                                              c->d_stats, c->d_lcp);
-    k_partition_init<<<grid_for(nbins, 256), 256, 0, c->stream>>>(c->d_lb, mincode, shift, nbins, (uint32_t)partoffset, gcursor);
-    k_partition<BITS><<<grid_for((c->n + 31) / 32, 256), 256, 0, c->stream>>>(T, c->cp, c->n, mincode, maxcode, shift, nbins,
-                                                                             gcursor, c->d_suf64);
-    const size_t smem = ((size_t)4 << shift);
-    if (smem <= 160 * 1024) {
-      if (smem > 48 * 1024)
-        CK(cudaFuncSetAttribute(k_scatter_bins, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      k_scatter_bins<<<nbins, 1024, smem, c->stream>>>(c->d_suf64, gcursor, c->d_lb, c->d_cursor, c->d_sa, mincode, maxcode,
-                                                       shift, (uint32_t)partoffset);
-    } else {
-      k_partition_gaps<<<grid_for((uint64_t)nbins * 32, 256), 256, 0, c->stream>>>(gcursor, c->d_lb, mincode, maxcode, shift,
-                                                                                  nbins, (uint32_t)partoffset, c->d_suf64);
-      k_scatter_records<<<grid_for(width, 256), 256, 0, c->stream>>>(c->d_suf64, width, c->d_cursor, c->d_sa,
-                                                                     (uint32_t)partoffset);
-    }
-  }
-  if (c->padcap > 1) {
-    ProfScope ps(c, KC_PADDED);
-    k_place_padded<<<grid_for(c->padcap, 256), 256, 0, c->stream>>>(c->d_padkey, c->d_padpos, c->d_persist, c->d_lb,
-                                                                     c->d_csc, c->cp.sigma, c->cp.pl, mincode, maxcode, out);
   }
   {
-    ProfScope ps(c, KC_SORT);
-    uint64_t warps = ncodes < 148ull * 64 ? ncodes : 148ull * 64;   // 8 blocks of 8 warps per SM
-    const uint32_t medmax = c->sort_maxbucket == SORT_MAXBUCKET ? MED_MAX : 0;   // testing knob disables both
-    k_sort_buckets<BITS><<<grid_for(warps * 32, 256), 256, 0, c->stream>>>(T, out, c->d_lb, c->d_cursor, mincode, maxcode,
-                                                                          c->cp.pl, c->d_fbbits, c->sort_maxbucket,
-                                                                          c->d_medlist, medmax, tile ? 1 : 0, fbwords);
+    ProfScope ps(c, KC_SCATTER);
+    k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, 2 * fbwords,
+                                                              c->d_stats, c->d_lcp);
   }
-  if (c->sort_maxbucket == SORT_MAXBUCKET && width > SORT_MAXBUCKET) {
-    ProfScope ps(c, KC_SORT);
-    const size_t smem = (size_t)MED_MAX * 12;
-    CK(cudaFuncSetAttribute(k_sort_medium<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_sort_medium<BITS><<<148 * 4, 256, smem, c->stream>>>(T, out, c->d_lb, c->d_cursor, c->d_medlist, mincode, c->cp.pl,
-                                                          c->d_fbbits, fbwords);
+  for (int k = 0; k < S; ++k) {
+    if (enqueue_range<BITS>(c, T, out, mincode, blo[k], blo[k + 1] - 1, boff[k], boff[k + 1] - boff[k], fbwords, k == 0))
+      return -1;
+    if (S > 1) CK(cudaEventRecord(c->slice_ev[k], c->stream));
   }
-  // Bucket borders and the 64-bit image are launched right away: in the common case (no bucket
-  // needs refinement) the part is finished with a single host round trip.  If refinement was
-  // needed, both are simply repeated on the final order.
-  for (int pass = 0; pass < 2; ++pass) {
+  if (S > 1) {
+    for (int k = 0; k < S; ++k) {
+      const uint64_t o = boff[k], w = boff[k + 1] - boff[k];
+      if (w == 0) continue;
+      CK(cudaStreamWaitEvent(c->copy_stream, c->slice_ev[k], 0));
+      if (h_suf) {
+        if (h_suf_u32) CK(cudaMemcpyAsync((uint32_t *)h_suf + o, c->d_sa + o, w * 4, cudaMemcpyDeviceToHost, c->copy_stream));
+        else CK(cudaMemcpyAsync((uint64_t *)h_suf + o, c->d_suf64 + o, w * 8, cudaMemcpyDeviceToHost, c->copy_stream));
+      }
+      if (h_lcp) CK(cudaMemcpyAsync(h_lcp + o, c->d_lcp + o, w, cudaMemcpyDeviceToHost, c->copy_stream));
+    }
+  }
+  if (sync_stats(c)) return -1;
+  bool copied = S > 1;
+  if (S > 1) CK(cudaStreamSynchronize(c->copy_stream));
+  if (c->h_stats->fb_elems != 0) {
+    // some buckets need refinement: finish them, then redo borders and the image on the final order
+    if (refine_impl<BITS>(c, out, mincode, maxcode, width, info)) return -1;
     {
-      ProfScope ps(c, KC_BOUNDARY, partoffset > 0 ? 2 : 1);
+      ProfScope ps(c, KC_BOUNDARY, partoffset > 0 ? 3 : 2);
+      k_reset_boundary_stats<<<1, 1, 0, c->stream>>>(c->d_stats);
       k_boundary<BITS><<<grid_for(ncodes, 256), 256, 0, c->stream>>>(T, c->cp, out, c->d_lb, c->d_csc, mincode, maxcode);
       if (partoffset > 0)
         k_part_first<BITS><<<1, 32, 0, c->stream>>>(T, c->cp, out, c->d_lb, c->numcodes, c->d_csc, c->d_padkey, c->d_persist);
@@ -2440,12 +2551,15 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
     }
     CK(cudaGetLastError());
     if (sync_stats(c)) return -1;
-    if (pass == 1 || c->h_stats->fb_elems == 0) break;
-    if (refine_impl<BITS>(c, out, mincode, maxcode, width, info)) return -1;
-    {
-      ProfScope ps(c, KC_BOUNDARY);
-      k_reset_boundary_stats<<<1, 1, 0, c->stream>>>(c->d_stats);
+    copied = false;
+  }
+  if (to_host && !copied) {
+    if (h_suf) {
+      if (h_suf_u32) CK(cudaMemcpyAsync(h_suf, c->d_sa, width * 4, cudaMemcpyDeviceToHost, c->stream));
+      else CK(cudaMemcpyAsync(h_suf, c->d_suf64, width * 8, cudaMemcpyDeviceToHost, c->stream));
     }
+    if (h_lcp) CK(cudaMemcpyAsync(h_lcp, c->d_lcp, width, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
   }
   info->numoflargelcpvalues = c->h_stats->llv_count;
   info->maxbranchdepth = c->h_stats->maxdepth > c->h_stats->bmax ? c->h_stats->maxdepth : c->h_stats->bmax;
@@ -2462,7 +2576,8 @@ extern "C" int gtb200_sort_part_device(gtb200_ctx *c, uint64_t mincode, uint64_t
     return set_error("gtb200_sort_part_device: code range [%llu,%llu] invalid (numofallcodes %llu)",
                      (unsigned long long)mincode, (unsigned long long)maxcode, (unsigned long long)c->numcodes);
   CK(cudaSetDevice(c->device));
-  return c->bits == 2 ? sort_part_impl<2>(c, mincode, maxcode, info) : sort_part_impl<8>(c, mincode, maxcode, info);
+  return c->bits == 2 ? sort_part_impl<2>(c, mincode, maxcode, info, nullptr, 0, nullptr)
+                      : sort_part_impl<8>(c, mincode, maxcode, info, nullptr, 0, nullptr);
 }
 
 extern "C" int gtb200_part_device(gtb200_ctx *c, void **suftab_dev, void **lcptab_dev, void **llv_dev) {
@@ -2496,8 +2611,16 @@ extern "C" int gtb200_fetch_part(gtb200_ctx *c, void *suftab, int suftab_is_uint
 
 extern "C" int gtb200_sort_part(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, void *suftab, int suftab_is_uint32,
                                 uint8_t *lcptab, gtb200_largelcp *llv, uint64_t llv_capacity, gtb200_partinfo *info) {
-  if (gtb200_sort_part_device(c, mincode, maxcode, info)) return -1;
-  return gtb200_fetch_part(c, suftab, suftab_is_uint32, lcptab, llv, llv_capacity);
+  if (!c || !info) return set_error("gtb200_sort_part: null argument");
+  if (!c->counted) return set_error("gtb200_sort_part: call gtb200_count first");
+  if (mincode > maxcode || maxcode >= c->numcodes)
+    return set_error("gtb200_sort_part: code range [%llu,%llu] invalid (numofallcodes %llu)", (unsigned long long)mincode,
+                     (unsigned long long)maxcode, (unsigned long long)c->numcodes);
+  CK(cudaSetDevice(c->device));
+  const int rc = c->bits == 2 ? sort_part_impl<2>(c, mincode, maxcode, info, suftab, suftab_is_uint32, lcptab)
+                              : sort_part_impl<8>(c, mincode, maxcode, info, suftab, suftab_is_uint32, lcptab);
+  if (rc) return rc;
+  return gtb200_fetch_part(c, nullptr, 0, nullptr, llv, llv_capacity);   // suftab and lcptab are already on the host
 }
 
 extern "C" int gtb200_tail(gtb200_ctx *c, uint64_t first, uint64_t count, void *suftab, int suftab_is_uint32) {

@@ -23,6 +23,7 @@ CASES = {
     "dna_nruns_parts3": (lambda: synth.multi_dna_with_nruns(300_000, nseq=6, seed=82), "dna", ["-parts", "3"]),
     "dna_repeats_pl5": (lambda: synth.genome_like_dna(250_000, seed=83), "dna", ["-pl", "5"]),
     "dna_suftabuint": (lambda: synth.random_dna(100_000, seed=84), "dna", ["-suftabuint"]),
+    "dna_bwt_parts2": (lambda: synth.multi_dna_with_nruns(120_000, nseq=4, seed=87), "dna", ["-bwt", "-parts", "2"]),
     "protein_parts2": (lambda: synth.random_protein(400, seed=85), "protein", ["-parts", "2"]),
 }
 
@@ -43,7 +44,8 @@ def test_gt_suffixerator_dropin_is_byte_identical(case, tmp_path):
     common = ["suffixerator", "-" + alphabet, "-suf", "-lcp", "-bck", "-tis", "-des", "-sds", "-ssp"] + extra
     _run(GT_REF, common + ["-indexname", "ref", "-db", fasta], str(tmp_path))
     _run(GT_B200, common + ["-indexname", "b200", "-db", fasta], str(tmp_path))
-    for ext in ("suf", "lcp", "llv", "bck", "esq", "prj"):
+    exts = ("suf", "lcp", "llv", "bck", "esq", "prj") + (("bwt",) if "-bwt" in extra else ())
+    for ext in exts:
         a = open(tmp_path / f"ref.{ext}", "rb").read()
         b = open(tmp_path / f"b200.{ext}", "rb").read()
         assert a == b, f".{ext} differs between the reference and the B200 drop-in ({len(a)} vs {len(b)} bytes)"

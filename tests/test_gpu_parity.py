@@ -295,6 +295,23 @@ def test_sharded_count_equals_replicated_count():
         it.delete()
 
 
+@pytest.mark.parametrize("pipeline", ["0", "1"])
+def test_pipelined_fetch_matches(pipeline, monkeypatch):
+    """gtb200_sort_part cuts a large part into code ranges and copies finished slices while the next range is
+    sorted; with and without that overlap the host buffers hold the same bytes (also when refinement has to
+    redo the part afterwards)."""
+    monkeypatch.setenv("GTB200_PIPELINE", pipeline)
+    enc = synth.multi_dna_with_nruns(5_000_000, nseq=8, seed=95)
+    want = oracle.build(enc, 4)
+    got = sfx.suffixerator(enc, "dna")
+    _compare(got, want, f"pipeline{pipeline}/plain")
+    rep = synth.genome_like_dna(3_000_000, seed=96)
+    want = oracle.build(rep, 4)
+    got = sfx.suffixerator(rep, "dna", parts=1)
+    _compare(got, want, f"pipeline{pipeline}/repeats")
+    assert got["fallback_suffixes"] > 0
+
+
 def test_suftabuint_and_tail_paging():
     enc = synth.multi_dna_with_nruns(100_000, nseq=5, seed=21)
     want = oracle.build(enc, 4)
