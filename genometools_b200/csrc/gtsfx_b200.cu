@@ -409,6 +409,35 @@ __global__ void k_pack_bytes(const uint8_t *__restrict__ enc, uint64_t n, uint64
   mask[t] = mw;
 }
 
+// Readmodes (core/readmode_api.h:24-27): the index of `-dir rev|cpl|rcl` is the index of the reversed and/or
+// complemented sequence, so the device copy of the text is transformed once and everything else is unchanged.
+// One thread per 64 output positions.
+template <int BITS>
+__global__ void k_readmode_transform(const uint64_t *__restrict__ text, const uint64_t *__restrict__ mask, uint64_t n,
+                                     int reverse, int complement, uint64_t *__restrict__ otext,
+                                     uint64_t *__restrict__ omask, uint64_t nchunks) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nchunks) return;
+  constexpr int SPW = 64 / BITS;
+  const uint64_t p0 = t << 6;
+  uint64_t mw = 0;
+  for (int wq = 0; wq < 64 / SPW; ++wq) {
+    uint64_t word = 0;
+    for (int k = 0; k < SPW; ++k) {
+      const uint64_t p = p0 + (uint64_t)wq * SPW + k;
+      if (p >= n) continue;
+      const uint64_t src = reverse ? n - 1 - p : p;
+      const bool sp = (mask[src >> 6] >> (src & 63)) & 1ull;
+      uint64_t sym = (text[src / SPW] >> (64 - BITS * (src % SPW + 1))) & ((1ull << BITS) - 1);
+      if (sp) { mw |= 1ull << (wq * SPW + k); sym = 0; }
+      else if (complement) sym = 3 - sym;
+      word |= sym << (64 - BITS * (k + 1));
+    }
+    otext[t * (64 / SPW) + wq] = word;
+  }
+  omask[t] = mw;
+}
+
 // range derivation from the bitmap (byte input): count run starts per mask word
 __global__ void k_runs_count(const uint64_t *__restrict__ mask, uint64_t n, uint64_t nwords, uint32_t *cnt,
                              uint32_t *popc) {
@@ -1760,6 +1789,31 @@ static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
       if (c->bits == 2) k_pack_bytes<2><<<grid_for(nchunks, 256), 256, 0, c->stream>>>(d_enc, n, c->d_text, c->d_mask, nchunks);
       else k_pack_bytes<8><<<grid_for(nchunks, 256), 256, 0, c->stream>>>(d_enc, n, c->d_text, c->d_mask, nchunks);
     }
+    CK(cudaStreamSynchronize(c->stream));
+    dfree(c, tmp);
+  }
+  if (seq->readmode != 0) {
+    const int rev = seq->readmode == 1 || seq->readmode == 3, cpl = seq->readmode == 2 || seq->readmode == 3;
+    uint64_t *tmp2;
+    const size_t words = c->ntextwords + c->nmaskwords;
+    CK(dmalloc(c, &tmp2, words * 8));
+    CK(cudaMemsetAsync(tmp2, 0, words * 8, c->stream));
+    {
+      ProfScope ps(c, KC_PREP);
+      if (c->bits == 2)
+        k_readmode_transform<2><<<grid_for(nchunks, 256), 256, 0, c->stream>>>(c->d_text, c->d_mask, n, rev, cpl, tmp2,
+                                                                             tmp2 + c->ntextwords, nchunks);
+      else
+        k_readmode_transform<8><<<grid_for(nchunks, 256), 256, 0, c->stream>>>(c->d_text, c->d_mask, n, rev, cpl, tmp2,
+                                                                             tmp2 + c->ntextwords, nchunks);
+    }
+    CK(cudaMemcpyAsync(c->d_text, tmp2, words * 8, cudaMemcpyDeviceToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    dfree(c, tmp2);
+    dfree(c, c->d_ranges);          // the host's ranges describe the forward sequence
+    c->d_ranges = nullptr;
+  }
+  if (!c->d_ranges) {
     // derive the special ranges from the bitmap
     uint32_t *cnt, *popc;
     CK(dmalloc(c, &cnt, (nchunks + 1) * 4));
@@ -1779,7 +1833,6 @@ static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
     CK(cudaStreamSynchronize(c->stream));
     dfree(c, cnt);
     dfree(c, popc);
-    dfree(c, tmp);
   }
   {
     ProfScope ps(c, KC_PREP);
@@ -1824,6 +1877,9 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
   if (seq->twobitencoding && seq->numofspecialranges && !seq->specialranges)
     return set_error("gtb200_open: specialranges missing");
   if (prefixlength < 1) return set_error("gtb200_open: prefixlength must be >= 1");
+  if (seq->readmode < 0 || seq->readmode > 3) return set_error("gtb200_open: readmode %d unknown", seq->readmode);
+  if ((seq->readmode == 2 || seq->readmode == 3) && seq->numofchars != 4)
+    return set_error("gtb200_open: complement readmodes need the DNA alphabet");
   CK(cudaSetDevice(device));
   gtb200_ctx *c = new gtb200_ctx();
   c->device = device;

@@ -47,7 +47,7 @@ class SeqDesc(C.Structure):
     _fields_ = [("numofchars", C.c_uint), ("totallength", C.c_uint64),
                 ("twobitencoding", C.c_void_p), ("numofwords", C.c_uint64),
                 ("encoded", C.c_void_p), ("specialranges", C.c_void_p),
-                ("numofspecialranges", C.c_uint64), ("memory", C.c_int)]
+                ("numofspecialranges", C.c_uint64), ("memory", C.c_int), ("readmode", C.c_int)]
 
 
 class CountInfo(C.Structure):
@@ -146,7 +146,7 @@ class Sfxiterator:
                  enc: np.ndarray | int | None = None, twobit: np.ndarray | int | None = None,
                  ranges: np.ndarray | int | None = None, numofwords: int = 0, numofranges: int = 0,
                  device: int = 0, device_ptrs: bool = False, with_lcp: bool = True, suftabuint: bool = False,
-                 code_range: tuple[int, int] | None = None):
+                 code_range: tuple[int, int] | None = None, readmode: int = 0):
         L = load_library()
         self._L = L
         self._ctx = C.c_void_p()
@@ -159,6 +159,7 @@ class Sfxiterator:
         desc.numofchars = sigma
         desc.totallength = totallength
         desc.memory = 1 if device_ptrs else 0
+        desc.readmode = readmode
         self._keep = []
         if twobit is not None:
             if device_ptrs:
@@ -305,7 +306,8 @@ class Sfxiterator:
 
 
 def suffixerator(enc: np.ndarray, alphabet: str = "dna", indexname: str | None = None, parts: int = 1,
-                 prefixlength: int | None = None, device: int = 0, use_twobit: bool | None = None) -> dict:
+                 prefixlength: int | None = None, device: int = 0, use_twobit: bool | None = None,
+                 readmode: int = 0) -> dict:
     """`gt suffixerator -suf -lcp -bck` on an encoded sequence: runs the iterator to exhaustion and
     returns the byte images of .suf/.lcp/.llv/.bck plus the .prj statistics; writes the files when
     ``indexname`` is given."""
@@ -315,9 +317,9 @@ def suffixerator(enc: np.ndarray, alphabet: str = "dna", indexname: str | None =
         use_twobit = alphabet == "dna"
     if use_twobit:
         it = Sfxiterator(sigma, n, prefixlength, parts, twobit=_encseq.twobit_pack(enc),
-                         ranges=_encseq.special_ranges(enc), device=device)
+                         ranges=_encseq.special_ranges(enc), device=device, readmode=readmode)
     else:
-        it = Sfxiterator(sigma, n, prefixlength, parts, enc=enc, device=device)
+        it = Sfxiterator(sigma, n, prefixlength, parts, enc=enc, device=device, readmode=readmode)
     suf_chunks, lcp_chunks, llv_chunks = [], [], []
     try:
         while True:

@@ -59,6 +59,8 @@ typedef struct {
   const gtb200_range *specialranges;
   uint64_t numofspecialranges;
   int memory;
+  int readmode;                     /* GtReadmode (src/core/readmode_api.h:24-27): 0 forward, 1 reverse, 2 complement,
+                                       3 reverse complement; the arrays above always describe the FORWARD sequence */
 } gtb200_seqdesc;
 
 /* What gt_Sfxiterator_new logs / needs after the counting phase. */

@@ -160,11 +160,6 @@ Sfxiterator *gt_Sfxiterator_new_withadditionalvalues(const GtEncseq *encseq,
   int p;
 
   gt_error_check(err);
-  if (readmode != GT_READMODE_FORWARD)
-  {
-    gt_error_set(err, "the B200 build of the suffixerator supports option -dir fwd only");
-    return NULL;
-  }
   if (sfxstrategy != NULL && (sfxstrategy->spmopt_minlength > 0 || sfxstrategy->compressedoutput))
   {
     gt_error_set(err, "the B200 build of the suffixerator supports neither -spmopt nor -compressedoutput");
@@ -187,6 +182,7 @@ Sfxiterator *gt_Sfxiterator_new_withadditionalvalues(const GtEncseq *encseq,
   seq.numofchars = gt_alphabet_num_of_chars(gt_encseq_alphabet(encseq));
   seq.totallength = sfi->totallength;
   seq.memory = GTB200_MEM_HOST;
+  seq.readmode = (int) readmode;   /* GtReadmode values are the C ABI's (core/readmode_api.h:24-27) */
   if (seq.numofchars == 4U && gt_encseq_has_twobitencoding(encseq))
   {
     GtUword k = 0, nr = gt_encseq_realspecialranges(encseq);

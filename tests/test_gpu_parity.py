@@ -312,6 +312,30 @@ def test_pipelined_fetch_matches(pipeline, monkeypatch):
     assert got["fallback_suffixes"] > 0
 
 
+def _apply_readmode(enc, readmode):
+    e = enc[::-1].copy() if readmode in (1, 3) else enc.copy()
+    return np.where(e < 4, 3 - e, e).astype(np.uint8) if readmode in (2, 3) else e
+
+
+@pytest.mark.parametrize("readmode", [1, 2, 3])
+@pytest.mark.parametrize("use_twobit", [True, False])
+def test_readmodes(readmode, use_twobit):
+    """-dir rev / cpl / rcl (GtReadmode 1/2/3): the index of the transformed sequence (checked against the
+    reference in tests/test_oracle.py); the caller still hands over the forward sequence."""
+    enc = synth.multi_dna_with_nruns(300_000, nseq=6, seed=97)
+    want = oracle.build(_apply_readmode(enc, readmode), 4)
+    got = sfx.suffixerator(enc, "dna", parts=2, readmode=readmode, use_twobit=use_twobit)
+    _compare(got, want, f"readmode{readmode}/twobit{use_twobit}")
+    if readmode == 1:
+        prot = synth.random_protein(300, seed=98)
+        wantp = oracle.build(prot[::-1].copy(), 20, 3)
+        gotp = sfx.suffixerator(prot, "protein", prefixlength=3, readmode=1)
+        _compare(gotp, wantp, "readmode1/protein")
+    else:
+        with pytest.raises(sfx.Gtb200Error):
+            sfx.suffixerator(synth.random_protein(50, seed=99), "protein", prefixlength=2, readmode=readmode)
+
+
 def test_suftabuint_and_tail_paging():
     enc = synth.multi_dna_with_nruns(100_000, nseq=5, seed=21)
     want = oracle.build(enc, 4)

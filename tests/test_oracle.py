@@ -69,3 +69,22 @@ def test_encoder_roundtrip_and_ranges():
     i = np.flatnonzero(~sp)
     got = (tw[i // 32] >> (62 - 2 * (i % 32)).astype(np.uint64)) & np.uint64(3)
     assert np.array_equal(got.astype(np.uint8), enc[i])
+
+
+@pytest.mark.skipif(not oracle.have_reference(), reason="oracle/_ref/gt_ref not built")
+@pytest.mark.parametrize("direction,readmode", [("rev", 1), ("cpl", 2), ("rcl", 3)])
+def test_readmode_semantics_against_reference(direction, readmode):
+    """`-dir rev|cpl|rcl` indexes the reversed / complemented sequence (specials stay specials): pins the
+    transformation the GPU tests apply before asking the oracle."""
+    enc = synth.multi_dna_with_nruns(20_000, nseq=3, seed=5)
+    with tempfile.TemporaryDirectory() as tmp:
+        fa = os.path.join(tmp, "x.fna")
+        encseq.write_fasta(fa, encseq.decode_to_fasta_bytes(enc, "dna"))
+        ref = oracle.run_reference(fa, "dna", extra=["-dir", direction])
+    e = enc[::-1].copy() if readmode in (1, 3) else enc.copy()
+    if readmode in (2, 3):
+        e = np.where(e < 4, 3 - e, e).astype(np.uint8)
+    o = oracle.build(e, 4, int(ref["prj"]["prefixlength"]))
+    for ext in ("suf", "lcp", "llv", "bck"):
+        assert o[ext] == ref[ext], ext
+    assert ref["prj"]["readmode"] == str(readmode)
