@@ -10,7 +10,8 @@ sums, insertion, in-bucket sort, LCP, tail.  metric = suffixes/s (suffixes = tot
            the library's stream, L2 flushed between steps, max over ranks).
  * e2e   : the same work through the host-facing call (Sfxiterator over the C ABI) with HOST buffers:
            pinned H2D of the 2-bit sequence + range table, D2H of .suf (8 B/suffix) + .lcp + .bck tables.
- * N > 1 : one process per GPU.  The genome grows with N (N x the single-GPU size: weak scaling);
+ * N > 1 : one process per GPU.  The genome grows with N (N x the single-GPU size: weak scaling; --scaling strong
+           keeps the named genome and splits it, which is how the 3.1 Gbp target runs on 8 GPUs);
            rank 0 uploads, the packed sequence is broadcast over NCCL, every rank counts (replicated,
            n/4 bytes) and sorts + LCP-annotates its own bucket range (the reference's -parts split).
            No collective inside the timed device region.
@@ -163,7 +164,7 @@ def bench_reference(args):
     if rank != 0:
         return
     from oracle import oracle
-    enc, alphabet = make_workload(args.workload, args.gpus)
+    enc, alphabet = make_workload(args.workload, 1 if args.scaling == "strong" else args.gpus)
     budget = 12_000_000
     sample = enc if enc.shape[0] <= budget else enc[:budget]
     what = "whole workload" if sample is enc else f"first {budget} symbols"
@@ -186,7 +187,7 @@ def bench_reference(args):
     line = {
         "impl": "reference", "metric": "suffixes/sec for SA+LCP", "value": value, "unit": "suffixes/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": per * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "u64", "data": "synthetic",
         "config": {"workload": WORKLOADS[args.workload][1], "totallength": int(enc.shape[0]), "sample": what},
         "cpu_baseline": {"value": value, "unit": "suffixes/s", "cores": 1, "kind": kind,
                          "sample": f"{what}; gt suffixerator -suf -lcp -bck -tis, single thread (the reference "
@@ -206,6 +207,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=None)
     ap.add_argument("--skip-e2e", action="store_true", help="exploratory runs only: leaves e2e out of the line")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak (default): genome = N x the named size; strong: the named genome is split over the N GPUs")
     ap.add_argument("--verify", action="store_true", help="N > 1: compare every rank's part with a single-context run on rank 0")
     ap.add_argument("--shrink", type=int, default=1, help="exploratory: run on 1/D of the named workload size")
     args = ap.parse_args()
@@ -243,7 +246,7 @@ def main():
     meta = torch.zeros(3, dtype=torch.int64, device=dev)
     enc = None
     if rank == 0:
-        enc, _ = make_workload(args.workload, world)
+        enc, _ = make_workload(args.workload, 1 if args.scaling == "strong" else world)
         n = int(enc.shape[0])
         if alphabet == "dna":
             words_h = torch.from_numpy(encseq.twobit_pack(enc).view(np.int64)).pin_memory()
@@ -450,8 +453,8 @@ def main():
         line = {
             "metric": "suffixes/sec for SA+LCP", "value": value, "unit": "suffixes/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "u32 positions / u64 keys", "data": "synthetic",
-            "config": {"workload": WORKLOADS[args.workload][1] + (f" x{world} (genome grows with N)" if world > 1 else "")
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "u32 positions / u64 keys", "data": "synthetic",
+            "config": {"workload": WORKLOADS[args.workload][1] + (f" x{world} (genome grows with N)" if world > 1 and args.scaling == "weak" else "")
                        + (f" SHRUNK 1/{SHRINK}" if SHRINK > 1 else ""),
                        "totallength": n, "prefixlength": it.prefixlength, "suffixes": n + 1,
                        "sharding": f"{world} bucket ranges (-parts split), text broadcast over NCCL, count "
@@ -488,16 +491,24 @@ def main():
         sufv = np.empty(width, dtype=np.uint64)
         lcpv = np.empty(width, dtype=np.uint8)
         sfx._check(L.gtb200_sort_part(itv.ctx, mincode, maxcode, sufv.ctypes.data, 0, lcpv.ctypes.data, None, 0, C.byref(pv)))
-        mine = (int(pv.partoffset), width, hashlib.sha256(sufv.tobytes()).hexdigest(), hashlib.sha256(lcpv.tobytes()).hexdigest())
+        mine = (int(pv.partoffset), width, hashlib.sha256(sufv.data).hexdigest(), hashlib.sha256(lcpv.data).hexdigest())
         itv.delete()
         allparts = [None] * world
         dist.all_gather_object(allparts, mine)
         if rank == 0:
-            full = sfx.suffixerator(enc, alphabet, parts=1, device=local)
+            # single-context run of the whole genome on rank 0 (one part, prefix doubling available)
+            if alphabet == "dna":
+                itf = sfx.Sfxiterator(sigma, n, None, 1, twobit=words_d.data_ptr(), ranges=ranges_d.data_ptr(),
+                                      numofwords=nwords, numofranges=nrangewords // 2, device=local, device_ptrs=True)
+            else:
+                itf = sfx.Sfxiterator(sigma, n, None, 1, enc=words_d.data_ptr(), device=local, device_ptrs=True)
+            fsuf, flcp, _, _ = itf.next()
+            itf.delete()
             ok = True
             for off, w, hs, hl in allparts:
-                ok &= hashlib.sha256(full["suf"][off * 8:(off + w) * 8]).hexdigest() == hs
-                ok &= hashlib.sha256(full["lcp"][off:off + w]).hexdigest() == hl
+                ok &= hashlib.sha256(fsuf[off:off + w].data).hexdigest() == hs
+                ok &= hashlib.sha256(flcp[off:off + w].data).hexdigest() == hl
+            ok &= sum(w for _, w, _, _ in allparts) == fsuf.shape[0]
             print("VERIFY multi-GPU parts vs single context:", "PASS" if ok else "FAIL", file=sys.stderr)
             if not ok:
                 raise SystemExit("multi-GPU verification failed")
