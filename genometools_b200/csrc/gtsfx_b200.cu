@@ -310,12 +310,14 @@ static int device_scan(gtb200_ctx *c, const uint32_t *in, uint32_t *out, uint64_
     if (d_total) CK(cudaMemsetAsync(d_total, 0, sizeof *d_total, c->stream));
     return 0;
   }
-  const uint64_t ntiles = (n + SC_TILE - 1) / SC_TILE;
+  const int rounds = n <= (1u << 21) ? 2 : SC_ROUNDS;
+  const uint64_t tile = (uint64_t)SC_THREADS * rounds;
+  const uint64_t ntiles = (n + tile - 1) / tile;
   if (ensure_tilesums(c, ntiles)) return -1;
   ProfScope ps(c, cls, 3);
-  k_scan_tilesums<<<(unsigned)ntiles, SC_THREADS, 0, c->stream>>>(in, n, c->d_tilesums);
+  k_scan_tilesums<<<(unsigned)ntiles, SC_THREADS, 0, c->stream>>>(in, n, c->d_tilesums, rounds);
   k_scan_spine<<<1, SC_THREADS, 0, c->stream>>>(c->d_tilesums, (uint32_t)ntiles, d_total);
-  k_scan_apply<<<(unsigned)ntiles, SC_THREADS, 0, c->stream>>>(in, out, n, c->d_tilesums, append_total);
+  k_scan_apply<<<(unsigned)ntiles, SC_THREADS, 0, c->stream>>>(in, out, n, c->d_tilesums, append_total, rounds);
   CK(cudaGetLastError());
   return 0;
 }
@@ -879,15 +881,15 @@ struct WarpSorter {
 // LCP.  Returns false (nothing written) if two suffixes agree on all pl+W symbols.
 template <int BITS, int E>
 __device__ __forceinline__ bool warp_sort_bucket(const Text<BITS> &T, const PartOut &out, const uint32_t *src,
-                                                 const uint8_t *srcL, uint32_t start, uint32_t cnt, unsigned pl, int lane,
-                                                 unsigned long long &sum, uint32_t &mx) {
+                                                 const uint32_t *pre, const uint8_t *srcL, uint32_t start, uint32_t cnt,
+                                                 unsigned pl, int lane, unsigned long long &sum, uint32_t &mx) {
   uint64_t k[E];
   uint32_t v[E];
 #pragma unroll
   for (int e = 0; e < E; ++e) {
     const uint32_t i = e * 32 + lane;
     if (i < cnt) {
-      v[e] = src[i];
+      v[e] = pre ? pre[e] : src[i];
       k[e] = srcL ? make_key_known<BITS>(T, (uint64_t)v[e] + pl, (unsigned)srcL[i] - pl)
                   : make_key<BITS>(T, (uint64_t)v[e] + pl);
     } else {
@@ -973,8 +975,9 @@ struct WarpSorter32 {
 // Returns 0 = done, 1 = redo with warp_sort_bucket.
 template <int BITS, int E>
 __device__ __forceinline__ int warp_sort_bucket32(const Text<BITS> &T, const PartOut &out, const uint32_t *src,
-                                                  const uint8_t *srcL, uint32_t start, uint32_t cnt, unsigned pl, int lane,
-                                                  uint64_t *skey, uint32_t *spos, unsigned long long &sum, uint32_t &mx) {
+                                                  const uint32_t *pre, const uint8_t *srcL, uint32_t start, uint32_t cnt,
+                                                  unsigned pl, int lane, uint64_t *skey, uint32_t *spos,
+                                                  unsigned long long &sum, uint32_t &mx) {
   uint32_t k[E];
   __syncwarp();
 #pragma unroll
@@ -982,7 +985,7 @@ __device__ __forceinline__ int warp_sort_bucket32(const Text<BITS> &T, const Par
     const uint32_t i = e * 32 + lane;
     k[e] = 0xffffffffu;
     if (i < cnt) {
-      const uint32_t p = src[i];
+      const uint32_t p = pre ? pre[e] : src[i];
       const uint64_t fk = srcL ? make_key_known<BITS>(T, (uint64_t)p + pl, (unsigned)srcL[i] - pl)
                                : make_key<BITS>(T, (uint64_t)p + pl);
       skey[i] = fk;
@@ -1030,12 +1033,14 @@ __device__ __forceinline__ int warp_sort_bucket32(const Text<BITS> &T, const Par
 
 template <int BITS, int E>
 __device__ __forceinline__ bool warp_sort_any(const Text<BITS> &T, const PartOut &out, const uint32_t *src,
-                                              const uint8_t *srcL, uint32_t start, uint32_t cnt, unsigned pl, int lane,
-                                              uint64_t *skey, uint32_t *spos, unsigned long long &sum, uint32_t &mx) {
+                                              const uint32_t *pre, const uint8_t *srcL, uint32_t start, uint32_t cnt,
+                                              unsigned pl, int lane, uint64_t *skey, uint32_t *spos,
+                                              unsigned long long &sum, uint32_t &mx) {
+  // pre: the bucket's positions already in registers (element e*32+lane in pre[e]), loaded one bucket ahead
   if (BITS == 2) {
-    if (warp_sort_bucket32<BITS, E>(T, out, src, srcL, start, cnt, pl, lane, skey, spos, sum, mx) == 0) return true;
+    if (warp_sort_bucket32<BITS, E>(T, out, src, pre, srcL, start, cnt, pl, lane, skey, spos, sum, mx) == 0) return true;
   }
-  return warp_sort_bucket<BITS, E>(T, out, src, srcL, start, cnt, pl, lane, sum, mx);
+  return warp_sort_bucket<BITS, E>(T, out, src, pre, srcL, start, cnt, pl, lane, sum, mx);
 }
 
 template <int BITS>
@@ -1054,12 +1059,39 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
   const uint64_t nw = ((uint64_t)gridDim.x * blockDim.x) >> 5;
   unsigned long long sum = 0;
   uint32_t mx = 0;
-  uint32_t nb0 = 0, ncur = 0;
-  if (mincode + gw <= maxcode) { nb0 = lb[mincode + gw]; ncur = cursor[mincode + gw]; }
+  // Software pipeline over this warp's buckets: while bucket c is sorted, the positions of bucket c+nw and the
+  // bounds of bucket c+2nw are already in flight, so only the text gather of the current bucket is exposed.
+  uint32_t nb0 = 0, ncur = 0, n2b0 = 0, n2cur = 0;
+  uint32_t npos[4] = {0, 0, 0, 0};
+  {
+    const uint64_t c0 = mincode + gw;
+    if (c0 <= maxcode) {
+      nb0 = lb[c0]; ncur = cursor[c0];
+      const uint32_t ncnt = ncur - nb0;
+      if (ncnt >= 2 && ncnt <= SORT_MAXBUCKET) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (e * 32 + lane < ncnt) npos[e] = out.sa[nb0 - out.partoffset + e * 32 + lane];
+      }
+    }
+    if (c0 + nw <= maxcode) { n2b0 = lb[c0 + nw]; n2cur = cursor[c0 + nw]; }
+  }
   for (uint64_t c = mincode + gw; c <= maxcode; c += nw) {
     const uint32_t b0 = nb0;
     const uint32_t cnt = ncur - b0;
-    if (c + nw <= maxcode) { nb0 = lb[c + nw]; ncur = cursor[c + nw]; }   // bounds of the next bucket, in flight early
+    uint32_t pos[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) pos[e] = npos[e];
+    nb0 = n2b0; ncur = n2cur;                      // bucket c+nw: bounds arrived, request its positions
+    if (c + nw <= maxcode) {
+      const uint32_t ncnt = ncur - nb0;
+      if (ncnt >= 2 && ncnt <= SORT_MAXBUCKET) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (e * 32 + lane < ncnt) npos[e] = out.sa[nb0 - out.partoffset + e * 32 + lane];
+      }
+    }
+    if (c + 2 * nw <= maxcode) { n2b0 = lb[c + 2 * nw]; n2cur = cursor[c + 2 * nw]; }
     if (cnt <= 1) continue;
     const uint32_t start = b0 - out.partoffset;
     bool ok = false;
@@ -1069,9 +1101,9 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
         continue;
       }
       ok = false;
-    } else if (cnt <= 32) ok = warp_sort_any<BITS, 1>(T, out, out.sa + start, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
-    else if (cnt <= 64) ok = warp_sort_any<BITS, 2>(T, out, out.sa + start, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
-    else if (cnt <= 128) ok = warp_sort_any<BITS, 4>(T, out, out.sa + start, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
+    } else if (cnt <= 32) ok = warp_sort_any<BITS, 1>(T, out, out.sa + start, pos, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
+    else if (cnt <= 64) ok = warp_sort_any<BITS, 2>(T, out, out.sa + start, pos, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
+    else if (cnt <= 128) ok = warp_sort_any<BITS, 4>(T, out, out.sa + start, pos, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
     if (!ok && lane == 0) {
       const uint64_t rel = c - mincode;
       // cnt <= maxbucket: sorted, only its tie groups are refined; otherwise the whole bucket is

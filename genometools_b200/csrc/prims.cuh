@@ -32,13 +32,15 @@ __device__ __forceinline__ uint32_t block_excl_scan256(uint32_t v, uint32_t *tot
   return woff + x - v;
 }
 
+// rounds: tile = 256 * rounds counters per block (16 for large tables; 2 for small ones, where sixteen
+// dependent block scans per block would leave the GPU idle)
 __global__ void __launch_bounds__(SC_THREADS) k_scan_tilesums(const uint32_t *__restrict__ in, uint64_t n,
-                                                              uint32_t *__restrict__ tilesums) {
+                                                              uint32_t *__restrict__ tilesums, int rounds) {
   __shared__ uint32_t sm[8];
-  const uint64_t base = (uint64_t)blockIdx.x * SC_TILE;
+  const uint64_t base = (uint64_t)blockIdx.x * SC_THREADS * rounds;
   uint32_t s = 0;
 #pragma unroll 4
-  for (int r = 0; r < SC_ROUNDS; ++r) {
+  for (int r = 0; r < rounds; ++r) {
     const uint64_t i = base + (uint64_t)r * SC_THREADS + threadIdx.x;
     if (i < n) s += in[i];
   }
@@ -73,12 +75,12 @@ __global__ void __launch_bounds__(SC_THREADS) k_scan_spine(uint32_t *__restrict_
 // appended as out[n] (the bucket table's last entry).
 __global__ void __launch_bounds__(SC_THREADS) k_scan_apply(const uint32_t *in, uint32_t *out, uint64_t n,
                                                            const uint32_t *__restrict__ tilesums,
-                                                           int append_total) {
+                                                           int append_total, int rounds) {
   __shared__ uint32_t sm[8];
-  const uint64_t base = (uint64_t)blockIdx.x * SC_TILE;
+  const uint64_t base = (uint64_t)blockIdx.x * SC_THREADS * rounds;
   uint32_t carry = tilesums[blockIdx.x];
 #pragma unroll 1
-  for (int r = 0; r < SC_ROUNDS; ++r) {
+  for (int r = 0; r < rounds; ++r) {
     const uint64_t i = base + (uint64_t)r * SC_THREADS + threadIdx.x;
     const uint32_t v = i < n ? in[i] : 0;
     uint32_t tot;

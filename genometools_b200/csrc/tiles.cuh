@@ -291,9 +291,9 @@ __global__ void __launch_bounds__(256) k_tile_sort(Text<BITS> T, PartOut out, co
         uint32_t *src = s_pos + ls;
         const uint8_t *srcL = recL ? s_len + ls : nullptr;
         bool clean = true;                              // sorted and free of ties
-        if (cf <= 32) clean = warp_sort_any<BITS, 1>(T, out, src, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
-        else if (cf <= 64) clean = warp_sort_any<BITS, 2>(T, out, src, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
-        else if (cf <= SORT_MAXBUCKET) clean = warp_sort_any<BITS, 4>(T, out, src, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
+        if (cf <= 32) clean = warp_sort_any<BITS, 1>(T, out, src, nullptr, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
+        else if (cf <= 64) clean = warp_sort_any<BITS, 2>(T, out, src, nullptr, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
+        else if (cf <= SORT_MAXBUCKET) clean = warp_sort_any<BITS, 4>(T, out, src, nullptr, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
         else {                                          // too large for a warp: leave it to the global sorters
           for (uint32_t i = lane; i < cf; i += 32) out.sa[start + i] = src[i];
           done = false;
