@@ -2448,7 +2448,15 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
     uint32_t *gcurF = c->d_bins, *gcur1 = gcurF + nbinsF, *start1 = gcur1 + SP_MAXBINS, *blkfirst = start1 + SP_MAXBINS;
     CK(cudaFuncSetAttribute(k_stage_partition<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SP_SMEM));
     CK(cudaFuncSetAttribute(k_stage_partition<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SP_SMEM));
-    const unsigned textblocks = grid_for(c->n, SP_CHUNK);
+    // blocks of the text-level partition scan reps x 8192 positions when the range covers only 1/reps of the suffixes
+    int reps = 1;
+    if (c->nsort > 0 && rwidth > 0) {
+      const uint64_t ratio = c->nsort / rwidth;
+      reps = ratio >= 8 ? 8 : ratio >= 2 ? (int)ratio : 1;
+    }
+    const unsigned textblocks = grid_for(c->n, (uint64_t)SP_CHUNK * reps);
+    if (reps > 1)
+      CK(cudaFuncSetAttribute(k_stage_partition_sparse<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SP_SMEM_SPARSE));
     // records carry min(real length, 63) in their top 6 bits when the code leaves room for it
     const int recL = (c->numcodes <= (1ull << 26) && c->cp.pl + Text<BITS>::W <= 63) ? 1 : 0;
     {
@@ -2456,14 +2464,22 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
       k_bins_init<<<grid_for(nbinsF, 256), 256, 0, c->stream>>>(c->d_lb, lo, shiftF, nbinsF, out.partoffset, gcurF,
                                                                 nullptr);
       if (!nb1) {
-        k_stage_partition<BITS, true><<<textblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, lo, hi, shiftF, nbinsF,
-                                                                               nullptr, nullptr, nullptr, nullptr, 0, 0, gcurF,
-                                                                               c->d_suf64, recL);
+        if (reps > 1)
+          k_stage_partition_sparse<BITS><<<textblocks, 256, SP_SMEM_SPARSE, c->stream>>>(T, c->cp, c->n, lo, hi, shiftF, nbinsF,
+                                                                                         reps, gcurF, c->d_suf64, recL);
+        else
+          k_stage_partition<BITS, true><<<textblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, lo, hi, shiftF, nbinsF,
+                                                                                 nullptr, nullptr, nullptr, nullptr, 0, 0, gcurF,
+                                                                                 c->d_suf64, recL);
       } else {
         k_bins_init<<<grid_for(nb1, 256), 256, 0, c->stream>>>(c->d_lb, lo, shift1, nb1, out.partoffset, gcur1, start1);
-        k_stage_partition<BITS, true><<<textblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, lo, hi, shift1, nb1,
-                                                                               nullptr, nullptr, nullptr, nullptr, 0, 0, gcur1,
-                                                                               c->d_recB, recL);
+        if (reps > 1)
+          k_stage_partition_sparse<BITS><<<textblocks, 256, SP_SMEM_SPARSE, c->stream>>>(T, c->cp, c->n, lo, hi, shift1, nb1,
+                                                                                         reps, gcur1, c->d_recB, recL);
+        else
+          k_stage_partition<BITS, true><<<textblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, lo, hi, shift1, nb1,
+                                                                                 nullptr, nullptr, nullptr, nullptr, 0, 0, gcur1,
+                                                                                 c->d_recB, recL);
         k_chunk_table<<<1, 256, 0, c->stream>>>(start1, gcur1, nb1, blkfirst);
         const unsigned recblocks = (unsigned)(rwidth / SP_CHUNK + nb1 + 1);
         k_stage_partition<BITS, false><<<recblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, lo, hi, shiftF,

@@ -319,3 +319,93 @@ __global__ void __launch_bounds__(256) k_tile_sort(Text<BITS> T, PartOut out, co
     if (mx) atomicMax(&out.stats->maxdepth, mx);
   }
 }
+
+// ---------------------------------------------------------------------------------------------
+// Sparse variant of the text-level partition: when the part covers only a fraction of the codes
+// (one of P parts, one of N GPUs, one slice of the pipelined fetch) most positions are rejected,
+// and a block of 8192 positions would reserve almost one global range per record.  Here a block
+// scans `reps` x 8192 positions so that it still collects about 8192 records: pass 0 only counts,
+// pass 1 recomputes the codes and takes its local rank from a second shared-memory cursor.  If a
+// block nevertheless collects more than the staging buffer holds, it writes its records straight
+// to their reserved ranges (correct, just not coalesced).
+// dynamic shared memory: stage[SP_CHUNK] u64 | h[SP_MAXBINS] | lstart[SP_MAXBINS] | misc[16] | cur[SP_MAXBINS]
+#define SP_SMEM_SPARSE (SP_SMEM + SP_MAXBINS * 4)
+
+template <int BITS>
+__global__ void __launch_bounds__(256) k_stage_partition_sparse(Text<BITS> T, CodeParams cp, uint64_t n, uint64_t mincode,
+                                                                 uint64_t maxcode, int shift, uint32_t nbins, int reps,
+                                                                 uint32_t *__restrict__ gcursor,
+                                                                 uint64_t *__restrict__ rec_out, int recL) {
+  extern __shared__ __align__(16) unsigned char sp_raw[];
+  uint64_t *stage = (uint64_t *)sp_raw;
+  uint32_t *h = (uint32_t *)(stage + SP_CHUNK);
+  uint32_t *lstart = h + SP_MAXBINS;
+  uint32_t *misc = lstart + SP_MAXBINS;
+  uint32_t *cur = misc + 16;
+  for (uint32_t i = threadIdx.x; i < nbins; i += 256) h[i] = 0;
+  __syncthreads();
+  const uint64_t plmask = (1ull << cp.pl) - 1ull;
+  const uint64_t tbase = ((uint64_t)blockIdx.x * reps) * 256 + threadIdx.x;   // word index of repetition 0
+  for (int rep = 0; rep < reps; ++rep) {
+    const uint64_t t = tbase + (uint64_t)rep * 256;
+    const uint64_t p0 = t << 5;
+    if (p0 >= n) break;
+    const uint64_t mw = T.maskwin(p0);
+    uint64_t hi = 0, lo = 0;
+    if (BITS == 2) { hi = __ldg(T.w + t); lo = __ldg(T.w + t + 1); }
+#pragma unroll 8
+    for (int i = 0; i < 32; ++i) {
+      if (((mw >> i) & plmask) != 0) continue;
+      uint64_t win;
+      if (BITS == 2) win = i ? (hi << (2 * i)) | (lo >> (64 - 2 * i)) : hi;
+      else win = T.window(p0 + i);
+      const uint64_t code = prefix_value<BITS>(win, cp.pl, cp);
+      if (code >= mincode && code <= maxcode) atomicAdd(&h[(uint32_t)((code - mincode) >> shift)], 1u);
+    }
+  }
+  __syncthreads();
+  const uint32_t total = sp_scan_bins(h, lstart, nbins, misc);
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < nbins; i += 256) {
+    const uint32_t cnt = h[i];
+    cur[i] = lstart[i];
+    h[i] = cnt ? atomicAdd(&gcursor[i], cnt) - lstart[i] : 0u;   // global index = h[bin] + local index
+  }
+  __syncthreads();
+  const bool staged = total <= SP_CHUNK;
+  for (int rep = 0; rep < reps; ++rep) {
+    const uint64_t t = tbase + (uint64_t)rep * 256;
+    const uint64_t p0 = t << 5;
+    if (p0 >= n) break;
+    const uint64_t mw = T.maskwin(p0);
+    const uint64_t mw1 = recL ? T.maskwin(p0 + 64) : ~0ull;
+    uint64_t hi = 0, lo = 0;
+    if (BITS == 2) { hi = __ldg(T.w + t); lo = __ldg(T.w + t + 1); }
+#pragma unroll 8
+    for (int i = 0; i < 32; ++i) {
+      if (((mw >> i) & plmask) != 0) continue;
+      uint64_t win;
+      if (BITS == 2) win = i ? (hi << (2 * i)) | (lo >> (64 - 2 * i)) : hi;
+      else win = T.window(p0 + i);
+      const uint64_t code = prefix_value<BITS>(win, cp.pl, cp);
+      if (code < mincode || code > maxcode) continue;
+      const uint32_t bin = (uint32_t)((code - mincode) >> shift);
+      uint64_t rec = (code << 32) | (uint64_t)(uint32_t)(p0 + i);
+      if (recL) {
+        const uint64_t m = i ? (mw >> i) | (mw1 << (64 - i)) : mw;
+        const unsigned L = m ? (unsigned)(__ffsll((long long)m) - 1) : 63u;
+        rec |= (uint64_t)(L < 63u ? L : 63u) << 58;
+      }
+      const uint32_t r = atomicAdd(&cur[bin], 1u);
+      if (staged) stage[r] = rec;
+      else __stcs(rec_out + h[bin] + r, rec);
+    }
+  }
+  if (!staged) return;
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < total; i += 256) {
+    const uint64_t r = stage[i];
+    const uint32_t bin = (uint32_t)((rec_code(r, recL) - mincode) >> shift);
+    __stcs(rec_out + h[bin] + i, r);
+  }
+}
