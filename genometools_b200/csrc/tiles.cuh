@@ -331,6 +331,23 @@ __global__ void __launch_bounds__(256) k_tile_sort(Text<BITS> T, PartOut out, co
 // dynamic shared memory: stage[SP_CHUNK] u64 | h[SP_MAXBINS] | lstart[SP_MAXBINS] | misc[16] | cur[SP_MAXBINS]
 #define SP_SMEM_SPARSE (SP_SMEM + SP_MAXBINS * 4)
 
+// bit i of the result = position p0+i starts a regular suffix whose code lies in [mincode,maxcode]
+template <int BITS>
+__device__ __forceinline__ uint32_t sp_select(const Text<BITS> &T, const CodeParams &cp, uint64_t p0, uint64_t mw,
+                                              uint64_t hi, uint64_t lo, uint64_t plmask, uint64_t mincode, uint64_t maxcode) {
+  uint32_t sel = 0;
+#pragma unroll 8
+  for (int i = 0; i < 32; ++i) {
+    if (((mw >> i) & plmask) != 0) continue;
+    uint64_t win;
+    if (BITS == 2) win = i ? (hi << (2 * i)) | (lo >> (64 - 2 * i)) : hi;
+    else win = T.window(p0 + i);
+    const uint64_t code = prefix_value<BITS>(win, cp.pl, cp);
+    if (code >= mincode && code <= maxcode) sel |= 1u << i;
+  }
+  return sel;
+}
+
 template <int BITS>
 __global__ void __launch_bounds__(256) k_stage_partition_sparse(Text<BITS> T, CodeParams cp, uint64_t n, uint64_t mincode,
                                                                  uint64_t maxcode, int shift, uint32_t nbins, int reps,
@@ -346,21 +363,30 @@ __global__ void __launch_bounds__(256) k_stage_partition_sparse(Text<BITS> T, Co
   __syncthreads();
   const uint64_t plmask = (1ull << cp.pl) - 1ull;
   const uint64_t tbase = ((uint64_t)blockIdx.x * reps) * 256 + threadIdx.x;   // word index of repetition 0
-  for (int rep = 0; rep < reps; ++rep) {
-    const uint64_t t = tbase + (uint64_t)rep * 256;
-    const uint64_t p0 = t << 5;
-    if (p0 >= n) break;
-    const uint64_t mw = T.maskwin(p0);
-    uint64_t hi = 0, lo = 0;
-    if (BITS == 2) { hi = __ldg(T.w + t); lo = __ldg(T.w + t + 1); }
-#pragma unroll 8
-    for (int i = 0; i < 32; ++i) {
-      if (((mw >> i) & plmask) != 0) continue;
-      uint64_t win;
-      if (BITS == 2) win = i ? (hi << (2 * i)) | (lo >> (64 - 2 * i)) : hi;
-      else win = T.window(p0 + i);
-      const uint64_t code = prefix_value<BITS>(win, cp.pl, cp);
-      if (code >= mincode && code <= maxcode) atomicAdd(&h[(uint32_t)((code - mincode) >> shift)], 1u);
+  uint32_t selbits[8];                       // per repetition: which of the thread's 32 positions are in range
+#pragma unroll
+  for (int rep = 0; rep < 8; ++rep) {
+    selbits[rep] = 0;
+    if (rep < reps) {
+      const uint64_t t = tbase + (uint64_t)rep * 256;
+      const uint64_t p0 = t << 5;
+      if (p0 < n) {
+        const uint64_t mw = T.maskwin(p0);
+        uint64_t hi = 0, lo = 0;
+        if (BITS == 2) { hi = __ldg(T.w + t); lo = __ldg(T.w + t + 1); }
+        uint32_t sel = sp_select<BITS>(T, cp, p0, mw, hi, lo, plmask, mincode, maxcode);
+        selbits[rep] = sel;
+        // only the selected positions (about 32/reps of them) reach the shared-memory atomics
+        while (sel) {
+          const int i = __ffs(sel) - 1;
+          sel &= sel - 1;
+          uint64_t win;
+          if (BITS == 2) win = i ? (hi << (2 * i)) | (lo >> (64 - 2 * i)) : hi;
+          else win = T.window(p0 + i);
+          const uint64_t code = prefix_value<BITS>(win, cp.pl, cp);
+          atomicAdd(&h[(uint32_t)((code - mincode) >> shift)], 1u);
+        }
+      }
     }
   }
   __syncthreads();
@@ -373,32 +399,34 @@ __global__ void __launch_bounds__(256) k_stage_partition_sparse(Text<BITS> T, Co
   }
   __syncthreads();
   const bool staged = total <= SP_CHUNK;
-  for (int rep = 0; rep < reps; ++rep) {
-    const uint64_t t = tbase + (uint64_t)rep * 256;
-    const uint64_t p0 = t << 5;
-    if (p0 >= n) break;
-    const uint64_t mw = T.maskwin(p0);
-    const uint64_t mw1 = recL ? T.maskwin(p0 + 64) : ~0ull;
-    uint64_t hi = 0, lo = 0;
-    if (BITS == 2) { hi = __ldg(T.w + t); lo = __ldg(T.w + t + 1); }
-#pragma unroll 8
-    for (int i = 0; i < 32; ++i) {
-      if (((mw >> i) & plmask) != 0) continue;
-      uint64_t win;
-      if (BITS == 2) win = i ? (hi << (2 * i)) | (lo >> (64 - 2 * i)) : hi;
-      else win = T.window(p0 + i);
-      const uint64_t code = prefix_value<BITS>(win, cp.pl, cp);
-      if (code < mincode || code > maxcode) continue;
-      const uint32_t bin = (uint32_t)((code - mincode) >> shift);
-      uint64_t rec = (code << 32) | (uint64_t)(uint32_t)(p0 + i);
-      if (recL) {
-        const uint64_t m = i ? (mw >> i) | (mw1 << (64 - i)) : mw;
-        const unsigned L = m ? (unsigned)(__ffsll((long long)m) - 1) : 63u;
-        rec |= (uint64_t)(L < 63u ? L : 63u) << 58;
+#pragma unroll
+  for (int rep = 0; rep < 8; ++rep) {
+    uint32_t sel = selbits[rep];
+    if (sel) {
+      const uint64_t t = tbase + (uint64_t)rep * 256;
+      const uint64_t p0 = t << 5;
+      const uint64_t mw = T.maskwin(p0);
+      const uint64_t mw1 = recL ? T.maskwin(p0 + 64) : ~0ull;
+      uint64_t hi = 0, lo = 0;
+      if (BITS == 2) { hi = __ldg(T.w + t); lo = __ldg(T.w + t + 1); }
+      while (sel) {
+        const int i = __ffs(sel) - 1;
+        sel &= sel - 1;
+        uint64_t win;
+        if (BITS == 2) win = i ? (hi << (2 * i)) | (lo >> (64 - 2 * i)) : hi;
+        else win = T.window(p0 + i);
+        const uint64_t code = prefix_value<BITS>(win, cp.pl, cp);
+        const uint32_t bin = (uint32_t)((code - mincode) >> shift);
+        uint64_t rec = (code << 32) | (uint64_t)(uint32_t)(p0 + i);
+        if (recL) {
+          const uint64_t m = i ? (mw >> i) | (mw1 << (64 - i)) : mw;
+          const unsigned L = m ? (unsigned)(__ffsll((long long)m) - 1) : 63u;
+          rec |= (uint64_t)(L < 63u ? L : 63u) << 58;
+        }
+        const uint32_t r = atomicAdd(&cur[bin], 1u);
+        if (staged) stage[r] = rec;
+        else __stcs(rec_out + h[bin] + r, rec);
       }
-      const uint32_t r = atomicAdd(&cur[bin], 1u);
-      if (staged) stage[r] = rec;
-      else __stcs(rec_out + h[bin] + r, rec);
     }
   }
   if (!staged) return;
