@@ -881,8 +881,9 @@ struct WarpSorter {
 // LCP.  Returns false (nothing written) if two suffixes agree on all pl+W symbols.
 template <int BITS, int E>
 __device__ __forceinline__ bool warp_sort_bucket(const Text<BITS> &T, const PartOut &out, const uint32_t *src,
-                                                 const uint32_t *pre, const uint8_t *srcL, uint32_t start, uint32_t cnt,
-                                                 unsigned pl, int lane, unsigned long long &sum, uint32_t &mx) {
+                                                 const uint32_t *pre, const uint8_t *srcL, const uint64_t *pkeys,
+                                                 uint32_t start, uint32_t cnt, unsigned pl, int lane,
+                                                 unsigned long long &sum, uint32_t &mx) {
   uint64_t k[E];
   uint32_t v[E];
 #pragma unroll
@@ -890,8 +891,9 @@ __device__ __forceinline__ bool warp_sort_bucket(const Text<BITS> &T, const Part
     const uint32_t i = e * 32 + lane;
     if (i < cnt) {
       v[e] = pre ? pre[e] : src[i];
-      k[e] = srcL ? make_key_known<BITS>(T, (uint64_t)v[e] + pl, (unsigned)srcL[i] - pl)
-                  : make_key<BITS>(T, (uint64_t)v[e] + pl);
+      k[e] = pkeys ? pkeys[i]
+                   : srcL ? make_key_known<BITS>(T, (uint64_t)v[e] + pl, (unsigned)srcL[i] - pl)
+                          : make_key<BITS>(T, (uint64_t)v[e] + pl);
     } else {
       v[e] = 0xffffffffu;
       k[e] = ~0ull;
@@ -975,25 +977,32 @@ struct WarpSorter32 {
 // Returns 0 = done, 1 = redo with warp_sort_bucket.
 template <int BITS, int E>
 __device__ __forceinline__ int warp_sort_bucket32(const Text<BITS> &T, const PartOut &out, const uint32_t *src,
-                                                  const uint32_t *pre, const uint8_t *srcL, uint32_t start, uint32_t cnt,
-                                                  unsigned pl, int lane, uint64_t *skey, uint32_t *spos,
-                                                  unsigned long long &sum, uint32_t &mx) {
+                                                  const uint32_t *pre, const uint8_t *srcL, const uint64_t *pkeys,
+                                                  uint32_t start, uint32_t cnt, unsigned pl, int lane, uint64_t *skey_w,
+                                                  uint32_t *spos_w, unsigned long long &sum, uint32_t &mx) {
+  // pkeys: the bucket's full keys are already in shared memory next to its positions (src); nothing is staged
+  const uint64_t *skey = pkeys ? pkeys : skey_w;
+  const uint32_t *spos = pkeys ? src : spos_w;
   uint32_t k[E];
-  __syncwarp();
+  if (!pkeys) __syncwarp();
 #pragma unroll
   for (int e = 0; e < E; ++e) {
     const uint32_t i = e * 32 + lane;
     k[e] = 0xffffffffu;
     if (i < cnt) {
-      const uint32_t p = pre ? pre[e] : src[i];
-      const uint64_t fk = srcL ? make_key_known<BITS>(T, (uint64_t)p + pl, (unsigned)srcL[i] - pl)
-                               : make_key<BITS>(T, (uint64_t)p + pl);
-      skey[i] = fk;
-      spos[i] = p;
+      uint64_t fk;
+      if (pkeys) fk = pkeys[i];
+      else {
+        const uint32_t p = pre ? pre[e] : src[i];
+        fk = srcL ? make_key_known<BITS>(T, (uint64_t)p + pl, (unsigned)srcL[i] - pl)
+                  : make_key<BITS>(T, (uint64_t)p + pl);
+        skey_w[i] = fk;
+        spos_w[i] = p;
+      }
       k[e] = ((uint32_t)(fk >> 40) << 8) | i;
     }
   }
-  __syncwarp();
+  if (!pkeys) __syncwarp();
   WarpSorter32<E>::sort(k, lane);
   uint64_t fk[E];
   uint32_t l[E];
@@ -1033,14 +1042,15 @@ __device__ __forceinline__ int warp_sort_bucket32(const Text<BITS> &T, const Par
 
 template <int BITS, int E>
 __device__ __forceinline__ bool warp_sort_any(const Text<BITS> &T, const PartOut &out, const uint32_t *src,
-                                              const uint32_t *pre, const uint8_t *srcL, uint32_t start, uint32_t cnt,
-                                              unsigned pl, int lane, uint64_t *skey, uint32_t *spos,
-                                              unsigned long long &sum, uint32_t &mx) {
+                                              const uint32_t *pre, const uint8_t *srcL, const uint64_t *pkeys,
+                                              uint32_t start, uint32_t cnt, unsigned pl, int lane, uint64_t *skey,
+                                              uint32_t *spos, unsigned long long &sum, uint32_t &mx) {
   // pre: the bucket's positions already in registers (element e*32+lane in pre[e]), loaded one bucket ahead
+  // pkeys: the bucket's keys already in shared memory (element i in pkeys[i], its position in src[i])
   if (BITS == 2) {
-    if (warp_sort_bucket32<BITS, E>(T, out, src, pre, srcL, start, cnt, pl, lane, skey, spos, sum, mx) == 0) return true;
+    if (warp_sort_bucket32<BITS, E>(T, out, src, pre, srcL, pkeys, start, cnt, pl, lane, skey, spos, sum, mx) == 0) return true;
   }
-  return warp_sort_bucket<BITS, E>(T, out, src, pre, srcL, start, cnt, pl, lane, sum, mx);
+  return warp_sort_bucket<BITS, E>(T, out, src, pre, srcL, pkeys, start, cnt, pl, lane, sum, mx);
 }
 
 template <int BITS>
@@ -1101,9 +1111,9 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
         continue;
       }
       ok = false;
-    } else if (cnt <= 32) ok = warp_sort_any<BITS, 1>(T, out, out.sa + start, pos, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
-    else if (cnt <= 64) ok = warp_sort_any<BITS, 2>(T, out, out.sa + start, pos, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
-    else if (cnt <= 128) ok = warp_sort_any<BITS, 4>(T, out, out.sa + start, pos, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
+    } else if (cnt <= 32) ok = warp_sort_any<BITS, 1>(T, out, out.sa + start, pos, nullptr, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
+    else if (cnt <= 64) ok = warp_sort_any<BITS, 2>(T, out, out.sa + start, pos, nullptr, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
+    else if (cnt <= 128) ok = warp_sort_any<BITS, 4>(T, out, out.sa + start, pos, nullptr, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
     if (!ok && lane == 0) {
       const uint64_t rel = c - mincode;
       // cnt <= maxbucket: sorted, only its tie groups are refined; otherwise the whole bucket is
@@ -2489,8 +2499,9 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
     }
     {
       ProfScope ps(c, KC_SORT);
-      const unsigned tb = nbinsF < 148u * 5 ? nbinsF : 148u * 5;
-      k_tile_sort<BITS><<<tb, 256, 0, c->stream>>>(T, out, c->d_lb, c->d_cursor, c->d_suf64, gcurF, lo, hi, shiftF,
+      const unsigned tb = nbinsF < 148u * 2 ? nbinsF : 148u * 2;     // two 512-thread blocks per SM, tiles dealt round-robin
+      CK(cudaFuncSetAttribute(k_tile_sort<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM));
+      k_tile_sort<BITS><<<tb, TS_THREADS, TS_SMEM, c->stream>>>(T, out, c->d_lb, c->d_cursor, c->d_suf64, gcurF, lo, hi, shiftF,
                                                    nbinsF, c->cp.pl, recL, fbb, fbwords);
     }
     CK(cudaGetLastError());

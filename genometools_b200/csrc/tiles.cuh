@@ -230,18 +230,23 @@ __global__ void __launch_bounds__(256) k_chunk_table(const uint32_t *__restrict_
 // ---------------------------------------------------------------------------------------------
 #define TILE_CAP 6144          // suffix-array slots (regular + special-padded) a tile may span
 #define TILE_MAXCODES 1024     // buckets per tile
+#define TS_THREADS 512
+#define TS_WARPS (TS_THREADS / 32)
+#define TS_BATCH 4             // records per thread in flight while their text windows are gathered
+// dynamic shared memory: key[TILE_CAP] u64 | pos[TILE_CAP] u32 | lb[TILE_MAXCODES+1] | cur[TILE_MAXCODES]
+#define TS_SMEM (TILE_CAP * 12 + (2 * TILE_MAXCODES + 1) * 4)
 
 template <int BITS>
-__global__ void __launch_bounds__(256) k_tile_sort(Text<BITS> T, PartOut out, const uint32_t *__restrict__ lb,
-                                                   uint32_t *__restrict__ cursor, const uint64_t *__restrict__ rec,
-                                                   const uint32_t *__restrict__ gcursor, uint64_t mincode,
-                                                   uint64_t maxcode, int shift, uint32_t nbins, unsigned pl, int recL,
-                                                   uint32_t *__restrict__ fbbits, uint64_t tieoff) {
-  __shared__ uint8_t s_len[TILE_CAP];
-  __shared__ uint32_t s_lb[TILE_MAXCODES + 1];
-  __shared__ uint32_t s_cur[TILE_MAXCODES];
-  __shared__ uint32_t s_pos[TILE_CAP];
-  __shared__ uint64_t s_key[8][SORT_MAXBUCKET];
+__global__ void __launch_bounds__(TS_THREADS, 2) k_tile_sort(Text<BITS> T, PartOut out, const uint32_t *__restrict__ lb,
+                                                             uint32_t *__restrict__ cursor, const uint64_t *__restrict__ rec,
+                                                             const uint32_t *__restrict__ gcursor, uint64_t mincode,
+                                                             uint64_t maxcode, int shift, uint32_t nbins, unsigned pl, int recL,
+                                                             uint32_t *__restrict__ fbbits, uint64_t tieoff) {
+  extern __shared__ __align__(16) unsigned char ts_raw[];
+  uint64_t *s_key = (uint64_t *)ts_raw;
+  uint32_t *s_pos = (uint32_t *)(s_key + TILE_CAP);
+  uint32_t *s_lb = s_pos + TILE_CAP;
+  uint32_t *s_cur = s_lb + TILE_MAXCODES + 1;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   unsigned long long sum = 0;
   uint32_t mx = 0;
@@ -255,7 +260,7 @@ __global__ void __launch_bounds__(256) k_tile_sort(Text<BITS> T, PartOut out, co
     const uint32_t rs = base - out.partoffset;          // part-local; also the tile's first record
     const uint32_t cnt = gcursor[g] - rs;
     __syncthreads();                                    // previous tile fully consumed
-    for (uint32_t i = threadIdx.x; i <= ncf; i += 256) {
+    for (uint32_t i = threadIdx.x; i <= ncf; i += TS_THREADS) {
       const uint32_t v = lb[c0 + i] - base;
       s_lb[i] = v;
       if (i < ncf) s_cur[i] = v;
@@ -263,24 +268,47 @@ __global__ void __launch_bounds__(256) k_tile_sort(Text<BITS> T, PartOut out, co
     __syncthreads();
     if (slots > TILE_CAP) {
       // too many suffixes for shared memory: plain insertion, the global kernels sort these buckets
-      for (uint32_t i = threadIdx.x; i < cnt; i += 256) {
+      for (uint32_t i = threadIdx.x; i < cnt; i += TS_THREADS) {
         const uint64_t r = __ldcs(rec + rs + i);
         const uint32_t slot = atomicAdd(&s_cur[(uint32_t)(rec_code(r, recL) - c0)], 1u);
         out.sa[rs + slot] = (uint32_t)r;
       }
       __syncthreads();
-      for (uint32_t i = threadIdx.x; i < ncf; i += 256) cursor[c0 + i] = base + s_cur[i];
+      for (uint32_t i = threadIdx.x; i < ncf; i += TS_THREADS) cursor[c0 + i] = base + s_cur[i];
       if (threadIdx.x == 0) atomicAdd(&out.stats->tile_leftover, 1u);
       continue;
     }
-    for (uint32_t i = threadIdx.x; i < cnt; i += 256) {
-      const uint64_t r = __ldcs(rec + rs + i);
-      const uint32_t slot = atomicAdd(&s_cur[(uint32_t)(rec_code(r, recL) - c0)], 1u);
-      s_pos[slot] = (uint32_t)r;
-      s_len[slot] = (uint8_t)(r >> 58);
+    // Insertion and key gather in one sweep: every thread keeps TS_BATCH records in flight, so the text windows
+    // of the whole tile are fetched with full memory-level parallelism; the warp sorters below read only
+    // shared memory.
+    for (uint32_t i0 = threadIdx.x; i0 < cnt; i0 += TS_THREADS * TS_BATCH) {
+      uint64_t r[TS_BATCH], key[TS_BATCH];
+#pragma unroll
+      for (int u = 0; u < TS_BATCH; ++u) {
+        const uint32_t i = i0 + u * TS_THREADS;
+        r[u] = i < cnt ? __ldcs(rec + rs + i) : 0ull;
+      }
+#pragma unroll
+      for (int u = 0; u < TS_BATCH; ++u) {
+        const uint32_t i = i0 + u * TS_THREADS;
+        key[u] = 0;
+        if (i < cnt) {
+          const uint64_t q = (uint64_t)(uint32_t)r[u] + pl;
+          key[u] = recL ? make_key_known<BITS>(T, q, (unsigned)(r[u] >> 58) - pl) : make_key<BITS>(T, q);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < TS_BATCH; ++u) {
+        const uint32_t i = i0 + u * TS_THREADS;
+        if (i < cnt) {
+          const uint32_t slot = atomicAdd(&s_cur[(uint32_t)(rec_code(r[u], recL) - c0)], 1u);
+          s_pos[slot] = (uint32_t)r[u];
+          s_key[slot] = key[u];
+        }
+      }
     }
     __syncthreads();
-    for (uint32_t f = wid; f < ncf; f += 8) {
+    for (uint32_t f = wid; f < ncf; f += TS_WARPS) {
       const uint32_t ls = s_lb[f];
       const uint32_t cf = s_cur[f] - ls;                // regular suffixes of bucket c0+f
       const uint32_t start = rs + ls;
@@ -288,12 +316,12 @@ __global__ void __launch_bounds__(256) k_tile_sort(Text<BITS> T, PartOut out, co
       if (cf == 1) {
         if (lane == 0) out.sa[start] = s_pos[ls];
       } else if (cf > 1) {
-        uint32_t *src = s_pos + ls;
-        const uint8_t *srcL = recL ? s_len + ls : nullptr;
+        const uint32_t *src = s_pos + ls;
+        const uint64_t *keys = s_key + ls;
         bool clean = true;                              // sorted and free of ties
-        if (cf <= 32) clean = warp_sort_any<BITS, 1>(T, out, src, nullptr, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
-        else if (cf <= 64) clean = warp_sort_any<BITS, 2>(T, out, src, nullptr, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
-        else if (cf <= SORT_MAXBUCKET) clean = warp_sort_any<BITS, 4>(T, out, src, nullptr, srcL, start, cf, pl, lane, s_key[wid], src, sum, mx);
+        if (cf <= 32) clean = warp_sort_any<BITS, 1>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else if (cf <= 64) clean = warp_sort_any<BITS, 2>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else if (cf <= SORT_MAXBUCKET) clean = warp_sort_any<BITS, 4>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
         else {                                          // too large for a warp: leave it to the global sorters
           for (uint32_t i = lane; i < cf; i += 32) out.sa[start + i] = src[i];
           done = false;
