@@ -132,6 +132,9 @@ struct gtb200_ctx {
   // scratch
   uint32_t *d_tilesums;
   uint64_t cap_tilesums;
+  unsigned long long *d_scanstate;   // look-back words of the single-pass scan, [cap_scanstate] + ticket word
+  uint64_t cap_scanstate;
+  uint64_t scan_epoch;
   void *d_scratch;
   size_t cap_scratch;
   std::vector<PoolBlock> blocks;   // every device allocation of this context
@@ -303,21 +306,38 @@ static int ensure_tilesums(gtb200_ctx *c, uint64_t ntiles) {
   return 0;
 }
 
-// exclusive scan on the context's stream; total (64-bit) lands in *d_total if non-null
+// exclusive scan on the context's stream (one launch); total (64-bit) lands in *d_total if non-null,
+// max(in[]) is folded into *d_max (atomicMax, caller zeroes it) if non-null
 static int device_scan(gtb200_ctx *c, const uint32_t *in, uint32_t *out, uint64_t n, int append_total,
-                       unsigned long long *d_total, int cls = KC_SCAN) {
+                       unsigned long long *d_total, int cls = KC_SCAN, unsigned int *d_max = nullptr) {
   if (n == 0) {
     if (d_total) CK(cudaMemsetAsync(d_total, 0, sizeof *d_total, c->stream));
     return 0;
   }
-  const int rounds = n <= (1u << 21) ? 2 : SC_ROUNDS;
-  const uint64_t tile = (uint64_t)SC_THREADS * rounds;
+  const int R = n <= (1u << 21) ? 2 : 16;
+  const uint64_t tile = (uint64_t)SC_THREADS * R;
   const uint64_t ntiles = (n + tile - 1) / tile;
-  if (ensure_tilesums(c, ntiles)) return -1;
-  ProfScope ps(c, cls, 3);
-  k_scan_tilesums<<<(unsigned)ntiles, SC_THREADS, 0, c->stream>>>(in, n, c->d_tilesums, rounds);
-  k_scan_spine<<<1, SC_THREADS, 0, c->stream>>>(c->d_tilesums, (uint32_t)ntiles, d_total);
-  k_scan_apply<<<(unsigned)ntiles, SC_THREADS, 0, c->stream>>>(in, out, n, c->d_tilesums, append_total, rounds);
+  if (ntiles > c->cap_scanstate || c->scan_epoch >= (1ull << 30) - 1) {
+    if (ntiles > c->cap_scanstate) {
+      dfree(c, c->d_scanstate);
+      c->d_scanstate = nullptr;
+      c->cap_scanstate = 0;
+      const uint64_t cap = ntiles < 1024 ? 1024 : ntiles;
+      CK(dmalloc(c, &c->d_scanstate, (cap + 1) * 8));
+      c->cap_scanstate = cap;
+    }
+    CK(cudaMemsetAsync(c->d_scanstate, 0, (c->cap_scanstate + 1) * 8, c->stream));   // epoch 0 = never ready
+    c->scan_epoch = 0;
+  }
+  const uint64_t epoch = ++c->scan_epoch;
+  unsigned int *ticket = (unsigned int *)(c->d_scanstate + c->cap_scanstate);
+  ProfScope ps(c, cls, 1);
+  if (R == 2)
+    k_scan_onepass<2><<<(unsigned)ntiles, SC_THREADS, 0, c->stream>>>(in, out, n, (uint32_t)ntiles, c->d_scanstate, ticket, epoch,
+                                                                    append_total, d_total, d_max);
+  else
+    k_scan_onepass<16><<<(unsigned)ntiles, SC_THREADS, 0, c->stream>>>(in, out, n, (uint32_t)ntiles, c->d_scanstate, ticket, epoch,
+                                                                     append_total, d_total, d_max);
   CK(cudaGetLastError());
   return 0;
 }
@@ -770,14 +790,6 @@ __global__ void __launch_bounds__(256) k_padded_small(Text<BITS> T, CodeParams c
   if (threadIdx.x == 0) *npadded = total;
 }
 
-__global__ void k_max_u32(const uint32_t *__restrict__ a, uint64_t n, unsigned int *out) {
-  uint32_t m = 0;
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
-    m = max(m, a[i]);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(GTB_FULL, m, o));
-  if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
-}
 
 __global__ void k_sum_u32(const uint32_t *__restrict__ a, uint64_t n, unsigned long long *out) {
   unsigned long long s = 0;
@@ -1988,22 +2000,21 @@ static int count_impl(gtb200_ctx *c, bool need_host_values, uint64_t pos_lo, uin
   const uint64_t tablewords = (c->numcodes + 2) + (c->numspecialcodes + 1) + (c->numdist + 1);
   if (!c->d_lb) {                            // first call: allocate the tables once, contiguously
     c->padcap = nr1 * (c->cp.pl - 1) + 1;
-    CK(dmalloc(c, &c->d_lb, tablewords * 4));
+    // the tables and the 64-byte block of persistent counters share one allocation: one memset clears both
+    CK(dmalloc(c, &c->d_lb, (tablewords + (tablewords & 1)) * 4 + 64));
+    c->d_persist = (unsigned long long *)(c->d_lb + tablewords + (tablewords & 1));
     c->d_csc = c->d_lb + (c->numcodes + 2);
     c->d_dist = c->d_csc + (c->numspecialcodes + 1);
     CK(dmalloc(c, &c->d_cursor, (c->numcodes + 2) * 4));
     CK(dmalloc(c, &c->d_padcnt, (nr1 + 1) * 4));
     CK(dmalloc(c, &c->d_padkey, c->padcap * 8));
     CK(dmalloc(c, &c->d_padpos, c->padcap * 4));
-    CK(dmalloc(c, &c->d_persist, 64));
   }
   const bool small = nr1 <= PADSMALL_CAP && c->padcap <= PADSMALL_CAP;
   uint32_t *cntoff = c->d_padcnt;
   uint32_t *hist_or_null = padded_counts ? c->d_lb : nullptr;
   if (phase != 2) {
-  CK(cudaMemsetAsync(c->d_persist, 0, 64, c->stream));
-  CK(cudaMemsetAsync(c->d_lb, 0, tablewords * 4, c->stream));
-  CK(cudaMemsetAsync(c->d_stats, 0, sizeof(PartStats), c->stream));
+  CK(cudaMemsetAsync(c->d_lb, 0, (tablewords + (tablewords & 1)) * 4 + 64, c->stream));   // tables + persistent counters
   if (pos_hi > pos_lo) {
     // A table larger than L2 is filled slice by slice (64 MB of counters per pass over the text), so
     // that the RED.ADDs always hit L2-resident lines; the text scan itself is cheap (n/4 bytes).
@@ -2042,11 +2053,8 @@ static int count_impl(gtb200_ctx *c, bool need_host_values, uint64_t pos_lo, uin
     CK(cudaGetLastError());
     return 0;
   }
-  {
-    ProfScope ps(c, KC_COUNT);
-    k_max_u32<<<592, 256, 0, c->stream>>>(c->d_lb, c->numcodes, (unsigned int *)(c->d_persist + 1));
-  }
-  if (device_scan(c, c->d_lb, c->d_lb, c->numcodes, 1, c->d_persist + 2)) return -1;
+  // prefix sum of the bucket counts; the largest bucket is reduced in the same launch
+  if (device_scan(c, c->d_lb, c->d_lb, c->numcodes, 1, c->d_persist + 2, KC_SCAN, (unsigned int *)(c->d_persist + 1))) return -1;
   c->counted = true;
   if (small && !need_host_values) {           // nothing the host needs: stay asynchronous
     CK(cudaGetLastError());
@@ -2417,7 +2425,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
   const uint64_t rcodes = hi - lo + 1;
   uint32_t *fbb = c->d_fbbits + ((lo - pmin) >> 5);
   if (rwidth == 0) return 0;
-  {
+  if (!first_of_part) {                       // k_part_init zeroed the statistics for the first range
     ProfScope ps(c, KC_SORT);
     k_reset_medcount<<<1, 1, 0, c->stream>>>(c->d_stats);
   }
@@ -2757,8 +2765,10 @@ extern "C" int gtb200_tail(gtb200_ctx *c, uint64_t first, uint64_t count, void *
                                                                    c->n, first, count, (uint64_t *)c->d_scratch);
   }
   CK(cudaGetLastError());
-  if (suftab) CK(cudaMemcpyAsync(suftab, c->d_scratch, count * esz, cudaMemcpyDeviceToHost, c->stream));
-  CK(cudaStreamSynchronize(c->stream));
+  if (suftab) {                               // without a host buffer the call stays stream-ordered (device consumers)
+    CK(cudaMemcpyAsync(suftab, c->d_scratch, count * esz, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+  }
   return 0;
 }
 

@@ -1,12 +1,10 @@
-// Hand-written device-wide primitives: exclusive scan over uint32 and a stable LSD radix sort of
-// (uint64 key, uint32 value) pairs.  Both are three-kernel reduce/scan/apply designs; they serve the
-// bucket-table prefix sum and the refinement path, neither of which is the dominant kernel.
+// Hand-written device-wide primitives: a single-pass (decoupled look-back) exclusive scan over uint32 and a
+// stable LSD radix sort of (uint64 key, uint32 value) pairs (histogram / scan / scatter per 8-bit digit).  They
+// serve the bucket-table prefix sum and the refinement path, neither of which is the dominant kernel.
 #pragma once
 #include "common.cuh"
 
 #define SC_THREADS 256
-#define SC_ROUNDS 16
-#define SC_TILE (SC_THREADS * SC_ROUNDS)
 
 // exclusive scan of one value per thread across a 256-thread block; *total = block sum.
 // sm must hold 8 words; contains two __syncthreads, safe to call repeatedly.
@@ -32,62 +30,123 @@ __device__ __forceinline__ uint32_t block_excl_scan256(uint32_t v, uint32_t *tot
   return woff + x - v;
 }
 
-// rounds: tile = 256 * rounds counters per block (16 for large tables; 2 for small ones, where sixteen
-// dependent block scans per block would leave the GPU idle)
-__global__ void __launch_bounds__(SC_THREADS) k_scan_tilesums(const uint32_t *__restrict__ in, uint64_t n,
-                                                              uint32_t *__restrict__ tilesums, int rounds) {
+// ---------------------------------------------------------------------------------------------
+// Single-pass exclusive scan (decoupled look-back): one launch instead of three.  Every block takes a
+// ticket (tiles are therefore processed in dispatch order and a block only ever waits for blocks that
+// already run), scans its 256*R values, publishes its aggregate, and warp 0 walks back over the
+// predecessors' published words until it meets an inclusive prefix.
+//   state word = epoch << 34 | flag << 32 | value;  flag 1 = tile aggregate, 2 = inclusive prefix.
+// The epoch changes with every launch, so words of earlier scans read as "not ready" and the array
+// never has to be cleared; the last ticket holder rewinds the ticket counter.
+// Optionally also reduces max(in[]) into *maxout (atomicMax; caller zeroes it).
+// ---------------------------------------------------------------------------------------------
+#define SCAN_FLAG_AGG 1ull
+#define SCAN_FLAG_PFX 2ull
+
+template <int R>
+__global__ void __launch_bounds__(SC_THREADS) k_scan_onepass(const uint32_t *in, uint32_t *out, uint64_t n, uint32_t ntiles,
+                                                             unsigned long long *__restrict__ state,
+                                                             unsigned int *__restrict__ ticket, uint64_t epoch,
+                                                             int append_total, unsigned long long *__restrict__ total_out,
+                                                             unsigned int *__restrict__ maxout) {
   __shared__ uint32_t sm[8];
-  const uint64_t base = (uint64_t)blockIdx.x * SC_THREADS * rounds;
-  uint32_t s = 0;
-#pragma unroll 4
-  for (int r = 0; r < rounds; ++r) {
-    const uint64_t i = base + (uint64_t)r * SC_THREADS + threadIdx.x;
-    if (i < n) s += in[i];
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(GTB_FULL, s, o);
-  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = s;
+  __shared__ uint32_t s_tile, s_excl;
+  if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
   __syncthreads();
-  if (threadIdx.x == 0) {
-    uint32_t t = 0;
-    for (int k = 0; k < 8; ++k) t += sm[k];
-    tilesums[blockIdx.x] = t;
+  const uint32_t tile = s_tile;
+  const uint64_t base = (uint64_t)tile * (SC_THREADS * R) + (uint64_t)threadIdx.x * R;
+  uint32_t v[R];
+  if (base + R <= n) {
+    if (R % 4 == 0 && (((uintptr_t)in) & 15) == 0) {
+#pragma unroll
+      for (int j = 0; j < R; j += 4) {
+        const uint4 q = *reinterpret_cast<const uint4 *>(in + base + j);
+        v[j] = q.x; v[j + 1] = q.y; v[j + 2] = q.z; v[j + 3] = q.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < R; ++j) v[j] = in[base + j];
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < R; ++j) v[j] = base + j < n ? in[base + j] : 0u;
   }
-}
-
-// single block: in-place exclusive scan of the tile sums, total written to *total_out (64-bit)
-__global__ void __launch_bounds__(SC_THREADS) k_scan_spine(uint32_t *__restrict__ tilesums, uint32_t ntiles,
-                                                           unsigned long long *__restrict__ total_out) {
-  __shared__ uint32_t sm[8];
-  unsigned long long carry = 0;
-  for (uint32_t base = 0; base < ntiles; base += SC_THREADS) {
-    const uint32_t i = base + threadIdx.x;
-    const uint32_t v = i < ntiles ? tilesums[i] : 0;
-    uint32_t tot;
-    const uint32_t ex = block_excl_scan256(v, &tot, sm);
-    if (i < ntiles) tilesums[i] = (uint32_t)(carry + ex);
-    carry += tot;
+  uint32_t tsum = 0, tmax = 0;
+#pragma unroll
+  for (int j = 0; j < R; ++j) {
+    tsum += v[j];
+    tmax = max(tmax, v[j]);
   }
-  if (threadIdx.x == 0 && total_out) *total_out = carry;
-}
-
-// out[i] = sum_{j<i} in[j] (mod 2^32); out may alias in.  If n_out == n+1 the grand total is
-// appended as out[n] (the bucket table's last entry).
-__global__ void __launch_bounds__(SC_THREADS) k_scan_apply(const uint32_t *in, uint32_t *out, uint64_t n,
-                                                           const uint32_t *__restrict__ tilesums,
-                                                           int append_total, int rounds) {
-  __shared__ uint32_t sm[8];
-  const uint64_t base = (uint64_t)blockIdx.x * SC_THREADS * rounds;
-  uint32_t carry = tilesums[blockIdx.x];
-#pragma unroll 1
-  for (int r = 0; r < rounds; ++r) {
-    const uint64_t i = base + (uint64_t)r * SC_THREADS + threadIdx.x;
-    const uint32_t v = i < n ? in[i] : 0;
-    uint32_t tot;
-    const uint32_t ex = block_excl_scan256(v, &tot, sm);
-    if (i < n) out[i] = carry + ex;
-    if (append_total && i == n - 1) out[n] = carry + ex + v;
-    carry += tot;
+  uint32_t tot;
+  const uint32_t ex = block_excl_scan256(tsum, &tot, sm);
+  if (maxout) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tmax = max(tmax, __shfl_xor_sync(GTB_FULL, tmax, o));
+    if ((threadIdx.x & 31) == 0 && tmax) atomicMax(maxout, tmax);
+  }
+  const unsigned long long tag = (unsigned long long)epoch << 34;
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    if (tile == 0) {
+      if (lane == 0) {
+        atomicExch(&state[0], tag | (SCAN_FLAG_PFX << 32) | tot);
+        s_excl = 0;
+      }
+    } else {
+      if (lane == 0) atomicExch(&state[tile], tag | (SCAN_FLAG_AGG << 32) | tot);
+      uint32_t excl = 0;
+      int64_t look = (int64_t)tile - 1;
+      while (true) {
+        const int64_t idx = look - lane;
+        unsigned long long st = tag | (SCAN_FLAG_PFX << 32);      // before tile 0: an inclusive prefix of 0
+        if (idx >= 0) {
+          do {
+            st = *((volatile unsigned long long *)&state[idx]);
+          } while ((st >> 34) != epoch || ((st >> 32) & 3ull) == 0);
+        }
+        const unsigned pmask = __ballot_sync(GTB_FULL, ((st >> 32) & 3ull) == SCAN_FLAG_PFX);
+        const int firstp = pmask ? __ffs(pmask) - 1 : 31;
+        uint32_t val = lane <= firstp ? (uint32_t)st : 0u;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(GTB_FULL, val, o);
+        excl += val;
+        if (pmask) break;
+        look -= 32;
+      }
+      if (lane == 0) {
+        atomicExch(&state[tile], tag | (SCAN_FLAG_PFX << 32) | (uint32_t)(excl + tot));
+        s_excl = excl;
+      }
+    }
+  }
+  __syncthreads();
+  uint32_t run = s_excl + ex;
+  if (base + R <= n) {
+    if (R % 4 == 0 && (((uintptr_t)out) & 15) == 0) {
+#pragma unroll
+      for (int j = 0; j < R; j += 4) {
+        uint4 q;
+        q.x = run; run += v[j];
+        q.y = run; run += v[j + 1];
+        q.z = run; run += v[j + 2];
+        q.w = run; run += v[j + 3];
+        *reinterpret_cast<uint4 *>(out + base + j) = q;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < R; ++j) { out[base + j] = run; run += v[j]; }
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+      if (base + j < n) { out[base + j] = run; run += v[j]; }
+    }
+  }
+  if (tile == ntiles - 1 && threadIdx.x == 0) {
+    const unsigned long long total = (unsigned long long)s_excl + tot;     // sums stay below 2^32 by construction
+    if (append_total) out[n] = (uint32_t)total;
+    if (total_out) *total_out = total;
+    *ticket = 0;                                   // every ticket of this launch has been handed out
   }
 }
 

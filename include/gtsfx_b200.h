@@ -180,7 +180,8 @@ int gtb200_sort_part(gtb200_ctx *ctx, uint64_t mincode, uint64_t maxcode, void *
 /*
  * Replaces gt_SSSPbuf_fillspecialnextpage (src/match/sfx-suffixgetset.c:586-690): entries
  * [first, first+count) of the tail of the suffix array (positions of all special symbols in
- * ascending order, then totallength; specialcharacters+1 entries in total).
+ * ascending order, then totallength; specialcharacters+1 entries in total).  With suftab == NULL
+ * the entries are only produced on the device, stream-ordered on gtb200_stream (no host wait).
  */
 int gtb200_tail(gtb200_ctx *ctx, uint64_t first, uint64_t count, void *suftab, int suftab_is_uint32);
 
