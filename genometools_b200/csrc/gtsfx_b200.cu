@@ -106,6 +106,7 @@ struct gtb200_ctx {
   uint32_t sort_maxbucket;   // buckets above this size take the refinement path (testing knob)
   uint64_t twolevel_bytes;   // parts whose 4-byte suffix array exceeds this use the two-level insertion
   bool l2_window;            // persisting-L2 window set on the stream
+  int fused_widen;           // 1 = direct path writes the 64-bit image from the sorters (GTB200_FUSED_WIDEN, testing knob)
   int pipeline;              // 1 = overlap D2H of finished slices with the sort of the next (GTB200_PIPELINE, testing knob)
   cudaStream_t copy_stream;
   cudaEvent_t slice_ev[8];
@@ -805,11 +806,21 @@ __global__ void k_sum_u32(const uint32_t *__restrict__ a, uint64_t n, unsigned l
 // ---------------------------------------------------------------------------------------------
 struct PartOut {
   uint32_t *sa;
+  uint64_t *sa64;            // non-null: finishers also write the 64-bit image (.suf format), k_widen is skipped
   uint8_t *lcp;
   gtb200_largelcp *llv;      // unordered append buffer (refinement only)
   PartStats *stats;
   uint32_t partoffset;
 };
+
+// final suffix-array entry: 32-bit working array and, on the direct path, the 64-bit image in the same sweep
+__device__ __forceinline__ void put_sa(const PartOut &o, uint32_t r, uint32_t p) {
+  __stcs(o.sa + r, p);
+  if (o.sa64) {
+    __stcs(o.sa64 + r, (uint64_t)p);
+    if (p == 0) o.stats->longest = (uint64_t)o.partoffset + r;
+  }
+}
 
 __device__ __forceinline__ void emit_large(const PartOut &o, uint32_t r, uint32_t value) {
   const unsigned long long slot = atomicAdd(&o.stats->llv_count, 1ull);
@@ -842,7 +853,7 @@ __global__ void k_place_padded(const uint64_t *__restrict__ padkey, const uint32
   const uint32_t npad = csc[(code - (sigma - 1)) / sigma];
   const uint32_t r = lb[code + 1] - npad + (uint32_t)(i - lo) - out.partoffset;
   const uint32_t L = pl - (uint32_t)(key & 63);
-  out.sa[r] = padpos[i];
+  put_sa(out, r, padpos[i]);
   out.lcp[r] = (uint8_t)L;               // own number of real symbols (src/match/sfx-lcpvalues.c:125-215);
   if (r + out.partoffset > lb[code])     // a bucket-first entry is overwritten by k_boundary
     atomicMax(&out.stats->maxdepth, L);
@@ -933,7 +944,7 @@ __device__ __forceinline__ bool warp_sort_bucket(const Text<BITS> &T, const Part
   for (int e = 0; e < E; ++e) {
     const uint32_t i = e * 32 + lane;
     if (i < cnt) {
-      __stcs(out.sa + start + i, v[e]);
+      put_sa(out, start + i, v[e]);
       if (i >= 1) {
         __stcs(out.lcp + start + i, (uint8_t)l[e]);      // provisional for tied pairs, rewritten by refinement
         if (!tp[e]) {
@@ -1041,7 +1052,7 @@ __device__ __forceinline__ int warp_sort_bucket32(const Text<BITS> &T, const Par
   for (int e = 0; e < E; ++e) {
     const uint32_t i = e * 32 + lane;
     if (i < cnt) {
-      __stcs(out.sa + start + i, spos[k[e] & 0xff]);
+      put_sa(out, start + i, spos[k[e] & 0xff]);
       if (i >= 1) {
         __stcs(out.lcp + start + i, (uint8_t)l[e]);
         sum += l[e];
@@ -1090,7 +1101,7 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
     if (c0 <= maxcode) {
       nb0 = lb[c0]; ncur = cursor[c0];
       const uint32_t ncnt = ncur - nb0;
-      if (ncnt >= 2 && ncnt <= SORT_MAXBUCKET) {
+      if (ncnt >= 1 && ncnt <= SORT_MAXBUCKET) {
 #pragma unroll
         for (int e = 0; e < 4; ++e)
           if (e * 32 + lane < ncnt) npos[e] = out.sa[nb0 - out.partoffset + e * 32 + lane];
@@ -1107,15 +1118,21 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
     nb0 = n2b0; ncur = n2cur;                      // bucket c+nw: bounds arrived, request its positions
     if (c + nw <= maxcode) {
       const uint32_t ncnt = ncur - nb0;
-      if (ncnt >= 2 && ncnt <= SORT_MAXBUCKET) {
+      if (ncnt >= 1 && ncnt <= SORT_MAXBUCKET) {
 #pragma unroll
         for (int e = 0; e < 4; ++e)
           if (e * 32 + lane < ncnt) npos[e] = out.sa[nb0 - out.partoffset + e * 32 + lane];
       }
     }
     if (c + 2 * nw <= maxcode) { n2b0 = lb[c + 2 * nw]; n2cur = cursor[c + 2 * nw]; }
-    if (cnt <= 1) continue;
     const uint32_t start = b0 - out.partoffset;
+    if (cnt <= 1) {                          // a single suffix is in place; only the 64-bit image is missing
+      if (cnt == 1 && out.sa64 && lane == 0) {
+        out.sa64[start] = pos[0];
+        if (pos[0] == 0) out.stats->longest = (uint64_t)out.partoffset + start;
+      }
+      continue;
+    }
     bool ok = false;
     if (cnt > maxbucket) {
       if (cnt <= medmax) {                 // too large for one warp: queue for k_sort_medium
@@ -1204,7 +1221,7 @@ __global__ void __launch_bounds__(256) k_sort_medium(Text<BITS> T, PartOut out, 
       atomicAdd(&out.stats->fb_buckets, 1u);
     }
     for (uint32_t i = threadIdx.x; i < cnt; i += 256) {
-      out.sa[start + i] = spos[i];
+      put_sa(out, start + i, spos[i]);
       if (i >= 1) {
         const uint32_t l = pl + key_common<BITS>(skey[i - 1], skey[i]);
         out.lcp[start + i] = (uint8_t)l;
@@ -1979,6 +1996,8 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
   }
   c->pipeline = 1;
   if (const char *e7 = getenv("GTB200_PIPELINE")) c->pipeline = atoi(e7);
+  c->fused_widen = 1;
+  if (const char *e8 = getenv("GTB200_FUSED_WIDEN")) c->fused_widen = atoi(e8);
   c->doubling = 1;
   if (const char *e6 = getenv("GTB200_DOUBLING")) c->doubling = atoi(e6);
   c->tile_mode = 1;
@@ -2515,6 +2534,10 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
     CK(cudaGetLastError());
   }
   const bool twolevel = !tile && rwidth * 4 > c->twolevel_bytes && rcodes >= 4096;
+  // Direct insertion leaves the 64-bit buffer free (the other two paths keep their records in it): the sorters
+  // then write the .suf image themselves and k_widen is not launched.  A later refinement redoes the image.
+  PartOut fin = out;
+  if (!tile && !twolevel && c->fused_widen) fin.sa64 = c->d_suf64;
   if (tile) {
     // insertion already done
   } else if (!twolevel) {
@@ -2547,13 +2570,13 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
   if (c->padcap > 1) {
     ProfScope ps(c, KC_PADDED);
     k_place_padded<<<grid_for(c->padcap, 256), 256, 0, c->stream>>>(c->d_padkey, c->d_padpos, c->d_persist, c->d_lb,
-                                                                     c->d_csc, c->cp.sigma, c->cp.pl, lo, hi, out);
+                                                                     c->d_csc, c->cp.sigma, c->cp.pl, lo, hi, fin);
   }
   {
     ProfScope ps(c, KC_SORT);
     uint64_t warps = rcodes < 148ull * 64 ? rcodes : 148ull * 64;   // 8 blocks of 8 warps per SM
     const uint32_t medmax = c->sort_maxbucket == SORT_MAXBUCKET ? MED_MAX : 0;   // testing knob disables both
-    k_sort_buckets<BITS><<<grid_for(warps * 32, 256), 256, 0, c->stream>>>(T, out, c->d_lb, c->d_cursor, lo, hi,
+    k_sort_buckets<BITS><<<grid_for(warps * 32, 256), 256, 0, c->stream>>>(T, fin, c->d_lb, c->d_cursor, lo, hi,
                                                                           c->cp.pl, fbb, c->sort_maxbucket,
                                                                           c->d_medlist, medmax, tile ? 1 : 0, fbwords);
   }
@@ -2561,7 +2584,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
     ProfScope ps(c, KC_SORT);
     const size_t smem = (size_t)MED_MAX * 12;
     CK(cudaFuncSetAttribute(k_sort_medium<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_sort_medium<BITS><<<148 * 4, 256, smem, c->stream>>>(T, out, c->d_lb, c->d_cursor, c->d_medlist, lo, c->cp.pl,
+    k_sort_medium<BITS><<<148 * 4, 256, smem, c->stream>>>(T, fin, c->d_lb, c->d_cursor, c->d_medlist, lo, c->cp.pl,
                                                           fbb, fbwords);
   }
   {
@@ -2570,7 +2593,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
     if (first_of_part && out.partoffset > 0)
       k_part_first<BITS><<<1, 32, 0, c->stream>>>(T, c->cp, out, c->d_lb, c->numcodes, c->d_csc, c->d_padkey, c->d_persist);
   }
-  {
+  if (!fin.sa64) {
     ProfScope ps(c, KC_WIDEN);
     k_widen<<<grid_for(rwidth, 256), 256, 0, c->stream>>>(c->d_sa + roff, rwidth, c->d_suf64 + roff, (uint64_t)out.partoffset + roff,
                                                          c->d_stats);
@@ -2606,6 +2629,7 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
   if (ensure_part_buffers(c, width, ncodes)) return -1;
   PartOut out;
   out.sa = c->d_sa;
+  out.sa64 = nullptr;
   out.lcp = c->d_lcp;
   out.llv = nullptr;
   out.stats = c->d_stats;

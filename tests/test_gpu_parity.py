@@ -312,6 +312,28 @@ def test_pipelined_fetch_matches(pipeline, monkeypatch):
     assert got["fallback_suffixes"] > 0
 
 
+@pytest.mark.parametrize("fused", ["0", "1"])
+def test_suf_image_from_sorters(fused, monkeypatch):
+    """On the direct-insertion path the sorters write the 64-bit .suf image themselves (GTB200_FUSED_WIDEN=1,
+    the default) instead of a separate widening pass: same bytes and the same `longest`, with one part, with
+    parts, with medium buckets (pl forced down) and when refinement has to redo the image."""
+    monkeypatch.setenv("GTB200_FUSED_WIDEN", fused)
+    enc = synth.multi_dna_with_nruns(700_000, nseq=5, seed=201)
+    want = oracle.build(enc, 4)
+    for parts in (1, 3):
+        got = sfx.suffixerator(enc, "dna", parts=parts)
+        _compare(got, want, f"fused{fused}/parts{parts}")
+        assert got["longest"] == int(np.flatnonzero(want["suf_array"] == 0)[0])
+    wantm = oracle.build(enc, 4, 4)                       # ~2700 suffixes per bucket: the block sorter finishes them
+    gotm = sfx.suffixerator(enc, "dna", prefixlength=4)
+    _compare(gotm, wantm, f"fused{fused}/medium")
+    rep = synth.repeat_rich_dna(200_000, seed=202)
+    wantr = oracle.build(rep, 4)
+    gotr = sfx.suffixerator(rep, "dna")
+    _compare(gotr, wantr, f"fused{fused}/repeats")
+    assert gotr["fallback_suffixes"] > 0
+
+
 def _apply_readmode(enc, readmode):
     e = enc[::-1].copy() if readmode in (1, 3) else enc.copy()
     return np.where(e < 4, 3 - e, e).astype(np.uint8) if readmode in (2, 3) else e
