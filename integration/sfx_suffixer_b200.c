@@ -39,6 +39,9 @@
 /* added to the B200 build of src/match/sfx-lcpvalues.c (integration/sfx_lcpvalues_b200.c) */
 void gt_Outlcpinfo_b200_writepart(GtOutlcpinfo *outlcpinfo, const uint8_t *lcp, GtUword width,
                                   const void *llv, GtUword nllv, double lcptabsum, GtUword maxbranchdepth);
+bool gt_Outlcpinfo_b200_wantsdist(const GtOutlcpinfo *outlcpinfo);
+void gt_Outlcpinfo_b200_distadd(GtOutlcpinfo *outlcpinfo, const uint8_t *lcp, GtUword from, GtUword to,
+                                const void *llv, GtUword nllv, GtUword partoffset, GtUword *llvidx);
 
 struct Sfxiterator
 {
@@ -183,7 +186,9 @@ Sfxiterator *gt_Sfxiterator_new_withadditionalvalues(const GtEncseq *encseq,
   seq.totallength = sfi->totallength;
   seq.memory = GTB200_MEM_HOST;
   seq.readmode = (int) readmode;   /* GtReadmode values are the C ABI's (core/readmode_api.h:24-27) */
-  if (seq.numofchars == 4U && gt_encseq_has_twobitencoding(encseq))
+  /* a mirrored encseq (-mirrored) stores only the forward half: its logical sequence is read through the
+     extractor below (src/core/encseq.c, gt_encseq_extract_encoded handles the virtual reverse complement) */
+  if (seq.numofchars == 4U && gt_encseq_has_twobitencoding(encseq) && !gt_encseq_is_mirrored(encseq))
   {
     GtUword k = 0, nr = gt_encseq_realspecialranges(encseq);
     seq.twobitencoding = (const uint64_t *) gt_encseq_twobitencoding_export(encseq);
@@ -332,6 +337,31 @@ const GtSuffixsortspace *gt_Sfxiterator_next(GtUword *numberofsuffixes, bool *sp
     {
       gt_Outlcpinfo_b200_writepart(sfi->outlcpinfo, sfi->lcpbuf, (GtUword) pi.width, sfi->llvbuf,
                                    (GtUword) pi.numoflargelcpvalues, pi.lcptabsum, (GtUword) pi.maxbranchdepth);
+      if (gt_Outlcpinfo_b200_wantsdist(sfi->outlcpinfo))
+      {
+        /* -lcpdist: replay the regular entries of every bucket of the part, as outlcpvalues sees them
+           (src/match/sfx-lcpvalues.c:622-693); the special-padded right end of a bucket is skipped */
+        const uint64_t sigma = (uint64_t) gt_alphabet_num_of_chars(gt_encseq_alphabet(sfi->encseq));
+        GtUword llvidx = 0;
+        uint64_t code;
+
+        for (code = sfi->mincodes[p]; code <= sfi->maxcodes[p]; code++)
+        {
+          const GtUword left = (GtUword) sfi->leftborder[code], right = (GtUword) sfi->leftborder[code + 1];
+          GtUword padded = 0;
+
+          if (code % sigma == sigma - 1)
+          {
+            padded = (GtUword) sfi->countspecialcodes[(code - (sigma - 1)) / sigma];
+          }
+          if (right - padded > left)
+          {
+            gt_Outlcpinfo_b200_distadd(sfi->outlcpinfo, sfi->lcpbuf, left - (GtUword) pi.partoffset,
+                                       right - padded - (GtUword) pi.partoffset, sfi->llvbuf,
+                                       (GtUword) pi.numoflargelcpvalues, (GtUword) pi.partoffset, &llvidx);
+          }
+        }
+      }
     }
     *numberofsuffixes = (GtUword) pi.width;
     if (specialsuffixes != NULL)

@@ -26,6 +26,16 @@ CASES = {
     "dna_dir_rcl": (lambda: synth.multi_dna_with_nruns(150_000, nseq=5, seed=88), "dna", ["-dir", "rcl", "-parts", "2"]),
     "dna_dir_rev_bwt": (lambda: synth.genome_like_dna(120_000, seed=89), "dna", ["-dir", "rev", "-bwt"]),
     "dna_bwt_parts2": (lambda: synth.multi_dna_with_nruns(120_000, nseq=4, seed=87), "dna", ["-bwt", "-parts", "2"]),
+    # options that change how the reference gets there, not what comes out (the drop-in ignores the strategy)
+    "dna_mirrored": (lambda: synth.multi_dna_with_nruns(90_000, nseq=4, seed=90), "dna", ["-mirrored"]),
+    "dna_mirrored_parts2": (lambda: synth.genome_like_dna(80_000, seed=91), "dna", ["-mirrored", "-parts", "2"]),
+    "dna_memlimit": (lambda: synth.multi_dna_with_nruns(200_000, nseq=3, seed=92), "dna", ["-memlimit", "2MB"]),
+    "dna_dc32": (lambda: synth.genome_like_dna(150_000, seed=93), "dna", ["-dc", "32"]),
+    "dna_cmpcharbychar": (lambda: synth.multi_dna_with_nruns(100_000, nseq=3, seed=94), "dna", ["-cmpcharbychar"]),
+    "dna_sat_uchar": (lambda: synth.multi_dna_with_nruns(100_000, nseq=3, seed=95), "dna", ["-sat", "uchar"]),
+    "dna_sat_direct": (lambda: synth.multi_dna_with_nruns(100_000, nseq=3, seed=96), "dna", ["-sat", "direct"]),
+    "dna_sat_bit": (lambda: synth.multi_dna_with_nruns(100_000, nseq=3, seed=97), "dna", ["-sat", "bit"]),
+    "dna_lcpdist": (lambda: synth.genome_like_dna(60_000, seed=98), "dna", ["-lcpdist"]),
     "protein_parts2": (lambda: synth.random_protein(400, seed=85), "protein", ["-parts", "2"]),
 }
 
@@ -44,14 +54,16 @@ def test_gt_suffixerator_dropin_is_byte_identical(case, tmp_path):
     fasta = str(tmp_path / "in.fna")
     encseq.write_fasta(fasta, encseq.decode_to_fasta_bytes(enc, alphabet))
     common = ["suffixerator", "-" + alphabet, "-suf", "-lcp", "-bck", "-tis", "-des", "-sds", "-ssp"] + extra
-    _run(GT_REF, common + ["-indexname", "ref", "-db", fasta], str(tmp_path))
-    _run(GT_B200, common + ["-indexname", "b200", "-db", fasta], str(tmp_path))
+    out_ref = _run(GT_REF, common + ["-indexname", "ref", "-db", fasta], str(tmp_path))
+    out_b200 = _run(GT_B200, common + ["-indexname", "b200", "-db", fasta], str(tmp_path))
+    if "-lcpdist" in extra:                    # the LCP histogram the reference prints on stdout
+        assert out_ref == out_b200
     exts = ("suf", "lcp", "llv", "bck", "esq", "prj") + (("bwt",) if "-bwt" in extra else ())
     for ext in exts:
         a = open(tmp_path / f"ref.{ext}", "rb").read()
         b = open(tmp_path / f"b200.{ext}", "rb").read()
         assert a == b, f".{ext} differs between the reference and the B200 drop-in ({len(a)} vs {len(b)} bytes)"
-    if "-suftabuint" not in extra and "-dir" not in extra:
+    if "-suftabuint" not in extra and "-dir" not in extra and "-mirrored" not in extra:
         # the reference's own checker on the drop-in's index
         _run(GT_REF, ["sfxmap", "-tis", "-suf", "-lcp", "-bck", "-esa", "b200"], str(tmp_path))
 
