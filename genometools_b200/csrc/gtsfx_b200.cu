@@ -957,30 +957,55 @@ __device__ __forceinline__ bool warp_sort_bucket(const Text<BITS> &T, const Part
   return !__any_sync(GTB_FULL, tie);   // false: sorted on pl+W symbols, tie groups go to the refinement path
 }
 
-// 32-bit variant: keys are (12 leading bases of the window << 8) | slot; min/max network
+// 32-bit variant: keys are (12 leading bases of the window << 8) | slot; min/max network.
+// Ascending-only form of the bitonic sorter (each merge starts with a flip, partner = index ^ (size-1), then
+// disperses with partner = index ^ stride; the lower index always keeps the minimum).  Padding keys
+// (0xffffffff at the top indices) therefore never move, and a bucket of 65..96 suffixes runs the 128-wide
+// network on E = 3 registers per lane, skipping every exchange with the absent fourth.
 template <int E>
 struct WarpSorter32 {
   __device__ static __forceinline__ void sort(uint32_t (&k)[E], int lane) {
+    constexpr int N = E <= 1 ? 32 : E <= 2 ? 64 : 128;
 #pragma unroll
-    for (int size = 2; size <= 32 * E; size <<= 1) {
+    for (int size = 2; size <= N; size <<= 1) {
+      if (size <= 32) {
+        const bool keepmin = (lane & (size >> 1)) == 0;
 #pragma unroll
-      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        for (int e = 0; e < E; ++e) {
+          const uint32_t o = __shfl_xor_sync(GTB_FULL, k[e], size - 1);
+          k[e] = keepmin ? min(k[e], o) : max(k[e], o);
+        }
+      } else {
+        const int me = (size >> 5) - 1;                 // register partner: e ^ 1 (size 64), e ^ 3 (size 128)
+        uint32_t o[E];
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+          const int pe = e ^ me;
+          o[e] = pe < E ? __shfl_xor_sync(GTB_FULL, k[pe < E ? pe : 0], 31) : 0xffffffffu;
+        }
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+          const int pe = e ^ me;
+          if (pe < E) k[e] = e < pe ? min(k[e], o[e]) : max(k[e], o[e]);
+        }
+      }
+#pragma unroll
+      for (int stride = size >> 2; stride > 0; stride >>= 1) {
         if (stride >= 32) {
           const int es = stride >> 5;
 #pragma unroll
           for (int e = 0; e < E; ++e) {
-            if ((e & es) == 0) {
-              const bool asc = (((e * 32) & size) == 0);
+            if ((e & es) == 0 && (e | es) < E) {
               const uint32_t lo = min(k[e], k[e | es]), hi = max(k[e], k[e | es]);
-              k[e] = asc ? lo : hi;
-              k[e | es] = asc ? hi : lo;
+              k[e] = lo;
+              k[e | es] = hi;
             }
           }
         } else {
+          const bool keepmin = (lane & stride) == 0;
 #pragma unroll
           for (int e = 0; e < E; ++e) {
             const uint32_t o = __shfl_xor_sync(GTB_FULL, k[e], stride);
-            const bool keepmin = ((((e * 32 + lane) & size) == 0) == ((lane & stride) == 0));
             k[e] = keepmin ? min(k[e], o) : max(k[e], o);
           }
         }
@@ -1073,7 +1098,7 @@ __device__ __forceinline__ bool warp_sort_any(const Text<BITS> &T, const PartOut
   if (BITS == 2) {
     if (warp_sort_bucket32<BITS, E>(T, out, src, pre, srcL, pkeys, start, cnt, pl, lane, skey, spos, sum, mx) == 0) return true;
   }
-  return warp_sort_bucket<BITS, E>(T, out, src, pre, srcL, pkeys, start, cnt, pl, lane, sum, mx);
+  return warp_sort_bucket<BITS, (E == 3 ? 4 : E)>(T, out, src, pre, srcL, pkeys, start, cnt, pl, lane, sum, mx);
 }
 
 template <int BITS>
@@ -1142,6 +1167,7 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
       ok = false;
     } else if (cnt <= 32) ok = warp_sort_any<BITS, 1>(T, out, out.sa + start, pos, nullptr, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
     else if (cnt <= 64) ok = warp_sort_any<BITS, 2>(T, out, out.sa + start, pos, nullptr, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
+    else if (cnt <= 96) ok = warp_sort_any<BITS, 3>(T, out, out.sa + start, pos, nullptr, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
     else if (cnt <= 128) ok = warp_sort_any<BITS, 4>(T, out, out.sa + start, pos, nullptr, nullptr, start, cnt, pl, lane, skey, spos, sum, mx);
     if (!ok && lane == 0) {
       const uint64_t rel = c - mincode;

@@ -321,6 +321,7 @@ __global__ void __launch_bounds__(TS_THREADS, 2) k_tile_sort(Text<BITS> T, PartO
         bool clean = true;                              // sorted and free of ties
         if (cf <= 32) clean = warp_sort_any<BITS, 1>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
         else if (cf <= 64) clean = warp_sort_any<BITS, 2>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else if (cf <= 96) clean = warp_sort_any<BITS, 3>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
         else if (cf <= SORT_MAXBUCKET) clean = warp_sort_any<BITS, 4>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
         else {                                          // too large for a warp: leave it to the global sorters
           for (uint32_t i = lane; i < cf; i += 32) out.sa[start + i] = src[i];
