@@ -296,9 +296,12 @@ def main():
     shard = (n // world + 63) // 64 * 64
     pos_lo, pos_hi = min(n, rank * shard), (n if rank == world - 1 else min(n, (rank + 1) * shard))
     tables = {}
-    # The all-reduce costs ~0.25 ms of launch + NCCL latency (measured at N = 2): it pays only when a replicated
-    # count of the whole genome is more expensive than that, i.e. for genomes of chr1 size and up.
-    sharded_count = world > 1 and n >= 64_000_000
+    # The all-reduce costs ~0.08 ms of launch + NCCL latency (measured at N = 2 on a 1 MB table: step 0.309 ms
+    # replicated, 0.365 ms sharded), counting ~5 ps per position: sharding pays once the (1 - 1/N) n positions a
+    # rank no longer counts are worth more than that.
+    sharded_count = world > 1 and n * (1.0 - 1.0 / world) >= 24_000_000
+    if os.environ.get("GTB200_BENCH_SHARDED_COUNT"):            # experiment knob: force either way
+        sharded_count = world > 1 and os.environ["GTB200_BENCH_SHARDED_COUNT"] == "1"
 
     def count_step(ctx):
         """Counting phase: replicated at N = 1; position-sharded + one all-reduce of the sigma^pl tables at N > 1."""
