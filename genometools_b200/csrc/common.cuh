@@ -12,7 +12,9 @@
 //   text : uint64_t words, symbols packed big-endian, BITS per symbol, SPW = 64/BITS per word:
 //          symbol i sits in bits [64-BITS*(i%SPW+1), 64-BITS*(i%SPW)) of word i/SPW.  For DNA
 //          (BITS=2) this IS GtEncseq's twobitencoding (src/core/encseq.c:73-81), uploaded as is.
-//          Other alphabets use BITS=8.  Special positions hold an arbitrary filler.
+//          Other alphabets use BITS=8.  Special positions hold an arbitrary filler for BITS=2 and
+//          0xff for BITS=8 (as do all bytes from position n to the end of the padding), so byte
+//          text can be keyed without the bitmap.
 //   mask : bitmap, bit (i&63) of word i>>6 (LSB first) is 1 iff position i holds a wildcard or
 //          separator; all bits >= totallength are 1 (the virtual end is a special, GT_UNIQUEINT,
 //          src/core/encseq.h:640).
@@ -55,10 +57,22 @@ struct Text {
 template <int BITS>
 __device__ __forceinline__ uint64_t make_key(const Text<BITS> &T, uint64_t q) {
   constexpr int W = Text<BITS>::W;
-  const uint64_t mw = T.maskwin(q);
-  unsigned avail = mw ? (unsigned)(__ffsll((long long)mw) - 1) : 64u;
+  unsigned avail;
+  const uint64_t win = T.window(q);
+  if (BITS == 8) {
+    // byte text: a special (and everything from position n on) is stored as 0xff/0xfe, real symbols are < 254,
+    // so the window itself tells where the first special is - no bitmap access.  z has a zero 7-bit field
+    // exactly where the byte is >= 0xfe; adding 0x7f sets bit 7 of every other field without carries.
+    const uint64_t z = ((~win) >> 1) & 0x7f7f7f7f7f7f7f7full;
+    const uint64_t real = (z + 0x7f7f7f7f7f7f7f7full) & 0x8080808080808080ull;
+    const uint64_t spm = real ^ 0x8080808080808080ull;
+    avail = spm ? (unsigned)__clzll((long long)spm) >> 3 : 8u;
+  } else {
+    const uint64_t mw = T.maskwin(q);
+    avail = mw ? (unsigned)(__ffsll((long long)mw) - 1) : 64u;
+  }
   if (avail > (unsigned)W) avail = W;
-  uint64_t x = T.window(q) >> 8;             // W symbols in bits 55..0
+  uint64_t x = win >> 8;                     // W symbols in bits 55..0
   if (avail < (unsigned)W) {
     const unsigned padbits = (W - avail) * BITS;   // 1..56
     x |= (~0ull) >> (64 - padbits);

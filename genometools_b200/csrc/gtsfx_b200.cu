@@ -424,7 +424,7 @@ __global__ void k_pack_bytes(const uint8_t *__restrict__ enc, uint64_t n, uint64
       const uint64_t p = p0 + (uint64_t)wq * SPW + k;
       uint8_t ch = p < n ? enc[p] : (uint8_t)255;
       const bool sp = ch >= 254;
-      if (sp) { mw |= 1ull << (wq * SPW + k); ch = 0; }
+      if (sp) { mw |= 1ull << (wq * SPW + k); ch = BITS == 8 ? 0xff : 0; }   // byte text keeps specials visible (common.cuh)
       word |= (uint64_t)ch << (64 - BITS * (k + 1));
     }
     text[t * (64 / SPW) + wq] = word;
@@ -448,11 +448,14 @@ __global__ void k_readmode_transform(const uint64_t *__restrict__ text, const ui
     uint64_t word = 0;
     for (int k = 0; k < SPW; ++k) {
       const uint64_t p = p0 + (uint64_t)wq * SPW + k;
-      if (p >= n) continue;
+      if (p >= n) {
+        if (BITS == 8) word |= 0xffull << (64 - BITS * (k + 1));
+        continue;
+      }
       const uint64_t src = reverse ? n - 1 - p : p;
       const bool sp = (mask[src >> 6] >> (src & 63)) & 1ull;
       uint64_t sym = (text[src / SPW] >> (64 - BITS * (src % SPW + 1))) & ((1ull << BITS) - 1);
-      if (sp) { mw |= 1ull << (wq * SPW + k); sym = 0; }
+      if (sp) { mw |= 1ull << (wq * SPW + k); sym = BITS == 8 ? 0xff : 0; }
       else if (complement) sym = 3 - sym;
       word |= sym << (64 - BITS * (k + 1));
     }
@@ -1012,6 +1015,30 @@ struct WarpSorter32 {
       }
     }
   }
+  // the last log2(32 E) steps of a merge (strides 16 E .. 1), for a chunk whose wider steps ran elsewhere
+  __device__ static __forceinline__ void tail(uint32_t (&k)[E], int lane) {
+#pragma unroll
+    for (int stride = 16 * E; stride > 0; stride >>= 1) {
+      if (stride >= 32) {
+        const int es = stride >> 5;
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+          if ((e & es) == 0 && (e | es) < E) {
+            const uint32_t lo = min(k[e], k[e | es]), hi = max(k[e], k[e | es]);
+            k[e] = lo;
+            k[e | es] = hi;
+          }
+        }
+      } else {
+        const bool keepmin = (lane & stride) == 0;
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+          const uint32_t o = __shfl_xor_sync(GTB_FULL, k[e], stride);
+          k[e] = keepmin ? min(k[e], o) : max(k[e], o);
+        }
+      }
+    }
+  }
 };
 
 #define GTB_MAXSLICES 8
@@ -1192,18 +1219,73 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
 
 #include "tiles.cuh"
 
-// Buckets of 257..MED_MAX suffixes: one block per bucket, (key,pos) pairs in shared memory, bitonic
-// network with __syncthreads between steps; LCP and tie detection as in the warp sorter.
-#define MED_MAX 4096
+// Buckets of 129..MED_MAX suffixes: one block per bucket.  Full 64-bit keys and positions are parked in shared
+// memory by slot; what is sorted is one 32-bit word per suffix, (20 leading key bits << 12) | slot:
+//   phase A  every warp sorts chunks of 32 E words in registers (WarpSorter32, no block barrier),
+//   phase B  log2(P / 32 E) merge levels: the wide exchanges (flip, strides >= chunk) run in shared memory
+//            with a barrier each, the narrow ones again in registers per chunk,
+//   fix-up   runs of equal 20-bit prefixes (short: the prefix covers 10 bases / 4 residues) are put in
+//            (key, position) order by the thread that finds the run start; a run longer than 32 sends the
+//            bucket to the exact block-wide 64-bit network below.
+// LCP and tie detection as in the warp sorter.
+#define MED_MAX 1024          // 16 KB of shared memory per block: eight blocks per SM hide the gathers and barriers
+#define MED_SMEM ((size_t)MED_MAX * 16)
+
+// 20 leading key bits: 10 bases, or 4 symbols squeezed to 5 bits each (values >= 31, padding included, collapse
+// to 31: a monotone map, so the order of the prefixes never contradicts the order of the keys)
+template <int BITS>
+__device__ __forceinline__ uint32_t key_prefix20(uint64_t key) {
+  if (BITS == 2) return (uint32_t)(key >> 44);
+  uint32_t r = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t b = (uint32_t)(key >> (56 - 8 * j)) & 0xffu;
+    r = (r << 5) | (b < 31u ? b : 31u);
+  }
+  return r;
+}
+
+template <int E>
+__device__ __forceinline__ void med_chunks(uint32_t *s32, uint32_t P, int wid, int lane, bool full_sort) {
+  for (uint32_t cb = wid * 32 * E; cb < P; cb += 8 * 32 * E) {
+    uint32_t k[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) k[e] = s32[cb + e * 32 + lane];
+    if (full_sort) WarpSorter32<E>::sort(k, lane);
+    else WarpSorter32<E>::tail(k, lane);
+#pragma unroll
+    for (int e = 0; e < E; ++e) s32[cb + e * 32 + lane] = k[e];
+  }
+}
+
+// exact fallback: block-wide bitonic network on the (key, position) pairs themselves
+__device__ __forceinline__ void med_bitonic64(uint64_t *skey, uint32_t *spos, uint32_t P) {
+  for (uint32_t size = 2; size <= P; size <<= 1) {
+    for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+      for (uint32_t i = threadIdx.x; i < P / 2; i += 256) {
+        const uint32_t lo = 2 * i - (i & (stride - 1)), hi = lo + stride;
+        const bool asc = ((lo & size) == 0);
+        const uint64_t ka = skey[lo], kb = skey[hi];
+        const uint32_t pa = spos[lo], pb = spos[hi];
+        const bool gt = ka > kb || (ka == kb && pa > pb);
+        if (gt == asc) { skey[lo] = kb; skey[hi] = ka; spos[lo] = pb; spos[hi] = pa; }
+      }
+      __syncthreads();
+    }
+  }
+}
+
 template <int BITS>
 __global__ void __launch_bounds__(256) k_sort_medium(Text<BITS> T, PartOut out, const uint32_t *__restrict__ lb,
                                                      const uint32_t *__restrict__ cursor,
                                                      const uint32_t *__restrict__ medlist, uint64_t mincode,
                                                      unsigned pl, uint32_t *__restrict__ fbbits, uint64_t tieoff) {
   extern __shared__ __align__(16) unsigned char sm_raw[];
-  uint64_t *skey = (uint64_t *)sm_raw;
-  uint32_t *spos = (uint32_t *)(skey + MED_MAX);
-  __shared__ int s_tie;
+  uint64_t *skey = (uint64_t *)sm_raw;                 // full keys by slot
+  uint32_t *spos = (uint32_t *)(skey + MED_MAX);       // positions by slot
+  uint32_t *s32 = spos + MED_MAX;                      // (prefix20 << 12) | slot, sorted in place
+  __shared__ int s_tie, s_bigrun;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const uint32_t nmed = out.stats->med_count;
   unsigned long long sum = 0;
   uint32_t mx = 0;
@@ -1215,30 +1297,84 @@ __global__ void __launch_bounds__(256) k_sort_medium(Text<BITS> T, PartOut out, 
     for (uint32_t i = threadIdx.x; i < P; i += 256) {
       if (i < cnt) {
         const uint32_t p = out.sa[start + i];
-        skey[i] = make_key<BITS>(T, (uint64_t)p + pl);
+        const uint64_t key = make_key<BITS>(T, (uint64_t)p + pl);
+        skey[i] = key;
         spos[i] = p;
+        s32[i] = (key_prefix20<BITS>(key) << 12) | i;
       } else {
-        skey[i] = ~0ull;
-        spos[i] = 0xffffffffu;
+        s32[i] = 0xffffffffu;
       }
     }
-    if (threadIdx.x == 0) s_tie = 0;
+    if (threadIdx.x == 0) { s_tie = 0; s_bigrun = 0; }
     __syncthreads();
-    for (uint32_t size = 2; size <= P; size <<= 1) {
-      for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+    // ---- sort the 32-bit words ----
+    const int Ew = (int)(P >> 8);                      // registers per lane of a warp chunk: 1, 2 or 4
+    const uint32_t C = 32u * Ew;
+    if (Ew == 1) med_chunks<1>(s32, P, wid, lane, true);
+    else if (Ew == 2) med_chunks<2>(s32, P, wid, lane, true);
+    else med_chunks<4>(s32, P, wid, lane, true);
+    __syncthreads();
+    for (uint32_t size = 2 * C; size <= P; size <<= 1) {
+      const uint32_t half = size >> 1;
+      for (uint32_t i = threadIdx.x; i < P / 2; i += 256) {        // flip: index ^ (size-1)
+        const uint32_t lo = (i / half) * size + (i & (half - 1)), hi = lo ^ (size - 1);
+        const uint32_t a = s32[lo], bb = s32[hi];
+        s32[lo] = min(a, bb);
+        s32[hi] = max(a, bb);
+      }
+      __syncthreads();
+      for (uint32_t stride = size >> 2; stride >= C; stride >>= 1) {
         for (uint32_t i = threadIdx.x; i < P / 2; i += 256) {
           const uint32_t lo = 2 * i - (i & (stride - 1)), hi = lo + stride;
-          const bool asc = ((lo & size) == 0);
-          const uint64_t ka = skey[lo], kb = skey[hi];
-          const uint32_t pa = spos[lo], pb = spos[hi];
-          const bool gt = ka > kb || (ka == kb && pa > pb);
-          if (gt == asc) { skey[lo] = kb; skey[hi] = ka; spos[lo] = pb; spos[hi] = pa; }
+          const uint32_t a = s32[lo], bb = s32[hi];
+          s32[lo] = min(a, bb);
+          s32[hi] = max(a, bb);
         }
         __syncthreads();
       }
+      if (Ew == 1) med_chunks<1>(s32, P, wid, lane, false);
+      else if (Ew == 2) med_chunks<2>(s32, P, wid, lane, false);
+      else med_chunks<4>(s32, P, wid, lane, false);
+      __syncthreads();
     }
-    for (uint32_t i = threadIdx.x + 1; i < cnt; i += 256)
-      if (skey[i - 1] == skey[i] && (skey[i] & 0xff) == 0) s_tie = 1;
+    // ---- fix-up: order inside runs of equal 20-bit prefixes by (key, position) ----
+    for (uint32_t r = threadIdx.x; r + 1 < cnt; r += 256) {
+      const uint32_t me = s32[r] >> 12;
+      if ((r == 0 || (s32[r - 1] >> 12) != me) && (s32[r + 1] >> 12) == me) {
+        uint32_t m = 2;
+        while (r + m < cnt && (s32[r + m] >> 12) == me && m <= 32) ++m;
+        if (m > 32) {
+          s_bigrun = 1;
+        } else {
+          for (uint32_t a = 1; a < m; ++a) {                         // insertion sort, m is 2 or 3 almost always
+            const uint32_t w = s32[r + a];
+            const uint64_t kw = skey[w & 0xfff];
+            const uint32_t pw = spos[w & 0xfff];
+            uint32_t j = a;
+            while (j > 0) {
+              const uint32_t v = s32[r + j - 1];
+              const uint64_t kv = skey[v & 0xfff];
+              if (kv < kw || (kv == kw && spos[v & 0xfff] < pw)) break;
+              s32[r + j] = v;
+              --j;
+            }
+            s32[r + j] = w;
+          }
+        }
+      }
+    }
+    __syncthreads();
+    if (s_bigrun) {                                     // block-uniform: exact network on the pairs, identity slots
+      for (uint32_t i = threadIdx.x + cnt; i < P; i += 256) { skey[i] = ~0ull; spos[i] = 0xffffffffu; }
+      __syncthreads();
+      med_bitonic64(skey, spos, P);
+      for (uint32_t i = threadIdx.x; i < cnt; i += 256) s32[i] = i;
+      __syncthreads();
+    }
+    for (uint32_t i = threadIdx.x + 1; i < cnt; i += 256) {
+      const uint64_t ka = skey[s32[i - 1] & 0xfff], kb = skey[s32[i] & 0xfff];
+      if (ka == kb && (kb & 0xff) == 0) s_tie = 1;
+    }
     __syncthreads();
     if (s_tie && threadIdx.x == 0) {                    // sorted on pl+W symbols; tie groups are refined
       const uint64_t rel = c - mincode;
@@ -1247,11 +1383,13 @@ __global__ void __launch_bounds__(256) k_sort_medium(Text<BITS> T, PartOut out, 
       atomicAdd(&out.stats->fb_buckets, 1u);
     }
     for (uint32_t i = threadIdx.x; i < cnt; i += 256) {
-      put_sa(out, start + i, spos[i]);
+      const uint32_t slot = s32[i] & 0xfff;
+      put_sa(out, start + i, spos[slot]);
       if (i >= 1) {
-        const uint32_t l = pl + key_common<BITS>(skey[i - 1], skey[i]);
+        const uint64_t ka = skey[s32[i - 1] & 0xfff], kb = skey[slot];
+        const uint32_t l = pl + key_common<BITS>(ka, kb);
         out.lcp[start + i] = (uint8_t)l;
-        if (!(skey[i - 1] == skey[i] && (skey[i] & 0xff) == 0)) {
+        if (!(ka == kb && (kb & 0xff) == 0)) {
           sum += l;
           mx = max(mx, l);
         }
@@ -1857,7 +1995,9 @@ static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
   }
   if (!c->h_stats) CK(cudaMallocHost(&c->h_stats, 256));
   CK(cudaMemsetAsync(c->d_stats, 0, sizeof(PartStats), c->stream));
-  CK(cudaMemsetAsync(c->d_text, 0, (c->ntextwords + c->nmaskwords) * 8, c->stream));
+  // byte text: every position that is not a real symbol reads 0xff, padding words included (make_key<8>)
+  CK(cudaMemsetAsync(c->d_text, c->bits == 8 ? 0xff : 0, c->ntextwords * 8, c->stream));
+  CK(cudaMemsetAsync(c->d_text + c->ntextwords, 0, c->nmaskwords * 8, c->stream));
   if (seq->twobitencoding) {
     uint64_t nw = (n + 31) / 32;
     if (seq->numofwords < nw) return set_error("twobitencoding has %llu words, %llu needed",
@@ -1894,7 +2034,8 @@ static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
     uint64_t *tmp2;
     const size_t words = c->ntextwords + c->nmaskwords;
     CK(dmalloc(c, &tmp2, words * 8));
-    CK(cudaMemsetAsync(tmp2, 0, words * 8, c->stream));
+    CK(cudaMemsetAsync(tmp2, c->bits == 8 ? 0xff : 0, c->ntextwords * 8, c->stream));
+    CK(cudaMemsetAsync(tmp2 + c->ntextwords, 0, c->nmaskwords * 8, c->stream));
     {
       ProfScope ps(c, KC_PREP);
       if (c->bits == 2)
@@ -2608,9 +2749,9 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
   }
   if (c->sort_maxbucket == SORT_MAXBUCKET && rwidth > SORT_MAXBUCKET) {
     ProfScope ps(c, KC_SORT);
-    const size_t smem = (size_t)MED_MAX * 12;
+    const size_t smem = MED_SMEM;
     CK(cudaFuncSetAttribute(k_sort_medium<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_sort_medium<BITS><<<148 * 4, 256, smem, c->stream>>>(T, fin, c->d_lb, c->d_cursor, c->d_medlist, lo, c->cp.pl,
+    k_sort_medium<BITS><<<148 * 8, 256, smem, c->stream>>>(T, fin, c->d_lb, c->d_cursor, c->d_medlist, lo, c->cp.pl,
                                                           fbb, fbwords);
   }
   {

@@ -233,17 +233,34 @@ def test_device_resident_input_matches_host_input():
 
 
 def test_medium_buckets_block_sorter():
-    """Buckets of 257..4096 suffixes take the block-level sorter (k_sort_medium), not the refinement path."""
+    """Buckets of 129..1024 suffixes take the block-level sorter (k_sort_medium), not the refinement path: all
+    three chunk widths (buckets around 200, 400 and 900 suffixes), equal 20-bit prefixes (the fix-up pass) and
+    larger buckets next to them (refinement)."""
     rng = np.random.default_rng(43)
+    for n, tag in ((200_000, "p1024"), (100_000, "p512"), (50_000, "p256")):
+        enc = rng.integers(0, 4, size=n, dtype=np.uint8)
+        want = oracle.build(enc, 4, 4)        # 256 buckets of ~780 / ~390 / ~195 suffixes
+        got = sfx.suffixerator(enc, "dna", prefixlength=4)
+        _compare(got, want, f"medium/dna/{tag}")
+        assert got["fallback_suffixes"] == 0
+    # runs of equal prefixes: a tandem repeat puts many suffixes with the same next 10 bases into one bucket
+    rep = np.concatenate([np.tile(rng.integers(0, 4, size=37, dtype=np.uint8), 40), rng.integers(0, 4, size=60_000, dtype=np.uint8),
+                          np.tile(rng.integers(0, 4, size=11, dtype=np.uint8), 30)]).astype(np.uint8)
+    want = oracle.build(rep, 4, 4)
+    got = sfx.suffixerator(rep, "dna", prefixlength=4)
+    _compare(got, want, "medium/dna/runs")
     enc = rng.integers(0, 4, size=600_000, dtype=np.uint8)
-    want = oracle.build(enc, 4, 4)            # 256 buckets of ~2300 suffixes
+    want = oracle.build(enc, 4, 4)            # ~2300 per bucket: beyond the block sorter, refined
     got = sfx.suffixerator(enc, "dna", prefixlength=4)
-    _compare(got, want, "medium/dna")
-    assert got["fallback_suffixes"] == 0
+    _compare(got, want, "medium/dna/large")
     prot = synth.random_protein(1500, seed=44)
-    want = oracle.build(prot, 20, 2)          # 400 buckets of ~1200 residues
+    want = oracle.build(prot, 20, 2)          # 400 buckets of ~1200 residues, non-uniform: both sides of the limit
     got = sfx.suffixerator(prot, "protein", prefixlength=2, parts=2)
     _compare(got, want, "medium/protein")
+    prot = synth.random_protein(600, seed=45)
+    want = oracle.build(prot, 20, 2)          # ~500 per bucket
+    got = sfx.suffixerator(prot, "protein", prefixlength=2)
+    _compare(got, want, "medium/protein500")
 
 
 def test_sharded_count_equals_replicated_count():
