@@ -437,7 +437,7 @@ def main():
         text_bytes = n * bits / 8 + n / 8                       # packed text + special bitmap, read once
         m = width
         ncodes_part = maxcode - mincode + 1
-        tile = alphabet == "dna" and m >= (1 << 24) and ncodes_part >= 1024    # the library's own rule
+        tile = m >= (1 << 24) and ncodes_part >= 1024 and m // ncodes_part <= 4096   # the library's own rule
         levels = 1
         if tile:                                    # same arithmetic as sort_part_impl
             sh = 0

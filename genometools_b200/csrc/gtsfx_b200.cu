@@ -2616,7 +2616,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
     k_reset_medcount<<<1, 1, 0, c->stream>>>(c->d_stats);
   }
   // ---- tile path (DNA): staged partition into shared-memory sized bins, then sort inside the tile ----
-  bool tile = BITS == 2 && c->tile_mode != 0 && rcodes >= 2 && (c->tile_mode == 2 || (rwidth >= (1u << 24) && rcodes >= 1024));
+  bool tile = c->tile_mode != 0 && rcodes >= 2 && (c->tile_mode == 2 || (rwidth >= (1u << 24) && rcodes >= 1024));
   int shiftF = 0, shift1 = 0;
   uint32_t nbinsF = 0, nb1 = 0;
   if (tile) {

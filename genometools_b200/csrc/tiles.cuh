@@ -293,8 +293,12 @@ __global__ void __launch_bounds__(TS_THREADS, 2) k_tile_sort(Text<BITS> T, PartO
         const uint32_t i = i0 + u * TS_THREADS;
         key[u] = 0;
         if (i < cnt) {
-          const uint64_t q = (uint64_t)(uint32_t)r[u] + pl;
-          key[u] = recL ? make_key_known<BITS>(T, q, (unsigned)(r[u] >> 58) - pl) : make_key<BITS>(T, q);
+          // buckets that cannot be finished here (more slots than a warp sorts) are only inserted: no gather
+          const uint32_t f = (uint32_t)(rec_code(r[u], recL) - c0);
+          if (s_lb[f + 1] - s_lb[f] <= SORT_MAXBUCKET) {
+            const uint64_t q = (uint64_t)(uint32_t)r[u] + pl;
+            key[u] = recL ? make_key_known<BITS>(T, q, (unsigned)(r[u] >> 58) - pl) : make_key<BITS>(T, q);
+          }
         }
       }
 #pragma unroll
@@ -319,10 +323,11 @@ __global__ void __launch_bounds__(TS_THREADS, 2) k_tile_sort(Text<BITS> T, PartO
         const uint32_t *src = s_pos + ls;
         const uint64_t *keys = s_key + ls;
         bool clean = true;                              // sorted and free of ties
-        if (cf <= 32) clean = warp_sort_any<BITS, 1>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
-        else if (cf <= 64) clean = warp_sort_any<BITS, 2>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
-        else if (cf <= 96) clean = warp_sort_any<BITS, 3>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
-        else if (cf <= SORT_MAXBUCKET) clean = warp_sort_any<BITS, 4>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        const bool keyed = s_lb[f + 1] - ls <= SORT_MAXBUCKET;   // otherwise the insertion sweep skipped the keys
+        if (keyed && cf <= 32) clean = warp_sort_any<BITS, 1>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else if (keyed && cf <= 64) clean = warp_sort_any<BITS, 2>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else if (keyed && cf <= 96) clean = warp_sort_any<BITS, 3>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else if (keyed && cf <= SORT_MAXBUCKET) clean = warp_sort_any<BITS, 4>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
         else {                                          // too large for a warp: leave it to the global sorters
           for (uint32_t i = lane; i < cf; i += 32) out.sa[start + i] = src[i];
           done = false;

@@ -120,6 +120,19 @@ def test_tile_path_forced(case, parts, levels, monkeypatch):
     _compare(got, want, f"tile/{case}/parts{parts}/levels{levels}")
 
 
+@pytest.mark.parametrize("levels", ["1", "2"])
+def test_tile_path_forced_protein(levels, monkeypatch):
+    """The same path on byte text (sigma = 20, codes are base-20 numbers): most buckets are larger than a warp
+    sorts, so the tile sorter only inserts them (no key gather) and the block sorter finishes them."""
+    monkeypatch.setenv("GTB200_TILE", "2")
+    monkeypatch.setenv("GTB200_TILE_LEVELS", levels)
+    for nseq, pl, parts in ((1500, 3, 1), (3000, 2, 2), (400, 4, 1)):
+        prot = synth.random_protein(nseq, seed=60 + nseq % 7)
+        want = oracle.build(prot, 20, pl)
+        got = sfx.suffixerator(prot, "protein", prefixlength=pl, parts=parts)
+        _compare(got, want, f"tile/protein/{nseq}/pl{pl}/levels{levels}")
+
+
 @pytest.mark.parametrize("doubling", ["0", "1"])
 @pytest.mark.parametrize("case", ["repeat_rich", "duplicate", "genome_like", "polyT", "maxbucket0"])
 def test_refinement_modes(case, doubling, monkeypatch):
