@@ -295,7 +295,7 @@ __global__ void __launch_bounds__(TS_THREADS, 2) k_tile_sort(Text<BITS> T, PartO
         if (i < cnt) {
           // buckets that cannot be finished here (more slots than a warp sorts) are only inserted: no gather
           const uint32_t f = (uint32_t)(rec_code(r[u], recL) - c0);
-          if (s_lb[f + 1] - s_lb[f] <= SORT_MAXBUCKET) {
+          if (BITS == 2 || s_lb[f + 1] - s_lb[f] <= SORT_MAXBUCKET) {   // DNA buckets are small by choice of pl: always keyed
             const uint64_t q = (uint64_t)(uint32_t)r[u] + pl;
             key[u] = recL ? make_key_known<BITS>(T, q, (unsigned)(r[u] >> 58) - pl) : make_key<BITS>(T, q);
           }
@@ -323,7 +323,7 @@ __global__ void __launch_bounds__(TS_THREADS, 2) k_tile_sort(Text<BITS> T, PartO
         const uint32_t *src = s_pos + ls;
         const uint64_t *keys = s_key + ls;
         bool clean = true;                              // sorted and free of ties
-        const bool keyed = s_lb[f + 1] - ls <= SORT_MAXBUCKET;   // otherwise the insertion sweep skipped the keys
+        const bool keyed = BITS == 2 || s_lb[f + 1] - ls <= SORT_MAXBUCKET;   // otherwise the insertion sweep skipped the keys
         if (keyed && cf <= 32) clean = warp_sort_any<BITS, 1>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
         else if (keyed && cf <= 64) clean = warp_sort_any<BITS, 2>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
         else if (keyed && cf <= 96) clean = warp_sort_any<BITS, 3>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
