@@ -18,12 +18,20 @@
 //   mask : bitmap, bit (i&63) of word i>>6 (LSB first) is 1 iff position i holds a wildcard or
 //          separator; all bits >= totallength are 1 (the virtual end is a special, GT_UNIQUEINT,
 //          src/core/encseq.h:640).
+//   gather: one 16-byte record per text word, {word i, word i+1}: the key window of any suffix (at most
+//          SPW-1 symbols of offset + W symbols) lies inside the record of the word it starts in, so the
+//          sorters fetch it with ONE aligned 128-bit load instead of two 64-bit ones.  For BITS=2 bit 0
+//          of the second word (its last base is never part of a key) says whether any of the record's
+//          first 59 positions is special; if not, the key needs no bitmap access either.  Costs a
+//          second copy of the text (n/2 bytes for DNA), pays for itself in the sort kernels, whose
+//          limit is the L1 tag rate of scattered loads.  Optional (g == nullptr: not built).
 // Both arrays are padded with two extra words so a 64-bit window may start at any position <= n.
 // ---------------------------------------------------------------------------------------------
 template <int BITS>
 struct Text {
   const uint64_t *__restrict__ w;
   const uint64_t *__restrict__ m;
+  const ulonglong2 *__restrict__ g;
   static constexpr int SPW = 64 / BITS;
   static constexpr int W = 56 / BITS;   // symbols per sort key (low byte of the key is a tag)
 
@@ -33,6 +41,21 @@ struct Text {
     const unsigned off = (unsigned)(p % SPW) * BITS;
     const uint64_t hi = __ldg(w + i), lo = __ldg(w + i + 1);
     return off ? (hi << off) | (lo >> (64 - off)) : hi;
+  }
+  // the same window through the gather table (only its leading W symbols are exact); special: the record
+  // holds a special somewhere, the caller consults the bitmap (BITS=2 only; byte text shows specials itself)
+  // g == nullptr (table not built: it would push the text out of L2, see open_impl): two 64-bit loads, and
+  // for BITS=2 the bitmap decides.
+  __device__ __forceinline__ uint64_t keywin(uint64_t p, bool &special) const {
+    const unsigned off = (unsigned)(p % SPW) * BITS;
+    if (g == nullptr) {
+      const uint64_t hi = __ldg(w + p / SPW), lo = __ldg(w + p / SPW + 1);
+      special = BITS == 2;
+      return off ? (hi << off) | (lo >> (64 - off)) : hi;
+    }
+    const ulonglong2 r = __ldg(g + p / SPW);
+    special = BITS == 2 && (r.y & 1ull);
+    return off ? (r.x << off) | (r.y >> (64 - off)) : r.x;
   }
   // bit j = 1 iff position p+j is special, j = 0..63
   __device__ __forceinline__ uint64_t maskwin(uint64_t p) const {
@@ -58,7 +81,9 @@ template <int BITS>
 __device__ __forceinline__ uint64_t make_key(const Text<BITS> &T, uint64_t q) {
   constexpr int W = Text<BITS>::W;
   unsigned avail;
-  const uint64_t win = T.window(q);
+  bool special;
+  const uint64_t win = T.keywin(q, special);
+  if (BITS == 2 && !special) return (win >> 8) << 8;      // W real symbols, tag 0
   if (BITS == 8) {
     // byte text: a special (and everything from position n on) is stored as 0xff/0xfe, real symbols are < 254,
     // so the window itself tells where the first special is - no bitmap access.  z has a zero 7-bit field
@@ -85,7 +110,8 @@ template <int BITS>
 __device__ __forceinline__ uint64_t make_key_known(const Text<BITS> &T, uint64_t q, unsigned avail) {
   constexpr int W = Text<BITS>::W;
   if (avail > (unsigned)W) avail = W;
-  uint64_t x = T.window(q) >> 8;
+  bool special;
+  uint64_t x = T.keywin(q, special) >> 8;
   if (avail < (unsigned)W) {
     const unsigned padbits = (W - avail) * BITS;
     x |= (~0ull) >> (64 - padbits);

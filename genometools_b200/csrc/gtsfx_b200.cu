@@ -89,6 +89,7 @@ struct gtb200_ctx {
   uint64_t n;
   uint64_t ntextwords, nmaskwords;
   uint64_t *d_text, *d_mask;
+  ulonglong2 *d_gather;      // {word i, word i+1} per text word (common.cuh)
   gtb200_range *d_ranges;
   uint64_t nranges;
   uint32_t *d_rangeoff;      // [nranges+1] exclusive scan of range lengths (tail paging)
@@ -430,6 +431,24 @@ __global__ void k_pack_bytes(const uint8_t *__restrict__ enc, uint64_t n, uint64
     text[t * (64 / SPW) + wq] = word;
   }
   mask[t] = mw;
+}
+
+// gather table (common.cuh): record i = {word i, word i+1}; BITS=2: bit 0 of the second word = any special among
+// the record's first 59 positions
+template <int BITS>
+__global__ void k_build_gather(const uint64_t *__restrict__ text, const uint64_t *__restrict__ mask, uint64_t nrec,
+                               ulonglong2 *__restrict__ g) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nrec) return;
+  ulonglong2 r;
+  r.x = text[i];
+  r.y = text[i + 1];
+  if (BITS == 2) {
+    const uint64_t m0 = i >> 1;
+    const uint64_t mw = (i & 1) ? (mask[m0] >> 32) | (mask[m0 + 1] << 32) : mask[m0];
+    r.y = (r.y & ~1ull) | ((mw & ((1ull << 59) - 1ull)) ? 1ull : 0ull);
+  }
+  g[i] = r;
 }
 
 // Readmodes (core/readmode_api.h:24-27): the index of `-dir rev|cpl|rcl` is the index of the reversed and/or
@@ -1949,6 +1968,7 @@ static Text<BITS> text_of(gtb200_ctx *c) {
   Text<BITS> T;
   T.w = c->d_text;
   T.m = c->d_mask;
+  T.g = c->d_gather;
   return T;
 }
 
@@ -2076,6 +2096,22 @@ static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
     ProfScope ps(c, KC_PREP);
     const uint64_t tailwords = c->nmaskwords - (n >> 6);
     k_mask_tail<<<grid_for(tailwords, 64), 64, 0, c->stream>>>(c->d_mask, n, c->nmaskwords);
+  }
+  // The sorters' gather table, built after the bitmap is final (ranges, readmode transform, tail bits) - only while
+  // it is small enough (<= 64 MB) to stay in the 126 MB L2 next to the text and the streams passing through.
+  // Measured: 4.6 Mbp sort 92 -> 71 us with it; at 250 Mbp (125 MB table) it evicts the text and costs 9 %;
+  // at 3.1 Gbp neither copy fits, DRAM fetches 64 bytes per random access either way: no difference.
+  // GTB200_GATHER = 0 never, 2 always (testing knob).
+  int gather_mode = 1;
+  if (const char *eg = getenv("GTB200_GATHER")) gather_mode = atoi(eg);
+  const uint64_t gather_bytes = (c->ntextwords - 1) * sizeof(ulonglong2);
+  c->d_gather = nullptr;
+  if (gather_mode == 2 || (gather_mode == 1 && gather_bytes <= (64ull << 20))) {
+    const uint64_t nrec = c->ntextwords - 1;
+    CK(dmalloc(c, &c->d_gather, nrec * sizeof(ulonglong2)));
+    ProfScope ps(c, KC_PREP);
+    if (c->bits == 2) k_build_gather<2><<<grid_for(nrec, 256), 256, 0, c->stream>>>(c->d_text, c->d_mask, nrec, c->d_gather);
+    else k_build_gather<8><<<grid_for(nrec, 256), 256, 0, c->stream>>>(c->d_text, c->d_mask, nrec, c->d_gather);
   }
   // tail paging table: exclusive scan of range lengths; total = specialcharacters
   CK(dmalloc(c, &c->d_rangeoff, (c->nranges + 2) * 4));

@@ -364,6 +364,30 @@ def test_suf_image_from_sorters(fused, monkeypatch):
     assert gotr["fallback_suffixes"] > 0
 
 
+@pytest.mark.parametrize("tile", ["1", "2"])
+@pytest.mark.parametrize("gather", ["0", "2"])
+def test_gather_table_modes(gather, tile, monkeypatch):
+    """Keys fetched through the 16-byte gather table (one load, bitmap only for records that hold a special) or
+    through two text words + bitmap (table not built): same index, on the direct and on the tile path, with
+    specials at every offset of a record, for DNA, protein and a reversed readmode."""
+    monkeypatch.setenv("GTB200_GATHER", gather)
+    monkeypatch.setenv("GTB200_TILE", tile)
+    rng = np.random.default_rng(77)
+    enc = rng.integers(0, 4, size=120_000, dtype=np.uint8)
+    enc[rng.integers(0, enc.shape[0], size=3000)] = 254          # single wildcards everywhere
+    enc[5000:5070] = 254
+    enc[np.arange(20_000, 26_000, 97)] = 255                     # separators at drifting record offsets
+    want = oracle.build(enc, 4)
+    _compare(sfx.suffixerator(enc, "dna", parts=2), want, f"gather{gather}/tile{tile}/dna")
+    wantr = oracle.build(_apply_readmode(enc, 3), 4)
+    _compare(sfx.suffixerator(enc, "dna", readmode=3), wantr, f"gather{gather}/tile{tile}/rcl")
+    prot = synth.random_protein(800, seed=78)
+    wantp = oracle.build(prot, 20, 3)
+    _compare(sfx.suffixerator(prot, "protein", prefixlength=3), wantp, f"gather{gather}/tile{tile}/protein")
+    rep = synth.repeat_rich_dna(unit=3000, copies=7, seed=79)
+    _compare(sfx.suffixerator(rep, "dna"), oracle.build(rep, 4), f"gather{gather}/tile{tile}/repeats")
+
+
 def _apply_readmode(enc, readmode):
     e = enc[::-1].copy() if readmode in (1, 3) else enc.copy()
     return np.where(e < 4, 3 - e, e).astype(np.uint8) if readmode in (2, 3) else e
