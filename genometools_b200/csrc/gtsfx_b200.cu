@@ -56,9 +56,10 @@ extern "C" int gtb200_device_count(void) {
 // context
 // ---------------------------------------------------------------------------------------------
 enum KClass { KC_PREP = 0, KC_COUNT, KC_SCAN, KC_PADDED, KC_SCATTER, KC_SORT, KC_REFINE, KC_RADIX,
-              KC_BOUNDARY, KC_WIDEN, KC_TAIL, KC_NUM };
+              KC_BOUNDARY, KC_WIDEN, KC_TAIL, KC_INIT, KC_SORTMED, KC_NUM };
 static const char *const kclass_names[KC_NUM] = {"prep", "count", "scan", "padded", "scatter", "sort_lcp",
-                                                 "refine", "radix", "boundary", "widen", "tail"};
+                                                 "refine", "radix", "boundary", "widen", "tail", "part_init",
+                                                 "sort_medium"};
 
 struct PartStats {          // lives in device memory, mirrored to pinned host memory at sync points
   unsigned long long lcpsum;
@@ -2648,7 +2649,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
   uint32_t *fbb = c->d_fbbits + ((lo - pmin) >> 5);
   if (rwidth == 0) return 0;
   if (!first_of_part) {                       // k_part_init zeroed the statistics for the first range
-    ProfScope ps(c, KC_SORT);
+    ProfScope ps(c, KC_INIT);
     k_reset_medcount<<<1, 1, 0, c->stream>>>(c->d_stats);
   }
   // ---- tile path (DNA): staged partition into shared-memory sized bins, then sort inside the tile ----
@@ -2784,7 +2785,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
                                                                           c->d_medlist, medmax, tile ? 1 : 0, fbwords);
   }
   if (c->sort_maxbucket == SORT_MAXBUCKET && rwidth > SORT_MAXBUCKET) {
-    ProfScope ps(c, KC_SORT);
+    ProfScope ps(c, KC_SORTMED);
     const size_t smem = MED_SMEM;
     CK(cudaFuncSetAttribute(k_sort_medium<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_sort_medium<BITS><<<148 * 8, 256, smem, c->stream>>>(T, fin, c->d_lb, c->d_cursor, c->d_medlist, lo, c->cp.pl,
@@ -2861,7 +2862,7 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
     }
   }
   {
-    ProfScope ps(c, KC_SCATTER);
+    ProfScope ps(c, KC_INIT);
     k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, 2 * fbwords,
                                                               c->d_stats, c->d_lcp);
   }
