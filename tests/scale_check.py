@@ -47,10 +47,15 @@ def main():
     ap.add_argument("--workload", default="chr1")
     ap.add_argument("--scale", type=int, default=1)
     ap.add_argument("--parts", type=int, default=1)
+    ap.add_argument("--shrink", type=int, default=1, help="1/D of the named size (protein at 1/16 is 62 M residues)")
     ap.add_argument("--reference", action="store_true")
     ap.add_argument("--samples", type=int, default=20000)
     args = ap.parse_args()
     t0 = time.time()
+    import bench
+    bench.SHRINK = max(1, args.shrink)
+    if args.scale > 8:
+        raise SystemExit("--scale multiplies the workload (N-GPU weak scaling); use --shrink to run a fraction")
     enc, alphabet = make_workload(args.workload, args.scale)
     n = enc.shape[0]
     print(f"workload {args.workload}: n={n} specials={int((enc >= 254).sum())} gen {time.time()-t0:.1f}s", flush=True)
