@@ -112,6 +112,9 @@ struct gtb200_ctx {
   int pipeline;              // 1 = overlap D2H of finished slices with the sort of the next (GTB200_PIPELINE, testing knob)
   cudaStream_t copy_stream;
   cudaEvent_t slice_ev[8];
+  cudaStream_t side_stream;  // small kernels that are independent of the main chain (special-padded suffixes) run beside it
+  cudaEvent_t side_ev[2];
+  int overlap;               // GTB200_OVERLAP=0 keeps everything on one stream (testing knob)
   int tile_mode;             // 0 off, 1 automatic, 2 forced (GTB200_TILE, testing knob)
   int tile_levels;           // 0 automatic, 1/2 forced (GTB200_TILE_LEVELS, testing knob)
   uint64_t *d_recB;          // second record buffer of the tile path (two partition levels)
@@ -204,7 +207,7 @@ struct ProfScope {
 static std::mutex g_pool_mu;
 static std::vector<PoolBlock> g_pool[64];
 static std::vector<void *> g_pinned_pool;
-struct StreamSet { cudaStream_t main, copy; cudaEvent_t ev[8]; };
+struct StreamSet { cudaStream_t main, copy, side; cudaEvent_t ev[8], sev[2]; };
 static std::vector<StreamSet> g_stream_pool[64];   // streams and events of closed contexts, reused by the next open
 
 static void pool_release_device(int dev) {   // caller holds g_pool_mu
@@ -277,6 +280,7 @@ extern "C" void gtb200_release_cached_memory(void) {
     for (auto &ss : g_stream_pool[d]) {
       cudaStreamDestroy(ss.main);
       if (ss.copy) { for (int k = 0; k < 8; ++k) cudaEventDestroy(ss.ev[k]); cudaStreamDestroy(ss.copy); }
+      if (ss.side) { for (int k = 0; k < 2; ++k) cudaEventDestroy(ss.sev[k]); cudaStreamDestroy(ss.side); }
     }
     g_stream_pool[d].clear();
   }
@@ -1930,6 +1934,7 @@ static void free_ctx(gtb200_ctx *c) {
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->l2_window) cudaCtxResetPersistingL2Cache();
   if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
+  if (c->side_stream) cudaStreamSynchronize(c->side_stream);
   {
     std::lock_guard<std::mutex> lock(g_pool_mu);
     for (auto &b : c->blocks) g_pool[c->device].push_back(b);
@@ -1942,11 +1947,14 @@ static void free_ctx(gtb200_ctx *c) {
     if (c->l2_window) {
       cudaStreamDestroy(c->stream);               // carries an access-policy attribute: not reusable
       if (c->copy_stream) { for (int k = 0; k < 8; ++k) cudaEventDestroy(c->slice_ev[k]); cudaStreamDestroy(c->copy_stream); }
+      if (c->side_stream) { for (int k = 0; k < 2; ++k) cudaEventDestroy(c->side_ev[k]); cudaStreamDestroy(c->side_stream); }
     } else {
       StreamSet ss;
       ss.main = c->stream;
       ss.copy = c->copy_stream;
+      ss.side = c->side_stream;
       for (int k = 0; k < 8; ++k) ss.ev[k] = c->slice_ev[k];
+      for (int k = 0; k < 2; ++k) ss.sev[k] = c->side_ev[k];
       std::lock_guard<std::mutex> lock(g_pool_mu);
       g_stream_pool[c->device].push_back(ss);
     }
@@ -2186,7 +2194,9 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
       g_stream_pool[device].pop_back();
       c->stream = ss.main;
       c->copy_stream = ss.copy;
+      c->side_stream = ss.side;
       for (int k = 0; k < 8; ++k) c->slice_ev[k] = ss.ev[k];
+      for (int k = 0; k < 2; ++k) c->side_ev[k] = ss.sev[k];
     }
   }
   if (!c->stream && cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
@@ -2200,6 +2210,8 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
   }
   c->pipeline = 1;
   if (const char *e7 = getenv("GTB200_PIPELINE")) c->pipeline = atoi(e7);
+  c->overlap = 1;
+  if (const char *e9 = getenv("GTB200_OVERLAP")) c->overlap = atoi(e9);
   c->fused_widen = 1;
   if (const char *e8 = getenv("GTB200_FUSED_WIDEN")) c->fused_widen = atoi(e8);
   c->doubling = 1;
@@ -2211,6 +2223,30 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
   if (const char *e3 = getenv("GTB200_TWOLEVEL_BYTES")) c->twolevel_bytes = strtoull(e3, nullptr, 10);   // testing knob
   if (open_impl(c, seq)) { free_ctx(c); return -1; }
   *out = c;
+  return 0;
+}
+
+// Side stream: fork = it waits for everything issued on the main stream so far, join = the main stream waits for it.
+// Off while kernel classes are being timed (their events sit on the main stream).
+static bool side_usable(gtb200_ctx *c) {
+  if (!c->overlap || c->prof_on) return false;
+  if (c->side_stream) return true;
+  if (cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking) != cudaSuccess) { c->side_stream = nullptr; return false; }
+  for (int k = 0; k < 2; ++k)
+    if (cudaEventCreateWithFlags(&c->side_ev[k], cudaEventDisableTiming) != cudaSuccess) {
+      c->overlap = 0;                       // stay on one stream for the rest of this context's life
+      return false;
+    }
+  return true;
+}
+static int side_fork(gtb200_ctx *c) {
+  CK(cudaEventRecord(c->side_ev[0], c->stream));
+  CK(cudaStreamWaitEvent(c->side_stream, c->side_ev[0], 0));
+  return 0;
+}
+static int side_join(gtb200_ctx *c) {
+  CK(cudaEventRecord(c->side_ev[1], c->side_stream));
+  CK(cudaStreamWaitEvent(c->stream, c->side_ev[1], 0));
   return 0;
 }
 
@@ -2238,6 +2274,9 @@ static int count_impl(gtb200_ctx *c, bool need_host_values, uint64_t pos_lo, uin
   uint32_t *hist_or_null = padded_counts ? c->d_lb : nullptr;
   if (phase != 2) {
   CK(cudaMemsetAsync(c->d_lb, 0, (tablewords + (tablewords & 1)) * 4 + 64, c->stream));   // tables + persistent counters
+  // the short list of special-padded suffixes is built beside the k-mer count (both only add into the zeroed tables)
+  const bool beside = small && side_usable(c);
+  if (beside && side_fork(c)) return -1;
   if (pos_hi > pos_lo) {
     // A table larger than L2 is filled slice by slice (64 MB of counters per pass over the text), so
     // that the RED.ADDs always hit L2-resident lines; the text scan itself is cheap (n/4 bytes).
@@ -2256,8 +2295,10 @@ static int count_impl(gtb200_ctx *c, bool need_host_values, uint64_t pos_lo, uin
   // special-padded suffixes
   if (small) {
     ProfScope ps(c, KC_PADDED);
-    k_padded_small<BITS><<<1, 256, 0, c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, hist_or_null, c->d_csc, c->d_dist,
-                                                   c->d_padkey, c->d_padpos, c->d_persist);
+    k_padded_small<BITS><<<1, 256, 0, beside ? c->side_stream : c->stream>>>(T, c->cp, n, c->d_ranges, c->nranges, hist_or_null,
+                                                                             c->d_csc, c->d_dist, c->d_padkey, c->d_padpos,
+                                                                             c->d_persist);
+    if (beside && side_join(c)) return -1;
   } else {
     {
       ProfScope ps(c, KC_PADDED);
@@ -2742,6 +2783,16 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
   // then write the .suf image themselves and k_widen is not launched.  A later refinement redoes the image.
   PartOut fin = out;
   if (!tile && !twolevel && c->fused_widen) fin.sa64 = c->d_suf64;
+  // special-padded suffixes go to the right end of their buckets: slots no other kernel of the range writes, so
+  // the placement runs beside the insertion (joined before the bucket borders are computed)
+  bool padded_beside = false;
+  if (c->padcap > 1) {
+    padded_beside = !tile && side_usable(c);
+    if (padded_beside && side_fork(c)) return -1;
+    ProfScope ps(c, KC_PADDED);
+    k_place_padded<<<grid_for(c->padcap, 256), 256, 0, padded_beside ? c->side_stream : c->stream>>>(
+        c->d_padkey, c->d_padpos, c->d_persist, c->d_lb, c->d_csc, c->cp.sigma, c->cp.pl, lo, hi, fin);
+  }
   if (tile) {
     // insertion already done
   } else if (!twolevel) {
@@ -2771,11 +2822,6 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
                                                                      out.partoffset);
     }
   }
-  if (c->padcap > 1) {
-    ProfScope ps(c, KC_PADDED);
-    k_place_padded<<<grid_for(c->padcap, 256), 256, 0, c->stream>>>(c->d_padkey, c->d_padpos, c->d_persist, c->d_lb,
-                                                                     c->d_csc, c->cp.sigma, c->cp.pl, lo, hi, fin);
-  }
   {
     ProfScope ps(c, KC_SORT);
     uint64_t warps = rcodes < 148ull * 64 ? rcodes : 148ull * 64;   // 8 blocks of 8 warps per SM
@@ -2791,6 +2837,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
     k_sort_medium<BITS><<<148 * 8, 256, smem, c->stream>>>(T, fin, c->d_lb, c->d_cursor, c->d_medlist, lo, c->cp.pl,
                                                           fbb, fbwords);
   }
+  if (padded_beside && side_join(c)) return -1;
   {
     ProfScope ps(c, KC_BOUNDARY, first_of_part && out.partoffset > 0 ? 2 : 1);
     k_boundary<BITS><<<grid_for(rcodes, 256), 256, 0, c->stream>>>(T, c->cp, out, c->d_lb, c->d_csc, lo, hi);

@@ -388,6 +388,35 @@ def test_gather_table_modes(gather, tile, monkeypatch):
     _compare(sfx.suffixerator(rep, "dna"), oracle.build(rep, 4), f"gather{gather}/tile{tile}/repeats")
 
 
+@pytest.mark.parametrize("overlap", ["0", "1"])
+def test_padded_suffixes_beside_the_main_stream(overlap, monkeypatch):
+    """The list of special-padded suffixes is built beside the k-mer count and placed beside the insertion on a
+    second stream (GTB200_OVERLAP=1, the default): same index with and without, on inputs where those suffixes
+    are many (a special every few bases), with parts, repeatedly on one context."""
+    monkeypatch.setenv("GTB200_OVERLAP", overlap)
+    rng = np.random.default_rng(310)
+    enc = rng.integers(0, 4, size=200_000, dtype=np.uint8)
+    enc[rng.integers(0, enc.shape[0], size=12_000)] = 254
+    enc[rng.integers(0, enc.shape[0], size=300)] = 255
+    want = oracle.build(enc, 4)
+    for parts in (1, 3):
+        _compare(sfx.suffixerator(enc, "dna", parts=parts), want, f"overlap{overlap}/parts{parts}")
+    import ctypes as C
+    L = sfx.load_library()
+    it = sfx.Sfxiterator(4, enc.shape[0], None, 1, enc=enc)           # three passes on the same context
+    width = it.parts[0][2]
+    suf = np.empty(width, dtype=np.uint64)
+    lcp = np.empty(width, dtype=np.uint8)
+    for _ in range(3):
+        suf[:] = 0
+        sfx._check(L.gtb200_count(it.ctx, None, None, None, None))
+        pi = sfx.PartInfo()
+        sfx._check(L.gtb200_sort_part(it.ctx, it.parts[0][0], it.parts[0][1], suf.ctypes.data, 0, lcp.ctypes.data, None, 0,
+                                      C.byref(pi)))
+        assert np.array_equal(suf, want["suf_array"][:width]) and lcp.tobytes() == want["lcp"][:width]
+    it.delete()
+
+
 def _apply_readmode(enc, readmode):
     e = enc[::-1].copy() if readmode in (1, 3) else enc.copy()
     return np.where(e < 4, 3 - e, e).astype(np.uint8) if readmode in (2, 3) else e
