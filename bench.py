@@ -64,8 +64,8 @@ def make_workload(name: str, scale: int):
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from one `ncu --set full`
 # capture of this same command (profiles/r1_ncu_full_ecoli.txt, profiles/r1_ncu_full_chr1.txt)
 NCU_TRAFFIC = {
-    ("ecoli", "scatter"): 7.29e6 + 5.31e6,      # k_kmers<2,1>: the 18 MB suffix array stays in L2 (algorithmic 20 MB)
-    ("ecoli", "sort_lcp"): 20.97e6 + 4.51e6,    # k_sort_buckets
+    ("ecoli", "scatter"): 5.30e6 + 3.31e6,      # k_kmers<2,1>: the 18 MB suffix array stays in L2 (algorithmic 20 MB)
+    ("ecoli", "sort_lcp"): 21.38e6 + 3.00e6,    # k_sort_buckets
     ("chr1", "sort_lcp"): 3.254e9 + 1.197e9,    # k_tile_sort
 }
 
