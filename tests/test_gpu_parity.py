@@ -126,11 +126,30 @@ def test_tile_path_forced_protein(levels, monkeypatch):
     sorts, so the tile sorter only inserts them (no key gather) and the block sorter finishes them."""
     monkeypatch.setenv("GTB200_TILE", "2")
     monkeypatch.setenv("GTB200_TILE_LEVELS", levels)
-    for nseq, pl, parts in ((1500, 3, 1), (3000, 2, 2), (400, 4, 1)):
+    for nseq, pl, parts in ((1500, 3, 1), (3000, 2, 2), (400, 4, 1), (900, 2, 1), (500, 2, 3)):
         prot = synth.random_protein(nseq, seed=60 + nseq % 7)
         want = oracle.build(prot, 20, pl)
         got = sfx.suffixerator(prot, "protein", prefixlength=pl, parts=parts)
         _compare(got, want, f"tile/protein/{nseq}/pl{pl}/levels{levels}")
+
+
+@pytest.mark.parametrize("levels", ["1", "2"])
+def test_tile_path_medium_buckets_dna(levels, monkeypatch):
+    """Buckets of 129..1024 suffixes inside a tile are sorted by one warp with shared-memory merges
+    (warp_sort_medium): all chunk counts, equal-prefix runs (fix-up), runs too long for the fix-up (handed to the
+    global sorters) and specials inside the keys."""
+    monkeypatch.setenv("GTB200_TILE", "2")
+    monkeypatch.setenv("GTB200_TILE_LEVELS", levels)
+    rng = np.random.default_rng(311)
+    for n, pl in ((40_000, 4), (100_000, 4), (200_000, 4), (250_000, 5)):      # ~160 / 390 / 780 / 240 per bucket
+        enc = rng.integers(0, 4, size=n, dtype=np.uint8)
+        enc[rng.integers(0, n, size=n // 500)] = 254
+        want = oracle.build(enc, 4, pl)
+        _compare(sfx.suffixerator(enc, "dna", prefixlength=pl), want, f"tilemed/{n}/pl{pl}/levels{levels}")
+    rep = np.concatenate([np.tile(rng.integers(0, 4, size=41, dtype=np.uint8), 60), rng.integers(0, 4, size=90_000, dtype=np.uint8),
+                          np.tile(rng.integers(0, 4, size=7, dtype=np.uint8), 50), rng.integers(0, 4, size=20_000, dtype=np.uint8)]).astype(np.uint8)
+    want = oracle.build(rep, 4, 4)
+    _compare(sfx.suffixerator(rep, "dna", prefixlength=4, parts=2), want, f"tilemed/runs/levels{levels}")
 
 
 @pytest.mark.parametrize("doubling", ["0", "1"])
