@@ -454,8 +454,9 @@ def main():
             # direct: text read + one 4-byte store; tile path: text read + 8-byte records written once per level
             # and re-read once between levels
             "scatter": text_bytes + (4 * m if not tile else 8 * m + (levels - 1) * 16 * m),
-            # direct: pos in, 8-byte text window, pos out, lcp out; tile path reads an 8-byte record instead of pos
-            "sort_lcp": ((4 if not tile else 8) + 8 + 4 + 1) * m,
+            # direct: pos in, 8-byte text window, pos out, lcp out, .suf entry out; tile path reads an 8-byte record
+            # instead of pos (both paths write the 64-bit image themselves, there is no widening pass)
+            "sort_lcp": ((4 if not tile else 8) + 8 + 4 + 1 + 8) * m,
             "boundary": 8 * ncodes_part,
             "widen": 12 * m,
         }

@@ -2722,7 +2722,9 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
       CK(dmalloc(c, &c->d_bins, binwords * 4));
       c->cap_bins = binwords;
     }
-    if (nb1 && c->part_width > c->cap_recB) {
+    // The records the tile sorter reads always end up in recB, so that the 64-bit buffer is free for the .suf image
+    // the sorters write themselves (with two levels the first one passes through the image buffer, dead by then).
+    if (c->part_width > c->cap_recB) {
       dfree(c, c->d_recB);
       CK(dmalloc(c, &c->d_recB, (c->part_width + 1) * 8));
       c->cap_recB = c->part_width;
@@ -2748,41 +2750,43 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
       if (!nb1) {
         if (reps > 1)
           k_stage_partition_sparse<BITS><<<textblocks, 256, SP_SMEM_SPARSE, c->stream>>>(T, c->cp, c->n, lo, hi, shiftF, nbinsF,
-                                                                                         reps, gcurF, c->d_suf64, recL);
+                                                                                         reps, gcurF, c->d_recB, recL);
         else
           k_stage_partition<BITS, true><<<textblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, lo, hi, shiftF, nbinsF,
                                                                                  nullptr, nullptr, nullptr, nullptr, 0, 0, gcurF,
-                                                                                 c->d_suf64, recL);
+                                                                                 c->d_recB, recL);
       } else {
         k_bins_init<<<grid_for(nb1, 256), 256, 0, c->stream>>>(c->d_lb, lo, shift1, nb1, out.partoffset, gcur1, start1);
         if (reps > 1)
           k_stage_partition_sparse<BITS><<<textblocks, 256, SP_SMEM_SPARSE, c->stream>>>(T, c->cp, c->n, lo, hi, shift1, nb1,
-                                                                                         reps, gcur1, c->d_recB, recL);
+                                                                                         reps, gcur1, c->d_suf64, recL);
         else
           k_stage_partition<BITS, true><<<textblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, lo, hi, shift1, nb1,
                                                                                  nullptr, nullptr, nullptr, nullptr, 0, 0, gcur1,
-                                                                                 c->d_recB, recL);
+                                                                                 c->d_suf64, recL);
         k_chunk_table<<<1, 256, 0, c->stream>>>(start1, gcur1, nb1, blkfirst);
         const unsigned recblocks = (unsigned)(rwidth / SP_CHUNK + nb1 + 1);
         k_stage_partition<BITS, false><<<recblocks, 256, SP_SMEM, c->stream>>>(T, c->cp, c->n, lo, hi, shiftF,
-                                                                               1u << (shift1 - shiftF), c->d_recB, start1, gcur1,
-                                                                               blkfirst, nb1, shift1, gcurF, c->d_suf64, recL);
+                                                                               1u << (shift1 - shiftF), c->d_suf64, start1, gcur1,
+                                                                               blkfirst, nb1, shift1, gcurF, c->d_recB, recL);
       }
     }
     {
       ProfScope ps(c, KC_SORT);
       const unsigned tb = nbinsF < 148u * 2 ? nbinsF : 148u * 2;     // two 512-thread blocks per SM, tiles dealt round-robin
       CK(cudaFuncSetAttribute(k_tile_sort<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM));
-      k_tile_sort<BITS><<<tb, TS_THREADS, TS_SMEM, c->stream>>>(T, out, c->d_lb, c->d_cursor, c->d_suf64, gcurF, lo, hi, shiftF,
+      PartOut tfin = out;
+      if (c->fused_widen) tfin.sa64 = c->d_suf64;          // records are in recB: the image buffer is free
+      k_tile_sort<BITS><<<tb, TS_THREADS, TS_SMEM, c->stream>>>(T, tfin, c->d_lb, c->d_cursor, c->d_recB, gcurF, lo, hi, shiftF,
                                                    nbinsF, c->cp.pl, recL, fbb, fbwords);
     }
     CK(cudaGetLastError());
   }
   const bool twolevel = !tile && rwidth * 4 > c->twolevel_bytes && rcodes >= 4096;
-  // Direct insertion leaves the 64-bit buffer free (the other two paths keep their records in it): the sorters
-  // then write the .suf image themselves and k_widen is not launched.  A later refinement redoes the image.
+  // Direct insertion and the tile path leave the 64-bit buffer free (the old two-level insertion keeps its records in
+  // it): the sorters then write the .suf image themselves and k_widen is not launched.  A later refinement redoes it.
   PartOut fin = out;
-  if (!tile && !twolevel && c->fused_widen) fin.sa64 = c->d_suf64;
+  if (!twolevel && c->fused_widen) fin.sa64 = c->d_suf64;
   // special-padded suffixes go to the right end of their buckets: slots no other kernel of the range writes, so
   // the placement runs beside the insertion (joined before the bucket borders are computed)
   bool padded_beside = false;

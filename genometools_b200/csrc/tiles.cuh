@@ -318,7 +318,7 @@ __global__ void __launch_bounds__(TS_THREADS, 2) k_tile_sort(Text<BITS> T, PartO
       const uint32_t start = rs + ls;
       bool done = true;
       if (cf == 1) {
-        if (lane == 0) out.sa[start] = s_pos[ls];
+        if (lane == 0) put_sa(out, start, s_pos[ls]);
       } else if (cf > 1) {
         const uint32_t *src = s_pos + ls;
         const uint64_t *keys = s_key + ls;
