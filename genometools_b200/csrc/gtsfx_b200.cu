@@ -108,6 +108,7 @@ struct gtb200_ctx {
   uint32_t sort_maxbucket;   // buckets above this size take the refinement path (testing knob)
   uint64_t twolevel_bytes;   // parts whose 4-byte suffix array exceeds this use the two-level insertion
   bool l2_window;            // persisting-L2 window set on the stream
+  bool part_imaged;          // every range of the current part had its 64-bit image written by the sorters
   int fused_widen;           // 1 = direct path writes the 64-bit image from the sorters (GTB200_FUSED_WIDEN, testing knob)
   int pipeline;              // 1 = overlap D2H of finished slices with the sort of the next (GTB200_PIPELINE, testing knob)
   cudaStream_t copy_stream;
@@ -1905,6 +1906,27 @@ __global__ void k_widen(const uint32_t *__restrict__ sa, uint64_t width, uint64_
   if (p == 0) stats->longest = partoffset + r;
 }
 
+// After refinement only the flagged buckets (never sorted, or sorted with tie groups) have a new order: when the
+// sorters wrote the 64-bit image themselves, just those buckets are re-imaged.  One block per 32 codes.
+__global__ void __launch_bounds__(256) k_widen_flagged(const uint32_t *__restrict__ sa, uint64_t *__restrict__ out64,
+                                                       const uint32_t *__restrict__ lb, const uint32_t *__restrict__ fbbits,
+                                                       const uint32_t *__restrict__ tiebits, uint64_t mincode,
+                                                       uint64_t maxcode, uint32_t partoffset, PartStats *stats) {
+  uint32_t bits = fbbits[blockIdx.x] | tiebits[blockIdx.x];
+  while (bits) {
+    const int b = __ffs(bits) - 1;
+    bits &= bits - 1;
+    const uint64_t code = mincode + ((uint64_t)blockIdx.x << 5) + b;
+    if (code > maxcode) break;
+    const uint32_t r0 = lb[code] - partoffset, r1 = lb[code + 1] - partoffset;
+    for (uint32_t r = r0 + threadIdx.x; r < r1; r += 256) {
+      const uint32_t p = sa[r];
+      out64[r] = p;
+      if (p == 0) stats->longest = (uint64_t)partoffset + r;
+    }
+  }
+}
+
 template <typename OUT>
 __global__ void k_tail(const gtb200_range *__restrict__ ranges, const uint32_t *__restrict__ rangeoff,
                        uint64_t nranges, uint64_t specialchars, uint64_t n, uint64_t first, uint64_t count, OUT *out) {
@@ -2787,6 +2809,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
   // it): the sorters then write the .suf image themselves and k_widen is not launched.  A later refinement redoes it.
   PartOut fin = out;
   if (!twolevel && c->fused_widen) fin.sa64 = c->d_suf64;
+  if (!fin.sa64) c->part_imaged = false;
   // special-padded suffixes go to the right end of their buckets: slots no other kernel of the range writes, so
   // the placement runs beside the insertion (joined before the bucket borders are computed)
   bool padded_beside = false;
@@ -2917,6 +2940,7 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
     k_part_init<<<grid_for(ncodes, 256), 256, 0, c->stream>>>(c->d_lb, c->d_cursor, mincode, ncodes, c->d_fbbits, 2 * fbwords,
                                                               c->d_stats, c->d_lcp);
   }
+  c->part_imaged = true;
   for (int k = 0; k < S; ++k) {
     if (enqueue_range<BITS>(c, T, out, mincode, blo[k], blo[k + 1] - 1, boff[k], boff[k + 1] - boff[k], fbwords, k == 0))
       return -1;
@@ -2949,7 +2973,11 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
     }
     {
       ProfScope ps(c, KC_WIDEN);
-      k_widen<<<grid_for(width, 256), 256, 0, c->stream>>>(c->d_sa, width, c->d_suf64, partoffset, c->d_stats);
+      if (c->part_imaged)
+        k_widen_flagged<<<(unsigned)fbwords, 256, 0, c->stream>>>(c->d_sa, c->d_suf64, c->d_lb, c->d_fbbits, c->d_fbbits + fbwords,
+                                                                 mincode, maxcode, (uint32_t)partoffset, c->d_stats);
+      else
+        k_widen<<<grid_for(width, 256), 256, 0, c->stream>>>(c->d_sa, width, c->d_suf64, partoffset, c->d_stats);
     }
     CK(cudaGetLastError());
     if (sync_stats(c)) return -1;
