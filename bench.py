@@ -66,7 +66,7 @@ def make_workload(name: str, scale: int):
 NCU_TRAFFIC = {
     ("ecoli", "scatter"): 5.30e6 + 3.31e6,      # k_kmers<2,1>: the 18 MB suffix array stays in L2 (algorithmic 20 MB)
     ("ecoli", "sort_lcp"): 21.38e6 + 3.00e6,    # k_sort_buckets
-    ("chr1", "sort_lcp"): 3.254e9 + 1.197e9,    # k_tile_sort
+    ("chr1", "sort_lcp"): 4.411e9 + 3.091e9,    # k_tile_sort (writes the 64-bit image too: 29 B x 238 M = 6.9 GB algorithmic)
 }
 
 
