@@ -61,13 +61,31 @@ def make_workload(name: str, scale: int):
     return synth.random_protein(max(1, total // 334), seed=5), "protein"
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from one `ncu --set full`
-# capture of this same command (profiles/r1_ncu_full_ecoli.txt, profiles/r1_ncu_full_chr1.txt)
-NCU_TRAFFIC = {
-    ("ecoli", "scatter"): 5.30e6 + 3.31e6,      # k_kmers<2,1>: the 18 MB suffix array stays in L2 (algorithmic 20 MB)
-    ("ecoli", "sort_lcp"): 21.38e6 + 3.00e6,    # k_sort_buckets
-    ("chr1", "sort_lcp"): 4.411e9 + 3.091e9,    # k_tile_sort (writes the 64-bit image too: 29 B x 238 M = 6.9 GB algorithmic)
-}
+def ncu_traffic(workload: str, kclass: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per step of one kernel class, as profiles/summarize.py extracted it
+    from the ncu launch list of this same command (profiles/ncu_traffic.json: {workload: {class: bytes}}).
+    None when no capture of the current kernels exists - never a typed-in constant."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
+            v = json.load(fh).get(workload, {}).get(kclass)
+        return float(v) if v is not None else None
+    except Exception:
+        return None
+
+
+def full_size_reference(workload: str):
+    """Whole-workload time of the unmodified reference (one thread), recorded when tests/golden/scale_fingerprints.json
+    was generated in the build container - context for the bounded sample timed live on this box."""
+    try:
+        with open(os.path.join(ROOT, "tests", "golden", "scale_fingerprints.json")) as fh:
+            rec = json.load(fh)[workload]
+        t = rec["reference"]["times_s"]
+        path_s = sum(t.get(k, 0.0) for k in ("counting prefix distribution", "inserting suffixes into buckets",
+                                              "sorting the buckets"))
+        return {"where": "build container (not this box), 1 thread", "overall_s": t.get("overall"),
+                "count_insert_sort_s": round(path_s, 2), "suffixes": rec["totallength"] + 1}
+    except Exception:
+        return None
 
 
 def peak_hbm():
@@ -150,6 +168,8 @@ def cpu_baseline(enc, alphabet, budget_n=12_000_000):
         return {"value": (sample.shape[0] + 1) / secs, "unit": "suffixes/s", "cores": 1, "kind": "reference",
                 "sample": f"{what}; oracle/_ref/gt_ref suffixerator -suf -lcp -bck -tis, 1 thread (-lcp forbids -j>1), "
                           f"TIME overall {overall:.2f} s of which count+insert+sort {path_s:.2f} s, wall {wall:.2f} s",
+                # the hot path alone (what `value` covers): count + insert + sort phases of the same run
+                "path_only_value": (sample.shape[0] + 1) / max(path_s, 1e-9),
                 "host_cores_available": os.cpu_count()}
     small = sample[:2_000_000]
     t0 = time.perf_counter()
@@ -204,12 +224,14 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="ecoli", choices=sorted(WORKLOADS))
+    # BASELINE.json quotes the metric on the 3.1 Gbp genome (configs[3]); it fits one B200
+    ap.add_argument("--workload", default="human", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=None)
     ap.add_argument("--skip-e2e", action="store_true", help="exploratory runs only: leaves e2e out of the line")
-    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
-                    help="weak (default): genome = N x the named size; strong: the named genome is split over the N GPUs")
+    ap.add_argument("--scaling", default="strong", choices=["weak", "strong"],
+                    help="strong (default): the named genome is split over the N GPUs by bucket range (BASELINE.json's "
+                         "3.1 Gbp at 1/2/4/8 GPUs); weak: genome = N x the named size (must stay below 2^32 symbols)")
     ap.add_argument("--verify", action="store_true", help="N > 1: compare every rank's part with a single-context run on rank 0")
     ap.add_argument("--shrink", type=int, default=1, help="exploratory: run on 1/D of the named workload size")
     args = ap.parse_args()
@@ -364,6 +386,7 @@ def main():
     dev_ms_instr, _ = timed_pass(args.steps)
     clocks = sampler.stop() if sampler else None
     prof = it.profile()
+    it_diag = it.part_diag()
     it.profile(enable=False)
     t = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -441,33 +464,42 @@ def main():
         text_bytes = n * bits / 8 + n / 8                       # packed text + special bitmap, read once
         m = width
         ncodes_part = maxcode - mincode + 1
-        tile = m >= (1 << 24) and ncodes_part >= 1024 and m // ncodes_part <= 4096   # the library's own rule
-        levels = 1
-        if tile:                                    # same arithmetic as sort_part_impl
-            sh = 0
-            while sh < 10 and ((m << (sh + 1)) // ncodes_part) <= 4608 and (ncodes_part >> (sh + 1)) >= 1:
-                sh += 1
-            levels = 2 if ((ncodes_part - 1) >> sh) + 1 > 1024 else 1
-        algo = {   # algorithmic bytes per step and kernel class (DESIGN.md "Kernels")
+        diag = it_diag                                          # what the library did for the last part (gtb200_part_diag)
+        tile, levels, keyed = bool(diag["tile"]), int(diag["levels"]), bool(diag["keyed"])
+        rec = 16 if keyed else 8                                # bytes per record of the tile path
+        med = int(diag["medium_suffixes"])
+        fb, rounds = int(pinfo.fallback_suffixes), int(pinfo.fallback_rounds)
+        npad = int(diag["padded_suffixes"])
+        algo = {   # algorithmic bytes per step and kernel class
             "count": text_bytes + 4 * numcodes,
             "scan": 8 * numcodes,
-            # direct: text read + one 4-byte store; tile path: text read + 8-byte records written once per level
-            # and re-read once between levels
-            "scatter": text_bytes + (4 * m if not tile else 8 * m + (levels - 1) * 16 * m),
-            # direct: pos in, 8-byte text window, pos out, lcp out, .suf entry out; tile path reads an 8-byte record
-            # instead of pos (both paths write the 64-bit image themselves, there is no widening pass)
-            "sort_lcp": ((4 if not tile else 8) + 8 + 4 + 1 + 8) * m,
+            "padded": 40 * npad + 12 * npad,                    # list built (key+pos in, radix passes aside) and placed
+            # direct: text read + one 4-byte store; tile path: text read + records written once per level and
+            # re-read once between levels
+            "scatter": text_bytes + (4 * m if not tile else rec * m + (levels - 1) * 2 * rec * m),
+            # direct: pos in, 8-byte text window, pos out, lcp out, .suf entry out; tile path reads a record instead
+            # (keyed records bring the 8-byte window with them)
+            "sort_lcp": ((4 + 8 if not tile else (16 if keyed else 8 + 8)) + 4 + 1 + 8) * max(m - med, 0),
+            "sort_medium": (4 + 8 + 4 + 1 + 8) * med,
+            # refinement: per round every open suffix passes ~11 radix passes of (8+4) bytes in and out
+            "refine": fb * max(rounds, 1) * 11 * 24, "radix": fb * max(rounds, 1) * 11 * 24,
             "boundary": 8 * ncodes_part,
             "widen": 12 * m,
+            "tail": 8 * (it.specialcharacters + 1),
+            "part_init": 8 * ncodes_part,
         }
-        kern = {k: v for k, v in prof.items() if v[1] > 0}
+        kern = {k: v for k, v in prof.items() if v[1] > 0 and k != "prep"}
         total_ms = sum(v[0] for v in kern.values())
-        dominant = max((k for k in kern if k in algo), key=lambda k: kern[k][0])
+        dominant = max(kern, key=lambda k: kern[k][0])          # the class with the most device time, whatever it is
         d_ms, d_launches = kern[dominant]
         launches_per_step = max(1, d_launches // args.steps)
         per_launch_s = d_ms * 1e-3 / d_launches
         achieved = algo[dominant] / launches_per_step / per_launch_s / 1e9
         peak, peak_src = peak_hbm()
+        traffic = ncu_traffic(args.workload, dominant) if world == 1 and SHRINK == 1 else None
+        per_class = {k: {"ms": round(v[0] / args.steps, 4),
+                         "frac": round(algo[k] / (v[0] / args.steps * 1e-3) / 1e9 / peak, 4) if v[0] > 0 and k in algo else None}
+                     for k, v in kern.items()}
         line = {
             "metric": "suffixes/sec for SA+LCP", "value": value, "unit": "suffixes/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
@@ -481,8 +513,11 @@ def main():
                        "passes": "value: K un-instrumented steps; kernel_ms_per_step/roofline: K more steps with CUDA events "
                                  "around every kernel class (that bracketing alone costs ~25 % at 4.6 Mbp)",
                        "fallback_suffixes": int(pinfo.fallback_suffixes),
-                       "insertion": ("tile path: staged partition x%d + shared-memory tile sort" % levels) if tile
-                                    else "direct scatter + warp bucket sort"},
+                       "insertion": ("tile path: staged partition x%d (%d-byte records%s) + shared-memory tile sort"
+                                     % (levels, rec, ", key travels with the record" if keyed else "")) if tile
+                                    else "direct scatter + warp bucket sort",
+                       "excluded_from_value": "gtb200_open's one-off device prep (special bitmap, range table, readmode "
+                                              "transform): kernel class prep; e2e includes it"},
             "e2e": None if args.skip_e2e else
                    {"value": (n + 1) / e2e_s, "unit": "suffixes/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "steps": e2e_steps},
@@ -490,7 +525,9 @@ def main():
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak,
-                         "traffic": NCU_TRAFFIC.get((args.workload, dominant)) if world == 1 and SHRINK == 1 else None,
+                         "traffic": (traffic / launches_per_step) if traffic is not None else None,
+                         "traffic_source": "profiles/ncu_traffic.json (ncu launch list of this command)" if traffic is not None else None,
+                         "per_class": per_class,
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": algo[dominant] / launches_per_step,
                          "avg_launch_ms": per_launch_s * 1e3,
@@ -503,6 +540,9 @@ def main():
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(enc, alphabet)
+            full = full_size_reference(args.workload) if SHRINK == 1 else None
+            if full:
+                line["cpu_baseline"]["full_size_run"] = full
         print(json.dumps(line))
     if args.verify and world > 1:
         import hashlib

@@ -15,8 +15,16 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GT_REF = os.path.join(ROOT, "oracle", "_ref", "gt_ref")
 GT_B200 = os.path.join(ROOT, "oracle", "_ref", "gt_b200")
-needs_binaries = pytest.mark.skipif(not (os.path.exists(GT_REF) and os.path.exists(GT_B200)),
-                                    reason="oracle/_ref/gt_ref or gt_b200 not built (make -C oracle; make -C integration)")
+
+
+@pytest.fixture(autouse=True)
+def _binaries_must_exist():
+    """These tests only run with -m gpu, i.e. on the GPU box, where the prebuilt binaries travel with the snapshot
+    (oracle/_ref is git-ignored, not gpurun-ignored).  Their absence is a broken build, not a reason to skip."""
+    for b in (GT_REF, GT_B200):
+        if not (os.path.isfile(b) and os.access(b, os.X_OK)):
+            pytest.fail(f"{b} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` in the build "
+                        "container (make -C oracle ref; make -C integration) before sending the tree to the GPU box")
 
 CASES = {
     "dna_nruns": (lambda: synth.multi_dna_with_nruns(300_000, nseq=6, seed=81), "dna", []),
@@ -46,7 +54,6 @@ def _run(binary, args, cwd):
     return p.stdout
 
 
-@needs_binaries
 @pytest.mark.parametrize("case", sorted(CASES))
 def test_gt_suffixerator_dropin_is_byte_identical(case, tmp_path):
     gen, alphabet, extra = CASES[case]
@@ -68,7 +75,6 @@ def test_gt_suffixerator_dropin_is_byte_identical(case, tmp_path):
         _run(GT_REF, ["sfxmap", "-tis", "-suf", "-lcp", "-bck", "-esa", "b200"], str(tmp_path))
 
 
-@needs_binaries
 def test_dropin_reports_device_errors_through_gterror(tmp_path):
     fasta = str(tmp_path / "in.fna")
     encseq.write_fasta(fasta, encseq.decode_to_fasta_bytes(synth.random_dna(2000, seed=86), "dna"))
