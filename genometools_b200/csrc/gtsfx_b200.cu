@@ -69,6 +69,7 @@ struct PartStats {          // lives in device memory, mirrored to pinned host m
   unsigned long long scan_total;
   unsigned long long scan_total2;
   unsigned long long bsum;       // bucket-boundary part of lcpsum
+  unsigned long long med_elems;  // suffixes in the buckets queued for the block-level sorter
   unsigned int maxdepth;
   unsigned int fb_buckets;
   unsigned int largest;
@@ -118,7 +119,10 @@ struct gtb200_ctx {
   int overlap;               // GTB200_OVERLAP=0 keeps everything on one stream (testing knob)
   int tile_mode;             // 0 off, 1 automatic, 2 forced (GTB200_TILE, testing knob)
   int tile_levels;           // 0 automatic, 1/2 forced (GTB200_TILE_LEVELS, testing knob)
-  uint64_t *d_recB;          // second record buffer of the tile path (two partition levels)
+  uint64_t *d_recB;          // second record buffer of the tile path (two partition levels); 16-byte records when keyed
+  int keyed_mode;            // 0 never, 1 automatic (text larger than L2's share), 2 always (GTB200_KEYED, testing knob)
+  uint64_t cap_suf64_bytes;
+  uint64_t diag[8];          // last part: [0] tile path, [1] partition levels, [2] keyed records, [3] suffixes in medium buckets
   uint32_t *d_isa;           // rank array of the prefix-doubling refinement (n+1 entries)
   uint64_t cap_isa;
   int doubling;              // 1 = prefix doubling when the part is the whole array (GTB200_DOUBLING, testing knob)
@@ -1213,7 +1217,10 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
     bool ok = false;
     if (cnt > maxbucket) {
       if (cnt <= medmax) {                 // too large for one warp: queue for k_sort_medium
-        if (lane == 0) medlist[atomicAdd(&out.stats->med_count, 1u)] = (uint32_t)c;
+        if (lane == 0) {
+          medlist[atomicAdd(&out.stats->med_count, 1u)] = (uint32_t)c;
+          atomicAdd(&out.stats->med_elems, (unsigned long long)cnt);
+        }
         continue;
       }
       ok = false;
@@ -1243,6 +1250,7 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
 }
 
 #include "tiles.cuh"
+#include "keyed.cuh"
 
 // Buckets of 129..MED_MAX suffixes: one block per bucket.  Full 64-bit keys and positions are parked in shared
 // memory by slot; what is sorted is one 32-bit word per suffix, (20 leading key bits << 12) | slot:
@@ -2240,6 +2248,8 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
   if (const char *e6 = getenv("GTB200_DOUBLING")) c->doubling = atoi(e6);
   c->tile_mode = 1;
   if (const char *e4 = getenv("GTB200_TILE")) c->tile_mode = atoi(e4);
+  c->keyed_mode = 1;
+  if (const char *e10 = getenv("GTB200_KEYED")) c->keyed_mode = atoi(e10);
   if (const char *e5 = getenv("GTB200_TILE_LEVELS")) c->tile_levels = atoi(e5);
   c->twolevel_bytes = 48ull << 20;
   if (const char *e3 = getenv("GTB200_TWOLEVEL_BYTES")) c->twolevel_bytes = strtoull(e3, nullptr, 10);   // testing knob
@@ -2444,18 +2454,23 @@ extern "C" int gtb200_count_finish(gtb200_ctx *c, uint32_t *leftborder, uint32_t
   return 0;
 }
 
-static int ensure_part_buffers(gtb200_ctx *c, uint64_t width, uint64_t ncodes_in_part) {
-  if (width > c->cap_width) {
+static int ensure_part_buffers(gtb200_ctx *c, uint64_t width, uint64_t ncodes_in_part, bool keyed) {
+  // keyed tile path: the level-1 records (16 bytes per suffix) pass through the image buffer, which is dead until
+  // the tile sorter writes the 8-byte .suf entries into its first half
+  const uint64_t suf64_bytes = (width + 1) * (keyed ? 16 : 8);
+  if (width > c->cap_width || suf64_bytes > c->cap_suf64_bytes) {
     dfree(c, c->d_sa);
     dfree(c, c->d_lcp);
     dfree(c, c->d_suf64);
     dfree(c, c->d_medlist);
-    c->d_sa = nullptr; c->d_lcp = nullptr; c->d_suf64 = nullptr; c->cap_width = 0;
+    c->d_sa = nullptr; c->d_lcp = nullptr; c->d_suf64 = nullptr; c->d_medlist = nullptr;
+    c->cap_width = 0; c->cap_suf64_bytes = 0;
     CK(dmalloc(c, &c->d_sa, (width + 1) * 4));
     CK(dmalloc(c, &c->d_lcp, width + 1));
-    CK(dmalloc(c, &c->d_suf64, (width + 1) * 8));
+    CK(dmalloc(c, &c->d_suf64, suf64_bytes));
     CK(dmalloc(c, &c->d_medlist, (width / (SORT_MAXBUCKET + 1) + 2) * 4));
     c->cap_width = width;
+    c->cap_suf64_bytes = suf64_bytes;
   }
   const uint64_t fbwords = 2 * ((ncodes_in_part + 31) / 32) + 2;   // unsorted-bucket bitmap, then tied-bucket bitmap
   if (fbwords > c->cap_fbwords) {
@@ -2604,6 +2619,8 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
     // ---- prefix doubling on ranks, then LCP of the refined entries by Phi/Kasai in text order ----
     if (c->n + 2 > c->cap_isa) {
       dfree(c, c->d_isa);
+      c->d_isa = nullptr;
+      c->cap_isa = 0;
       CK(dmalloc(c, &c->d_isa, (c->n + 2) * 4));
       c->cap_isa = c->n + 2;
     }
@@ -2707,7 +2724,7 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
 // [roff, roff+rwidth) of the part's buffers.  (lo - part mincode) is a multiple of 32.
 template <int BITS>
 static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out, uint64_t pmin, uint64_t lo, uint64_t hi,
-                         uint64_t roff, uint64_t rwidth, uint64_t fbwords, bool first_of_part) {
+                         uint64_t roff, uint64_t rwidth, uint64_t fbwords, bool first_of_part, bool keyed_ok) {
   const uint64_t rcodes = hi - lo + 1;
   uint32_t *fbb = c->d_fbbits + ((lo - pmin) >> 5);
   if (rwidth == 0) return 0;
@@ -2737,34 +2754,83 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
       nb1 = (uint32_t)(((rcodes - 1) >> shift1) + 1);
     }
   }
+  // records carry min(real length, 63) in their top 6 bits when the code leaves room for it
+  const int recL = (c->numcodes <= (1ull << 26) && c->cp.pl + Text<BITS>::W <= 63) ? 1 : 0;
+  const bool keyed = tile && keyed_ok && BITS == 2 && recL;
   if (tile) {
+    c->diag[0] = 1; c->diag[1] = nb1 ? 2 : 1; c->diag[2] = keyed ? 1 : 0;
     const uint64_t binwords = (uint64_t)nbinsF + 3 * SP_MAXBINS + 64;
     if (binwords > c->cap_bins) {
       dfree(c, c->d_bins);
+      c->d_bins = nullptr;
+      c->cap_bins = 0;
       CK(dmalloc(c, &c->d_bins, binwords * 4));
       c->cap_bins = binwords;
     }
     // The records the tile sorter reads always end up in recB, so that the 64-bit buffer is free for the .suf image
     // the sorters write themselves (with two levels the first one passes through the image buffer, dead by then).
-    if (c->part_width > c->cap_recB) {
+    const uint64_t recB_bytes = (c->part_width + 1) * (keyed ? 16 : 8);
+    if (recB_bytes > c->cap_recB) {
       dfree(c, c->d_recB);
-      CK(dmalloc(c, &c->d_recB, (c->part_width + 1) * 8));
-      c->cap_recB = c->part_width;
+      c->d_recB = nullptr;
+      c->cap_recB = 0;
+      CK(dmalloc(c, &c->d_recB, recB_bytes));
+      c->cap_recB = recB_bytes;
     }
     uint32_t *gcurF = c->d_bins, *gcur1 = gcurF + nbinsF, *start1 = gcur1 + SP_MAXBINS, *blkfirst = start1 + SP_MAXBINS;
-    CK(cudaFuncSetAttribute(k_stage_partition<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SP_SMEM));
-    CK(cudaFuncSetAttribute(k_stage_partition<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SP_SMEM));
-    // blocks of the text-level partition scan reps x 8192 positions when the range covers only 1/reps of the suffixes
+    // blocks of the text-level partition scan reps x chunk positions when the range covers only 1/reps of the suffixes
     int reps = 1;
     if (c->nsort > 0 && rwidth > 0) {
       const uint64_t ratio = c->nsort / rwidth;
       reps = ratio >= 8 ? 8 : ratio >= 2 ? (int)ratio : 1;
     }
+    if (keyed) {
+      // ---- keyed records (keyed.cuh): 16 bytes per suffix, the key travels with the record ----
+      CK(cudaFuncSetAttribute(k_keyed_partition_text<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
+      CK(cudaFuncSetAttribute(k_keyed_partition_text<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
+      CK(cudaFuncSetAttribute(k_keyed_partition_rec, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
+      const unsigned textblocks = grid_for(c->n, (uint64_t)KP_CHUNK * reps);
+      const int whole = (lo == 0 && hi == c->numcodes - 1) ? 1 : 0;
+      ulonglong2 *recX = (ulonglong2 *)c->d_suf64, *recY = (ulonglong2 *)c->d_recB;
+      const Text<2> T2 = text_of<2>(c);
+      {
+        ProfScope ps(c, KC_SCATTER, nb1 ? 5 : 2);
+        k_bins_init<<<grid_for(nbinsF, 256), 256, 0, c->stream>>>(c->d_lb, lo, shiftF, nbinsF, out.partoffset, gcurF,
+                                                                  nullptr);
+        uint32_t *gc = nb1 ? gcur1 : gcurF;
+        const int sh = nb1 ? shift1 : shiftF;
+        const uint32_t nb = nb1 ? nb1 : nbinsF;
+        ulonglong2 *dst = nb1 ? recX : recY;
+        if (nb1) k_bins_init<<<grid_for(nb1, 256), 256, 0, c->stream>>>(c->d_lb, lo, shift1, nb1, out.partoffset, gcur1, start1);
+        if (reps > 1)
+          k_keyed_partition_text<false><<<textblocks, 256, KP_SMEM, c->stream>>>(T2, c->cp.pl, c->n, lo, hi, whole, sh, nb, reps,
+                                                                                 gc, dst);
+        else
+          k_keyed_partition_text<true><<<textblocks, 256, KP_SMEM, c->stream>>>(T2, c->cp.pl, c->n, lo, hi, whole, sh, nb, 1,
+                                                                                gc, dst);
+        if (nb1) {
+          k_keyed_chunk_table<<<1, 256, 0, c->stream>>>(start1, gcur1, nb1, blkfirst);
+          const unsigned recblocks = (unsigned)(rwidth / KP_CHUNK + nb1 + 1);
+          k_keyed_partition_rec<<<recblocks, 512, KP_SMEM, c->stream>>>(lo, shiftF, 1u << (shift1 - shiftF), recX, start1, gcur1,
+                                                                        blkfirst, nb1, shift1, gcurF, recY);
+        }
+      }
+      {
+        ProfScope ps(c, KC_SORT);
+        const unsigned tb = nbinsF < 148u * 2 ? nbinsF : 148u * 2;
+        CK(cudaFuncSetAttribute(k_tile_sort_keyed, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM));
+        PartOut tfin = out;
+        if (c->fused_widen) tfin.sa64 = c->d_suf64;          // the level-1 records in it are dead by now
+        k_tile_sort_keyed<<<tb, TS_THREADS, TS_SMEM, c->stream>>>(T2, tfin, c->d_lb, c->d_cursor, recY, gcurF, lo, hi, shiftF,
+                                                                  nbinsF, c->cp.pl, fbb, fbwords);
+      }
+      CK(cudaGetLastError());
+    } else {
+    CK(cudaFuncSetAttribute(k_stage_partition<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SP_SMEM));
+    CK(cudaFuncSetAttribute(k_stage_partition<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SP_SMEM));
     const unsigned textblocks = grid_for(c->n, (uint64_t)SP_CHUNK * reps);
     if (reps > 1)
       CK(cudaFuncSetAttribute(k_stage_partition_sparse<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SP_SMEM_SPARSE));
-    // records carry min(real length, 63) in their top 6 bits when the code leaves room for it
-    const int recL = (c->numcodes <= (1ull << 26) && c->cp.pl + Text<BITS>::W <= 63) ? 1 : 0;
     {
       ProfScope ps(c, KC_SCATTER, nb1 ? 5 : 2);
       k_bins_init<<<grid_for(nbinsF, 256), 256, 0, c->stream>>>(c->d_lb, lo, shiftF, nbinsF, out.partoffset, gcurF,
@@ -2803,6 +2869,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
                                                    nbinsF, c->cp.pl, recL, fbb, fbwords);
     }
     CK(cudaGetLastError());
+    }
   }
   const bool twolevel = !tile && rwidth * 4 > c->twolevel_bytes && rcodes >= 4096;
   // Direct insertion and the tile path leave the 64-bit buffer free (the old two-level insertion keeps its records in
@@ -2904,7 +2971,12 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
   c->part_width = width;
   c->part_nllv = 0;
   if (width == 0) return 0;
-  if (ensure_part_buffers(c, width, ncodes)) return -1;
+  // keyed records once the packed text (and its bitmap) no longer fit L2 beside the streams passing through:
+  // the tile sorter's one random text access per suffix is then a 64-byte DRAM access
+  const bool keyed_ok = BITS == 2 && c->cp.pow2 && c->cp.pl <= 16 && c->keyed_mode != 0 &&
+                        (c->keyed_mode == 2 || (c->ntextwords + c->nmaskwords) * 8 > (96ull << 20));
+  memset(c->diag, 0, sizeof c->diag);
+  if (ensure_part_buffers(c, width, ncodes, keyed_ok)) return -1;
   PartOut out;
   out.sa = c->d_sa;
   out.sa64 = nullptr;
@@ -2942,7 +3014,8 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
   }
   c->part_imaged = true;
   for (int k = 0; k < S; ++k) {
-    if (enqueue_range<BITS>(c, T, out, mincode, blo[k], blo[k + 1] - 1, boff[k], boff[k + 1] - boff[k], fbwords, k == 0))
+    if (enqueue_range<BITS>(c, T, out, mincode, blo[k], blo[k + 1] - 1, boff[k], boff[k + 1] - boff[k], fbwords, k == 0,
+                            keyed_ok))
       return -1;
     if (S > 1) CK(cudaEventRecord(c->slice_ev[k], c->stream));
   }
@@ -2991,6 +3064,8 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
     if (h_lcp) CK(cudaMemcpyAsync(h_lcp, c->d_lcp, width, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
   }
+  c->diag[3] = c->h_stats->med_elems;
+  c->diag[4] = c->padcap ? c->padcap - 1 : 0;     // upper bound: (special ranges + 1) x (pl - 1)
   info->numoflargelcpvalues = c->h_stats->llv_count;
   info->maxbranchdepth = c->h_stats->maxdepth > c->h_stats->bmax ? c->h_stats->maxdepth : c->h_stats->bmax;
   info->lcptabsum = (double)(c->h_stats->lcpsum + c->h_stats->bsum);
@@ -3077,6 +3152,12 @@ extern "C" int gtb200_tail(gtb200_ctx *c, uint64_t first, uint64_t count, void *
     CK(cudaStreamSynchronize(c->stream));
   }
   return 0;
+}
+
+extern "C" int gtb200_part_diag(gtb200_ctx *c, uint64_t *values, int capacity) {
+  if (!c || !values) return set_error("gtb200_part_diag: null argument");
+  for (int i = 0; i < 8 && i < capacity; ++i) values[i] = c->diag[i];
+  return 8;
 }
 
 extern "C" int gtb200_profile_enable(gtb200_ctx *c, int on) {

@@ -1,0 +1,397 @@
+// Keyed tile path (DNA whose packed text does not fit L2): the records that travel through the two partition
+// levels carry the sort key of their suffix, so the tile sorter never touches the text.
+//
+//   record = 16 bytes {a, k}
+//     a = (min(real symbols ahead, 63) << 58) | (code << 32) | position        (code < 2^26)
+//     k = make_key_known(T, position + pl, real - pl): the 28 bases that follow the prefix, padded with ones
+//         from the first special on, low byte = 28 - (number of real bases among them)      (common.cuh)
+//
+// The level-1 partition reads the text sequentially and has those 28 bases in registers anyway (three
+// consecutive words cover every window of a thread's 16 positions); level 2 and the tile sorter stream the
+// records.  Against the 8-byte records of tiles.cuh this adds 32 bytes of streaming per suffix and removes one
+// random 64-byte DRAM access per suffix (3.1 Gbp: the text is 775 MB, L2 126 MB).
+//
+//   k_keyed_partition_text   block = 256 threads x 16 positions (x reps when the code range selects only a
+//                            fraction of the suffixes); counts per bin in shared memory, one global reservation
+//                            per block and bin, records staged bin by bin and written as contiguous runs.
+//   k_keyed_partition_rec    block = 512 threads x 8 records of one level-1 bin, same scheme.
+//   k_tile_sort_keyed        tiles.cuh's tile sorter with the gather removed.
+// Included by gtsfx_b200.cu after tiles.cuh.
+#pragma once
+
+#define KP_CHUNK 4096                   // records staged per block (64 KB)
+#define KP_PPT 16                       // positions per thread and repetition
+#define KP_MAXREPS 8
+// dynamic shared memory: stage[KP_CHUNK] 16 B | h[SP_MAXBINS] | lstart[SP_MAXBINS] | misc[16]   (72 KB: three blocks per SM)
+#define KP_SMEM (KP_CHUNK * 16 + 2 * SP_MAXBINS * 4 + 64)
+
+// exclusive scan of h[0..nbins) into lstart[] for a block of NT threads (NT = 256 or 512), nbins <= 1024;
+// sm holds NT/32 words
+template <int NT>
+__device__ __forceinline__ uint32_t kp_scan_bins(const uint32_t *h, uint32_t *lstart, uint32_t nbins, uint32_t *sm) {
+  constexpr int PER = SP_MAXBINS / NT;                 // 4 or 2 bins per thread
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  uint32_t v[PER], s = 0;
+#pragma unroll
+  for (int k = 0; k < PER; ++k) {
+    const uint32_t i = threadIdx.x * PER + k;
+    v[k] = i < nbins ? h[i] : 0;
+    s += v[k];
+  }
+  uint32_t x = s;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t y = __shfl_up_sync(GTB_FULL, x, o);
+    if (lane >= o) x += y;
+  }
+  __syncthreads();
+  if (lane == 31) sm[wid] = x;
+  __syncthreads();
+  uint32_t woff = 0, tot = 0;
+#pragma unroll
+  for (int k = 0; k < NT / 32; ++k) {
+    const uint32_t t = sm[k];
+    if (k < wid) woff += t;
+    tot += t;
+  }
+  uint32_t ex = woff + x - s;
+#pragma unroll
+  for (int k = 0; k < PER; ++k) {
+    const uint32_t i = threadIdx.x * PER + k;
+    if (i < nbins) lstart[i] = ex;
+    ex += v[k];
+  }
+  return tot;
+}
+
+// the 16 positions p0..p0+15 of one thread (p0 a multiple of 16): three text words and 80 mask bits
+struct KpWin {
+  uint64_t w0, w1, w2, mw, mw1;
+  unsigned o0;
+};
+
+__device__ __forceinline__ KpWin kp_load(const Text<2> &T, uint64_t p0) {
+  KpWin k;
+  const uint64_t t = p0 >> 5;
+  const unsigned s = (unsigned)(p0 & 63);
+  k.o0 = (unsigned)(p0 & 31);
+  k.w0 = __ldg(T.w + t);
+  k.w1 = __ldg(T.w + t + 1);
+  k.w2 = __ldg(T.w + t + 2);
+  const uint64_t m0 = __ldg(T.m + (p0 >> 6)), m1 = __ldg(T.m + (p0 >> 6) + 1);
+  k.mw = s ? (m0 >> s) | (m1 << (64 - s)) : m0;                       // positions p0 .. p0+63
+  k.mw1 = s ? (m1 >> s) | (__ldg(T.m + (p0 >> 6) + 2) << (64 - s)) : m1;   // positions p0+64 .. p0+127
+  return k;
+}
+
+__device__ __forceinline__ uint64_t kp_code(const KpWin &k, int i, unsigned pl) {
+  const unsigned o = k.o0 + i;
+  const uint64_t win = o ? (k.w0 << (2 * o)) | (k.w1 >> (64 - 2 * o)) : k.w0;
+  return win >> (64 - 2 * pl);
+}
+
+// bit i = position p0+i starts a suffix with >= pl real symbols whose code lies in [mincode, maxcode]
+__device__ __forceinline__ uint32_t kp_select(const KpWin &k, unsigned pl, uint64_t mincode, uint64_t maxcode, bool whole) {
+  const uint64_t plmask = (1ull << pl) - 1ull;
+  uint32_t sel = 0;
+#pragma unroll
+  for (int i = 0; i < KP_PPT; ++i) {
+    if (((k.mw >> i) & plmask) != 0) continue;
+    if (!whole) {
+      const uint64_t code = kp_code(k, i, pl);
+      if (code < mincode || code > maxcode) continue;
+    }
+    sel |= 1u << i;
+  }
+  return sel;
+}
+
+// the 16-byte record of position p0+i (selected, so it has >= pl real symbols ahead)
+__device__ __forceinline__ ulonglong2 kp_record(const KpWin &k, int i, uint64_t p0, unsigned pl, uint64_t code) {
+  constexpr unsigned W = Text<2>::W;
+  const uint64_t m = i ? (k.mw >> i) | (k.mw1 << (64 - i)) : k.mw;          // specials ahead of p0+i
+  const unsigned L = m ? (unsigned)(__ffsll((long long)m) - 1) : 63u;
+  const unsigned Lc = L < 63u ? L : 63u;
+  const unsigned ko = k.o0 + i + pl;                                         // 1 .. 31+pl
+  uint64_t kw;
+  if (ko < 32) kw = (k.w0 << (2 * ko)) | (k.w1 >> (64 - 2 * ko));
+  else if (ko == 32) kw = k.w1;
+  else kw = (k.w1 << (2 * (ko - 32))) | (k.w2 >> (64 - 2 * (ko - 32)));
+  unsigned avail = Lc - pl;
+  if (avail > W) avail = W;
+  uint64_t x = kw >> 8;
+  if (avail < W) x |= (~0ull) >> (64 - (W - avail) * 2);
+  ulonglong2 r;
+  r.x = ((uint64_t)Lc << 58) | (code << 32) | (uint64_t)(uint32_t)(p0 + i);
+  r.y = (x << 8) | (uint64_t)(W - avail);
+  return r;
+}
+
+// Level 1, from the text.  Block b scans positions [b*reps*4096, (b+1)*reps*4096); bin = (code-mincode)>>shift.
+// DENSE (reps == 1, every block stages at most 4096 records): the thread's text window stays in registers
+// between the counting and the staging pass.
+template <bool DENSE>
+__global__ void __launch_bounds__(256) k_keyed_partition_text(Text<2> T, unsigned pl, uint64_t n, uint64_t mincode,
+                                                               uint64_t maxcode, int whole, int shift, uint32_t nbins,
+                                                               int reps, uint32_t *__restrict__ gcursor,
+                                                               ulonglong2 *__restrict__ rec_out) {
+  extern __shared__ __align__(16) unsigned char kp_raw[];
+  ulonglong2 *stage = (ulonglong2 *)kp_raw;
+  uint32_t *h = (uint32_t *)(stage + KP_CHUNK);
+  uint32_t *lstart = h + SP_MAXBINS;                     // local bin starts, then the staging cursors
+  uint32_t *misc = lstart + SP_MAXBINS;
+  for (uint32_t i = threadIdx.x; i < nbins; i += 256) h[i] = 0;
+  __syncthreads();
+  if (DENSE) reps = 1;
+  const uint64_t pbase = (uint64_t)blockIdx.x * reps * KP_CHUNK + (uint64_t)threadIdx.x * KP_PPT;
+  uint32_t selbits[DENSE ? 1 : KP_MAXREPS / 2];          // 16 selection bits per repetition, two repetitions per word
+  KpWin kd;                                               // DENSE: the one window of this thread
+  kd.w0 = kd.w1 = kd.w2 = 0; kd.mw = kd.mw1 = ~0ull; kd.o0 = 0;
+#pragma unroll
+  for (int rep = 0; rep < (DENSE ? 1 : KP_MAXREPS); ++rep) {
+    if ((rep & 1) == 0) selbits[rep >> 1] = 0;
+    if (rep < reps) {
+      const uint64_t p0 = pbase + (uint64_t)rep * KP_CHUNK;
+      if (p0 < n) {
+        const KpWin k = kp_load(T, p0);
+        if (DENSE) kd = k;
+        uint32_t sel = kp_select(k, pl, mincode, maxcode, whole != 0);
+        selbits[rep >> 1] |= sel << ((rep & 1) * 16);
+        while (sel) {
+          const int i = __ffs(sel) - 1;
+          sel &= sel - 1;
+          atomicAdd(&h[(uint32_t)((kp_code(k, i, pl) - mincode) >> shift)], 1u);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  const uint32_t total = kp_scan_bins<256>(h, lstart, nbins, misc);
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < nbins; i += 256) {
+    const uint32_t cnt = h[i];
+    h[i] = cnt ? atomicAdd(&gcursor[i], cnt) - lstart[i] : 0u;      // global index = h[bin] + local index
+  }
+  __syncthreads();
+  const bool staged = total <= KP_CHUNK;
+#pragma unroll
+  for (int rep = 0; rep < (DENSE ? 1 : KP_MAXREPS); ++rep) {
+    uint32_t sel = (selbits[rep >> 1] >> ((rep & 1) * 16)) & 0xffffu;
+    if (sel) {
+      const uint64_t p0 = pbase + (uint64_t)rep * KP_CHUNK;
+      const KpWin k = DENSE ? kd : kp_load(T, p0);
+      while (sel) {
+        const int i = __ffs(sel) - 1;
+        sel &= sel - 1;
+        const uint64_t code = kp_code(k, i, pl);
+        const uint32_t bin = (uint32_t)((code - mincode) >> shift);
+        const ulonglong2 rec = kp_record(k, i, p0, pl, code);
+        const uint32_t r = atomicAdd(&lstart[bin], 1u);
+        if (staged) stage[r] = rec;
+        else rec_out[h[bin] + r] = rec;
+      }
+    }
+  }
+  if (!staged) return;
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < total; i += 256) {
+    const ulonglong2 r = stage[i];
+    const uint32_t bin = (uint32_t)((((r.x >> 32) & REC_CODE_MASK) - mincode) >> shift);
+    __stcs(rec_out + h[bin] + i, r);
+  }
+}
+
+// Level 2, from the records of one level-1 bin.  Block b handles one 4096-record chunk (blk_first = prefix sums of
+// the parents' chunk counts, chunk size KP_CHUNK); bin = child index inside the parent.
+__global__ void __launch_bounds__(512) k_keyed_partition_rec(uint64_t mincode, int shift, uint32_t nbins,
+                                                              const ulonglong2 *__restrict__ rec_in,
+                                                              const uint32_t *__restrict__ seg_start,
+                                                              const uint32_t *__restrict__ seg_end,
+                                                              const uint32_t *__restrict__ blk_first, uint32_t nparents,
+                                                              int parent_shift, uint32_t *__restrict__ gcursor,
+                                                              ulonglong2 *__restrict__ rec_out) {
+  extern __shared__ __align__(16) unsigned char kp_raw[];
+  ulonglong2 *stage = (ulonglong2 *)kp_raw;
+  uint32_t *h = (uint32_t *)(stage + KP_CHUNK);
+  uint32_t *lstart = h + SP_MAXBINS;
+  uint32_t *misc = lstart + SP_MAXBINS;                // [0..15] scan scratch, [8] parent, [9] chunk (read before the scan)
+  for (uint32_t i = threadIdx.x; i < nbins; i += 512) h[i] = 0;
+  if (threadIdx.x == 0) {
+    uint32_t lo2 = 0, hi2 = nparents;                  // blk_first[lo2] <= blockIdx.x < blk_first[hi2]
+    if (blockIdx.x >= blk_first[nparents]) {
+      misc[8] = 0xffffffffu;
+    } else {
+      while (hi2 - lo2 > 1) {
+        const uint32_t mid = (lo2 + hi2) >> 1;
+        if (blk_first[mid] <= blockIdx.x) lo2 = mid; else hi2 = mid;
+      }
+      misc[8] = lo2;
+      misc[9] = blockIdx.x - blk_first[lo2];
+    }
+  }
+  __syncthreads();
+  const uint32_t parent = misc[8];
+  if (parent == 0xffffffffu) return;
+  const uint32_t sbeg = seg_start[parent], send = seg_end[parent];
+  const uint32_t rbeg = sbeg + misc[9] * KP_CHUNK;
+  const uint32_t rcnt = send - rbeg < KP_CHUNK ? send - rbeg : KP_CHUNK;
+  const uint64_t binbase = (uint64_t)parent << (parent_shift - shift);
+  ulonglong2 r8[8];
+  uint32_t rk[4];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const uint32_t j = k * 512 + threadIdx.x;
+    r8[k] = j < rcnt ? __ldcs(rec_in + rbeg + j) : make_ulonglong2(0ull, 0ull);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) rk[k] = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const uint32_t j = k * 512 + threadIdx.x;
+    if (j < rcnt) {
+      const uint32_t bin = (uint32_t)(((((r8[k].x >> 32) & REC_CODE_MASK) - mincode) >> shift) - binbase);
+      const uint32_t q = atomicAdd(&h[bin], 1u);
+      rk[k >> 1] |= q << ((k & 1) * 16);
+    }
+  }
+  __syncthreads();
+  const uint32_t total = kp_scan_bins<512>(h, lstart, nbins, misc);
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < nbins; i += 512) {
+    const uint32_t cnt = h[i];
+    h[i] = cnt ? atomicAdd(&gcursor[binbase + i], cnt) - lstart[i] : 0u;
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const uint32_t j = k * 512 + threadIdx.x;
+    if (j < rcnt) {
+      const uint32_t bin = (uint32_t)(((((r8[k].x >> 32) & REC_CODE_MASK) - mincode) >> shift) - binbase);
+      stage[lstart[bin] + ((rk[k >> 1] >> ((k & 1) * 16)) & 0xffffu)] = r8[k];
+    }
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < total; i += 512) {
+    const ulonglong2 r = stage[i];
+    const uint32_t bin = (uint32_t)(((((r.x >> 32) & REC_CODE_MASK) - mincode) >> shift) - binbase);
+    __stcs(rec_out + h[bin] + i, r);
+  }
+}
+
+// blk_first[0..nparents]: prefix sums of ceil(records/KP_CHUNK) per level-1 bin (single block)
+__global__ void __launch_bounds__(256) k_keyed_chunk_table(const uint32_t *__restrict__ seg_start,
+                                                           const uint32_t *__restrict__ seg_end, uint32_t nparents,
+                                                           uint32_t *blk_first) {
+  __shared__ uint32_t sm[8];
+  uint32_t carry = 0;
+  for (uint32_t base = 0; base < nparents; base += 256) {
+    const uint32_t i = base + threadIdx.x;
+    const uint32_t v = i < nparents ? (seg_end[i] - seg_start[i] + KP_CHUNK - 1) / KP_CHUNK : 0;
+    uint32_t tot;
+    const uint32_t ex = block_excl_scan256(v, &tot, sm);
+    if (i < nparents) blk_first[i] = carry + ex;
+    carry += tot;
+  }
+  if (threadIdx.x == 0) blk_first[nparents] = carry;
+}
+
+// tiles.cuh's k_tile_sort for keyed records: insertion only moves (position, key) into the bucket's slots
+__global__ void __launch_bounds__(TS_THREADS, 2) k_tile_sort_keyed(Text<2> T, PartOut out, const uint32_t *__restrict__ lb,
+                                                                   uint32_t *__restrict__ cursor,
+                                                                   const ulonglong2 *__restrict__ rec,
+                                                                   const uint32_t *__restrict__ gcursor, uint64_t mincode,
+                                                                   uint64_t maxcode, int shift, uint32_t nbins, unsigned pl,
+                                                                   uint32_t *__restrict__ fbbits, uint64_t tieoff) {
+  extern __shared__ __align__(16) unsigned char ts_raw[];
+  uint64_t *s_key = (uint64_t *)ts_raw;
+  uint32_t *s_pos = (uint32_t *)(s_key + TILE_CAP);
+  uint32_t *s_lb = s_pos + TILE_CAP;
+  uint32_t *s_cur = s_lb + TILE_MAXCODES + 1;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  unsigned long long sum = 0;
+  uint32_t mx = 0;
+  for (uint32_t g = blockIdx.x; g < nbins; g += gridDim.x) {
+    const uint64_t c0 = mincode + ((uint64_t)g << shift);
+    uint64_t c1 = c0 + (1ull << shift);
+    if (c1 > maxcode + 1) c1 = maxcode + 1;
+    const uint32_t ncf = (uint32_t)(c1 - c0);
+    const uint32_t base = lb[c0];                       // global suffix-array index of the tile
+    const uint32_t slots = lb[c1] - base;
+    const uint32_t rs = base - out.partoffset;          // part-local; also the tile's first record
+    const uint32_t cnt = gcursor[g] - rs;
+    __syncthreads();                                    // previous tile fully consumed
+    for (uint32_t i = threadIdx.x; i <= ncf; i += TS_THREADS) {
+      const uint32_t v = lb[c0 + i] - base;
+      s_lb[i] = v;
+      if (i < ncf) s_cur[i] = v;
+    }
+    __syncthreads();
+    if (slots > TILE_CAP) {
+      // too many suffixes for shared memory: plain insertion, the global kernels sort these buckets
+      for (uint32_t i = threadIdx.x; i < cnt; i += TS_THREADS) {
+        const uint64_t a = __ldcs(&rec[rs + i].x);
+        const uint32_t slot = atomicAdd(&s_cur[(uint32_t)(((a >> 32) & REC_CODE_MASK) - c0)], 1u);
+        out.sa[rs + slot] = (uint32_t)a;
+      }
+      __syncthreads();
+      for (uint32_t i = threadIdx.x; i < ncf; i += TS_THREADS) cursor[c0 + i] = base + s_cur[i];
+      if (threadIdx.x == 0) atomicAdd(&out.stats->tile_leftover, 1u);
+      continue;
+    }
+    for (uint32_t i0 = threadIdx.x; i0 < cnt; i0 += TS_THREADS * TS_BATCH) {
+      ulonglong2 r[TS_BATCH];
+#pragma unroll
+      for (int u = 0; u < TS_BATCH; ++u) {
+        const uint32_t i = i0 + u * TS_THREADS;
+        r[u] = i < cnt ? __ldcs(rec + rs + i) : make_ulonglong2(0ull, 0ull);
+      }
+#pragma unroll
+      for (int u = 0; u < TS_BATCH; ++u) {
+        const uint32_t i = i0 + u * TS_THREADS;
+        if (i < cnt) {
+          const uint32_t slot = atomicAdd(&s_cur[(uint32_t)(((r[u].x >> 32) & REC_CODE_MASK) - c0)], 1u);
+          s_pos[slot] = (uint32_t)r[u].x;
+          s_key[slot] = r[u].y;
+        }
+      }
+    }
+    __syncthreads();
+    for (uint32_t f = wid; f < ncf; f += TS_WARPS) {
+      const uint32_t ls = s_lb[f];
+      const uint32_t cf = s_cur[f] - ls;                // regular suffixes of bucket c0+f
+      const uint32_t start = rs + ls;
+      bool done = true;
+      if (cf == 1) {
+        if (lane == 0) put_sa(out, start, s_pos[ls]);
+      } else if (cf > 1) {
+        const uint32_t *src = s_pos + ls;
+        const uint64_t *keys = s_key + ls;
+        bool clean = true;                              // sorted and free of ties
+        if (cf <= 32) clean = warp_sort_any<2, 1>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else if (cf <= 64) clean = warp_sort_any<2, 2>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else if (cf <= 96) clean = warp_sort_any<2, 3>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else if (cf <= SORT_MAXBUCKET) clean = warp_sort_any<2, 4>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else {                                          // too large for a warp: leave it to the global sorters
+          for (uint32_t i = lane; i < cf; i += 32) out.sa[start + i] = src[i];
+          done = false;
+          if (lane == 0) atomicAdd(&out.stats->tile_leftover, 1u);
+        }
+        if (!clean && lane == 0) {                      // sorted on pl+W symbols, tie groups go to refinement
+          const uint64_t rel = c0 + f - mincode;
+          atomicOr(&fbbits[tieoff + (rel >> 5)], 1u << (rel & 31));
+          atomicAdd(&out.stats->fb_elems, (unsigned long long)cf);
+          atomicAdd(&out.stats->fb_buckets, 1u);
+        }
+      }
+      if (lane == 0) cursor[c0 + f] = done ? base + ls : base + ls + cf;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sum += __shfl_xor_sync(GTB_FULL, sum, o);
+    mx = max(mx, __shfl_xor_sync(GTB_FULL, mx, o));
+  }
+  if (lane == 0) {
+    if (sum) atomicAdd(&out.stats->lcpsum, sum);
+    if (mx) atomicMax(&out.stats->maxdepth, mx);
+  }
+}

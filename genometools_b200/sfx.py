@@ -69,7 +69,7 @@ EXPORTS = [
     "gtb200_sort_part", "gtb200_tail", "gtb200_recommendedprefixlength", "gtb200_suftabparts",
     "gtb200_profile_enable", "gtb200_profile_read", "gtb200_profile_reset",
     "gtb200_leftborder_partialsums_noalloc", "gtb200_release_cached_memory",
-    "gtb200_count_shard", "gtb200_count_finish",
+    "gtb200_count_shard", "gtb200_count_finish", "gtb200_part_diag",
 ]
 
 
@@ -109,6 +109,7 @@ def load_library() -> C.CDLL:
     L.gtb200_count_finish.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(CountInfo)]
     L.gtb200_leftborder_partialsums_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
                                                         C.c_char_p, C.c_size_t]
+    L.gtb200_part_diag.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_int]
     _lib = L
     return L
 
@@ -222,6 +223,13 @@ class Sfxiterator:
         a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
         _check(self._L.gtb200_part_device(self._ctx, C.byref(a), C.byref(b), C.byref(c)))
         return a.value, b.value, c.value
+
+    def part_diag(self) -> dict:
+        """What the library did for the last sorted part (gtb200_part_diag)."""
+        v = (C.c_uint64 * 8)()
+        self._L.gtb200_part_diag(self._ctx, v, 8)
+        return {"tile": int(v[0]), "levels": int(v[1]), "keyed": int(v[2]), "medium_suffixes": int(v[3]),
+                "padded_suffixes": int(v[4])}
 
     def _account(self, info: PartInfo) -> None:
         self.partinfos.append(info)

@@ -207,6 +207,13 @@ int gtb200_profile_enable(gtb200_ctx *ctx, int on);
 int gtb200_profile_read(gtb200_ctx *ctx, const char **names, double *ms, uint64_t *launches, int capacity);
 void gtb200_profile_reset(gtb200_ctx *ctx);
 
+/* Diagnostics of the last sorted part, for the benchmark's roofline arithmetic (no reference counterpart; the
+ * reference logs the analogous sorter counters at src/match/sfx-bentsedg.c:1520-1525): values[0] = 1 if the tile
+ * path ran, [1] = partition levels (1 or 2), [2] = 1 if the records carried their sort keys (16-byte records),
+ * [3] = suffixes sorted by the block-level sorter (buckets of 129..1024), [4] = upper bound on the number of
+ * special-padded suffixes.  Returns the number of defined values (<= 8). */
+int gtb200_part_diag(gtb200_ctx *ctx, uint64_t *values, int capacity);
+
 /* -- entry point that never allocates -------------------------------------------------------- */
 
 /*

@@ -121,6 +121,33 @@ def test_tile_path_forced(case, parts, levels, monkeypatch):
 
 
 @pytest.mark.parametrize("levels", ["1", "2"])
+@pytest.mark.parametrize("parts", [1, 3])
+@pytest.mark.parametrize("case", sorted(TILE_CASES))
+def test_tile_path_keyed_records(case, parts, levels, monkeypatch):
+    """The tile path with 16-byte records that carry their sort key (what genomes larger than L2 use), forced on
+    small inputs: the keys built from three text words in the level-1 partition must equal the gathered ones,
+    including keys cut by specials, sparse code ranges (parts) and buckets handed to the other sorters."""
+    monkeypatch.setenv("GTB200_TILE", "2")
+    monkeypatch.setenv("GTB200_KEYED", "2")
+    monkeypatch.setenv("GTB200_TILE_LEVELS", levels)
+    enc, pl = TILE_CASES[case]()
+    want = oracle.build(enc, 4, pl)
+    got = sfx.suffixerator(enc, "dna", parts=parts, prefixlength=want["prefixlength"])
+    _compare(got, want, f"keyed/{case}/parts{parts}/levels{levels}")
+
+
+def test_tile_path_keyed_records_sliced_fetch(monkeypatch):
+    """Keyed records under the pipelined fetch: the part is cut into code ranges whose level-1 records pass through
+    the image buffer while earlier slices of the image are already being copied out."""
+    monkeypatch.setenv("GTB200_TILE", "2")
+    monkeypatch.setenv("GTB200_KEYED", "2")
+    enc = synth.multi_dna_with_nruns(5_000_000, nseq=8, seed=97)
+    want = oracle.build(enc, 4)
+    for parts in (1, 2):
+        _compare(sfx.suffixerator(enc, "dna", parts=parts), want, f"keyed/sliced/parts{parts}")
+
+
+@pytest.mark.parametrize("levels", ["1", "2"])
 def test_tile_path_forced_protein(levels, monkeypatch):
     """The same path on byte text (sigma = 20, codes are base-20 numbers): most buckets are larger than a warp
     sorts, so the tile sorter only inserts them (no key gather) and the block sorter finishes them."""
