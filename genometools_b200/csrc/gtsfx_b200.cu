@@ -122,6 +122,7 @@ struct gtb200_ctx {
   uint64_t *d_recB;          // second record buffer of the tile path (two partition levels); 16-byte records when keyed
   int keyed_mode;            // 0 never, 1 automatic (text larger than L2's share), 2 always (GTB200_KEYED, testing knob)
   uint64_t cap_suf64_bytes;
+  int csort;                 // 1 = keyed tiles are sorted by the counting sorter (GTB200_CSORT=0: warp networks, testing knob)
   uint64_t diag[8];          // last part: [0] tile path, [1] partition levels, [2] keyed records, [3] suffixes in medium buckets
   uint32_t *d_isa;           // rank array of the prefix-doubling refinement (n+1 entries)
   uint64_t cap_isa;
@@ -2249,6 +2250,8 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
   c->tile_mode = 1;
   if (const char *e4 = getenv("GTB200_TILE")) c->tile_mode = atoi(e4);
   c->keyed_mode = 1;
+  c->csort = 1;
+  if (const char *e11 = getenv("GTB200_CSORT")) c->csort = atoi(e11);
   if (const char *e10 = getenv("GTB200_KEYED")) c->keyed_mode = atoi(e10);
   if (const char *e5 = getenv("GTB200_TILE_LEVELS")) c->tile_levels = atoi(e5);
   c->twolevel_bytes = 48ull << 20;
@@ -2786,7 +2789,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
     }
     if (keyed) {
       // ---- keyed records (keyed.cuh): 16 bytes per suffix, the key travels with the record ----
-      CK(cudaFuncSetAttribute(k_keyed_partition_text<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
+      CK(cudaFuncSetAttribute(k_keyed_partition_dense, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
       CK(cudaFuncSetAttribute(k_keyed_partition_text<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
       CK(cudaFuncSetAttribute(k_keyed_partition_rec, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
       const unsigned textblocks = grid_for(c->n, (uint64_t)KP_CHUNK * reps);
@@ -2806,8 +2809,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
           k_keyed_partition_text<false><<<textblocks, 256, KP_SMEM, c->stream>>>(T2, c->cp.pl, c->n, lo, hi, whole, sh, nb, reps,
                                                                                  gc, dst);
         else
-          k_keyed_partition_text<true><<<textblocks, 256, KP_SMEM, c->stream>>>(T2, c->cp.pl, c->n, lo, hi, whole, sh, nb, 1,
-                                                                                gc, dst);
+          k_keyed_partition_dense<<<textblocks, 256, KP_SMEM, c->stream>>>(T2, c->cp.pl, c->n, lo, hi, whole, sh, nb, gc, dst);
         if (nb1) {
           k_keyed_chunk_table<<<1, 256, 0, c->stream>>>(start1, gcur1, nb1, blkfirst);
           const unsigned recblocks = (unsigned)(rwidth / KP_CHUNK + nb1 + 1);
@@ -2821,6 +2823,11 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
         CK(cudaFuncSetAttribute(k_tile_sort_keyed, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM));
         PartOut tfin = out;
         if (c->fused_widen) tfin.sa64 = c->d_suf64;          // the level-1 records in it are dead by now
+        if (c->csort) {
+          CK(cudaFuncSetAttribute(k_tile_csort, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
+          k_tile_csort<<<tb, TC_THREADS, TC_SMEM, c->stream>>>(tfin, c->d_lb, c->d_cursor, recY, gcurF, lo, hi, shiftF, nbinsF,
+                                                               c->cp.pl, fbb, fbwords);
+        } else
         k_tile_sort_keyed<<<tb, TS_THREADS, TS_SMEM, c->stream>>>(T2, tfin, c->d_lb, c->d_cursor, recY, gcurF, lo, hi, shiftF,
                                                                   nbinsF, c->cp.pl, fbb, fbwords);
       }
@@ -2973,7 +2980,7 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
   if (width == 0) return 0;
   // keyed records once the packed text (and its bitmap) no longer fit L2 beside the streams passing through:
   // the tile sorter's one random text access per suffix is then a 64-byte DRAM access
-  const bool keyed_ok = BITS == 2 && c->cp.pow2 && c->cp.pl <= 16 && c->keyed_mode != 0 &&
+  const bool keyed_ok = BITS == 2 && c->cp.pow2 && c->cp.pl <= 15 && c->keyed_mode != 0 &&
                         (c->keyed_mode == 2 || (c->ntextwords + c->nmaskwords) * 8 > (96ull << 20));
   memset(c->diag, 0, sizeof c->diag);
   if (ensure_part_buffers(c, width, ncodes, keyed_ok)) return -1;
