@@ -122,7 +122,6 @@ struct gtb200_ctx {
   uint64_t *d_recB;          // second record buffer of the tile path (two partition levels); 16-byte records when keyed
   int keyed_mode;            // 0 never, 1 automatic (text larger than L2's share), 2 always (GTB200_KEYED, testing knob)
   uint64_t cap_suf64_bytes;
-  int csort;                 // 1 = keyed tiles are sorted by the counting sorter (GTB200_CSORT=0: warp networks, testing knob)
   uint64_t diag[8];          // last part: [0] tile path, [1] partition levels, [2] keyed records, [3] suffixes in medium buckets
   uint32_t *d_isa;           // rank array of the prefix-doubling refinement (n+1 entries)
   uint64_t cap_isa;
@@ -2250,8 +2249,6 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
   c->tile_mode = 1;
   if (const char *e4 = getenv("GTB200_TILE")) c->tile_mode = atoi(e4);
   c->keyed_mode = 1;
-  c->csort = 1;
-  if (const char *e11 = getenv("GTB200_CSORT")) c->csort = atoi(e11);
   if (const char *e10 = getenv("GTB200_KEYED")) c->keyed_mode = atoi(e10);
   if (const char *e5 = getenv("GTB200_TILE_LEVELS")) c->tile_levels = atoi(e5);
   c->twolevel_bytes = 48ull << 20;
@@ -2823,11 +2820,6 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
         CK(cudaFuncSetAttribute(k_tile_sort_keyed, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM));
         PartOut tfin = out;
         if (c->fused_widen) tfin.sa64 = c->d_suf64;          // the level-1 records in it are dead by now
-        if (c->csort) {
-          CK(cudaFuncSetAttribute(k_tile_csort, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
-          k_tile_csort<<<tb, TC_THREADS, TC_SMEM, c->stream>>>(tfin, c->d_lb, c->d_cursor, recY, gcurF, lo, hi, shiftF, nbinsF,
-                                                               c->cp.pl, fbb, fbwords);
-        } else
         k_tile_sort_keyed<<<tb, TS_THREADS, TS_SMEM, c->stream>>>(T2, tfin, c->d_lb, c->d_cursor, recY, gcurF, lo, hi, shiftF,
                                                                   nbinsF, c->cp.pl, fbb, fbwords);
       }

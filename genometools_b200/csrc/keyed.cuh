@@ -489,265 +489,3 @@ __global__ void __launch_bounds__(TS_THREADS, 2) k_tile_sort_keyed(Text<2> T, Pa
     if (mx) atomicMax(&out.stats->maxdepth, mx);
   }
 }
-
-// ---------------------------------------------------------------------------------------------
-// Tile sorter for keyed records, second form: a counting sort instead of one sorting network per bucket.
-// A tile holds ncf <= 2^shift consecutive buckets (a few thousand suffixes).  Sort key inside the tile =
-// (bucket, leading sb = 14 - shift key bits): 16,384 sixteen-bit counters in shared memory - most sub-buckets hold
-// no or one suffix.
-//   P1 histogram (one shared-memory atomic per record), P2 block-wide scan of the counters, P3 scatter into the
-//   tile's slots (the second read of the records hits L2), P4 the few runs that share a sub-bucket are put in
-//   (key, position) order by the thread that finds the run start, P5 every slot writes its .suf entry (32- and
-//   64-bit) and the LCP with its left neighbour - consecutive threads, consecutive addresses, no per-bucket loop.
-// A run longer than 32 (deep repeats) sends its bucket to the global sorters, a pair equal on all pl+28 bases
-// flags the bucket for refinement: same contract as k_tile_sort (cursor[], fbbits, tile_leftover).
-// Against the warp networks: ~3.5 instead of ~8 warp instructions per suffix.
-// ---------------------------------------------------------------------------------------------
-#define TC_THREADS 512
-#define TC_CAP 5632
-#define TC_CNTWORDS 8192                 // 16,384 16-bit counters
-#define TC_EMPTY 0xffffffffu
-#define TC_BIG 1
-#define TC_TIE 2
-// dynamic shared memory: key[TC_CAP] u64 | pos[TC_CAP] | cnt[TC_CNTWORDS] | lb[TILE_MAXCODES+1] | off[TILE_MAXCODES]
-//                        | head[TC_CAP/32] | flag[TILE_MAXCODES] u8 | misc[32]        (108 KB: two blocks per SM)
-#define TC_SMEM (TC_CAP * 12 + TC_CNTWORDS * 4 + (2 * TILE_MAXCODES + 1) * 4 + (TC_CAP / 32) * 4 + TILE_MAXCODES + 128 + 12)
-
-// last f in [0, ncf) with s_lb[f] <= i (the non-empty bucket that owns slot i)
-__device__ __forceinline__ uint32_t tc_find_bucket(const uint32_t *s_lb, uint32_t ncf, uint32_t i) {
-  uint32_t lo = 0, hi = ncf;             // s_lb[lo] <= i < s_lb[hi]
-  while (hi - lo > 1) {
-    const uint32_t mid = (lo + hi) >> 1;
-    if (s_lb[mid] <= i) lo = mid; else hi = mid;
-  }
-  return lo;
-}
-
-__global__ void __launch_bounds__(TC_THREADS, 2) k_tile_csort(PartOut out, const uint32_t *__restrict__ lb,
-                                                              uint32_t *__restrict__ cursor,
-                                                              const ulonglong2 *__restrict__ rec,
-                                                              const uint32_t *__restrict__ gcursor, uint64_t mincode,
-                                                              uint64_t maxcode, int shift, uint32_t nbins, unsigned pl,
-                                                              uint32_t *__restrict__ fbbits, uint64_t tieoff) {
-  extern __shared__ __align__(16) unsigned char tc_raw[];
-  uint64_t *s_key = (uint64_t *)tc_raw;
-  uint32_t *s_pos = (uint32_t *)(s_key + TC_CAP);
-  uint32_t *s_cnt = s_pos + TC_CAP;
-  uint32_t *s_lb = s_cnt + TC_CNTWORDS;
-  uint32_t *s_off = s_lb + TILE_MAXCODES + 1;
-  uint32_t *s_head = s_off + TILE_MAXCODES;
-  unsigned char *s_flag = (unsigned char *)(s_head + TC_CAP / 32);
-  uint32_t *s_misc = (uint32_t *)(s_flag + TILE_MAXCODES);     // [0..15] warp sums of the scan, [16] a bucket was given up
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int sb = 14 - shift;             // sub-bucket bits (shift <= 10)
-  const int ksh = 64 - sb;
-  unsigned long long sum = 0;
-  uint32_t mx = 0;
-  for (uint32_t g = blockIdx.x; g < nbins; g += gridDim.x) {
-    const uint64_t c0 = mincode + ((uint64_t)g << shift);
-    uint64_t c1 = c0 + (1ull << shift);
-    if (c1 > maxcode + 1) c1 = maxcode + 1;
-    const uint32_t ncf = (uint32_t)(c1 - c0);
-    const uint32_t base = lb[c0];                       // global suffix-array index of the tile
-    const uint32_t slots = lb[c1] - base;
-    const uint32_t rs = base - out.partoffset;          // part-local; also the tile's first record
-    const uint32_t cnt = gcursor[g] - rs;
-    const uint32_t nwords = ((ncf << sb) + 1) >> 1;
-    __syncthreads();                                    // previous tile fully consumed
-    for (uint32_t i = threadIdx.x; i <= ncf; i += TC_THREADS) s_lb[i] = lb[c0 + i] - base;
-    for (uint32_t i = threadIdx.x; i < ncf; i += TC_THREADS) s_flag[i] = 0;
-    if (threadIdx.x == 0) s_misc[16] = 0;
-    __syncthreads();
-    if (slots > TC_CAP) {
-      // too many suffixes for shared memory: plain insertion, the global kernels sort these buckets
-      for (uint32_t i = threadIdx.x; i < ncf; i += TC_THREADS) s_off[i] = s_lb[i];
-      __syncthreads();
-      for (uint32_t i = threadIdx.x; i < cnt; i += TC_THREADS) {
-        const uint64_t a = __ldcs(&rec[rs + i].x);
-        const uint32_t slot = atomicAdd(&s_off[(uint32_t)(((a >> 32) & REC_CODE_MASK) - c0)], 1u);
-        out.sa[rs + slot] = (uint32_t)a;
-      }
-      __syncthreads();
-      for (uint32_t i = threadIdx.x; i < ncf; i += TC_THREADS) cursor[c0 + i] = base + s_off[i];
-      if (threadIdx.x == 0) atomicAdd(&out.stats->tile_leftover, 1u);
-      continue;
-    }
-    // ---- P0: clear counters, slots and bucket-start bits ----
-    for (uint32_t i = threadIdx.x * 4; i < ((nwords + 15u) & ~15u); i += TC_THREADS * 4)     // whole 16-word scan chunks
-      *(uint4 *)(s_cnt + i) = make_uint4(0u, 0u, 0u, 0u);
-    for (uint32_t i = threadIdx.x; i < slots; i += TC_THREADS) s_pos[i] = TC_EMPTY;
-    for (uint32_t i = threadIdx.x; i < (slots + 31) / 32; i += TC_THREADS) s_head[i] = 0;
-    __syncthreads();
-    for (uint32_t f = threadIdx.x; f < ncf; f += TC_THREADS) {
-      const uint32_t a = s_lb[f];
-      if (a < s_lb[f + 1]) atomicOr(&s_head[a >> 5], 1u << (a & 31));
-    }
-    // ---- P1: histogram over (bucket, leading key bits) ----
-    for (uint32_t i0 = threadIdx.x; i0 < cnt; i0 += TC_THREADS * TS_BATCH) {
-      ulonglong2 r[TS_BATCH];
-#pragma unroll
-      for (int u = 0; u < TS_BATCH; ++u) {
-        const uint32_t i = i0 + u * TC_THREADS;
-        r[u] = i < cnt ? __ldg(rec + rs + i) : make_ulonglong2(0ull, 0ull);
-      }
-#pragma unroll
-      for (int u = 0; u < TS_BATCH; ++u) {
-        const uint32_t i = i0 + u * TC_THREADS;
-        if (i < cnt) {
-          const uint32_t idx = (((uint32_t)(r[u].x >> 32) & (uint32_t)REC_CODE_MASK) - (uint32_t)c0) << sb | (uint32_t)(r[u].y >> ksh);
-          atomicAdd(&s_cnt[idx >> 1], (idx & 1u) ? 65536u : 1u);
-        }
-      }
-    }
-    __syncthreads();
-    // ---- P2: exclusive scan of the 16-bit counters (16 words = 32 counters per thread) ----
-    {
-      uint32_t w[16];
-      const uint32_t wb = threadIdx.x * 16;
-      uint32_t tsum = 0;
-      if (wb < nwords) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const uint4 q = *(const uint4 *)(s_cnt + wb + 4 * j);
-          w[4 * j] = q.x; w[4 * j + 1] = q.y; w[4 * j + 2] = q.z; w[4 * j + 3] = q.w;
-        }
-#pragma unroll
-        for (int j = 0; j < 16; ++j) tsum += (w[j] & 0xffffu) + (w[j] >> 16);
-      }
-      uint32_t x = tsum;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t y = __shfl_up_sync(GTB_FULL, x, o);
-        if (lane >= o) x += y;
-      }
-      if (lane == 31) s_misc[wid] = x;
-      __syncthreads();
-      uint32_t woff = 0;
-#pragma unroll
-      for (int k = 0; k < TC_THREADS / 32; ++k)
-        if (k < wid) woff += s_misc[k];
-      uint32_t run = woff + x - tsum;
-      if (wb < nwords) {
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const uint32_t lo = w[j] & 0xffffu, hi = w[j] >> 16;
-          w[j] = run | ((run + lo) << 16);
-          run += lo + hi;
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) *(uint4 *)(s_cnt + wb + 4 * j) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
-      }
-    }
-    __syncthreads();
-    // slot of a record = s_off[bucket] + (its rank among the tile's regular suffixes)
-    for (uint32_t f = threadIdx.x; f < ncf; f += TC_THREADS) s_off[f] = s_lb[f] - (s_cnt[(f << sb) >> 1] & 0xffffu);
-    __syncthreads();
-    // ---- P3: scatter (second read of the records: L2) ----
-    for (uint32_t i0 = threadIdx.x; i0 < cnt; i0 += TC_THREADS * TS_BATCH) {
-      ulonglong2 r[TS_BATCH];
-#pragma unroll
-      for (int u = 0; u < TS_BATCH; ++u) {
-        const uint32_t i = i0 + u * TC_THREADS;
-        r[u] = i < cnt ? __ldcs(rec + rs + i) : make_ulonglong2(0ull, 0ull);
-      }
-#pragma unroll
-      for (int u = 0; u < TS_BATCH; ++u) {
-        const uint32_t i = i0 + u * TC_THREADS;
-        if (i < cnt) {
-          const uint32_t f = ((uint32_t)(r[u].x >> 32) & (uint32_t)REC_CODE_MASK) - (uint32_t)c0;
-          const uint32_t idx = (f << sb) | (uint32_t)(r[u].y >> ksh);
-          const uint32_t old = atomicAdd(&s_cnt[idx >> 1], (idx & 1u) ? 65536u : 1u);
-          const uint32_t slot = s_off[f] + ((idx & 1u) ? (old >> 16) : (old & 0xffffu));
-          s_pos[slot] = (uint32_t)r[u].x;
-          s_key[slot] = r[u].y;
-        }
-      }
-    }
-    __syncthreads();
-    // ---- P4: runs that share a sub-bucket: (key, position) order by insertion ----
-    for (uint32_t i = threadIdx.x; i < slots; i += TC_THREADS) {
-      if (s_pos[i] == TC_EMPTY) continue;
-      const uint64_t top = s_key[i] >> ksh;
-      const bool hd = (s_head[i >> 5] >> (i & 31)) & 1u;
-      if (!hd && (s_key[i - 1] >> ksh) == top) continue;           // inside a run that starts further left
-      uint32_t m = 1;
-      while (i + m < slots && !((s_head[(i + m) >> 5] >> ((i + m) & 31)) & 1u) && s_pos[i + m] != TC_EMPTY &&
-             (s_key[i + m] >> ksh) == top) {
-        ++m;
-        if (m > 32) break;
-      }
-      if (m == 1) continue;
-      if (m > 32) {                                                 // deep repeat: the global sorters take the bucket
-        s_flag[tc_find_bucket(s_lb, ncf, i)] = TC_BIG;
-        s_misc[16] = 1;
-        continue;
-      }
-      for (uint32_t a = 1; a < m; ++a) {
-        const uint64_t kw = s_key[i + a];
-        const uint32_t pw = s_pos[i + a];
-        uint32_t j = a;
-        while (j > 0) {
-          const uint64_t kv = s_key[i + j - 1];
-          const uint32_t pv = s_pos[i + j - 1];
-          if (kv < kw || (kv == kw && pv < pw)) break;
-          s_key[i + j] = kv;
-          s_pos[i + j] = pv;
-          --j;
-        }
-        s_key[i + j] = kw;
-        s_pos[i + j] = pw;
-      }
-    }
-    __syncthreads();
-    // ---- P5: output ----
-    const bool anybig = s_misc[16] != 0;
-    for (uint32_t i = threadIdx.x; i < slots; i += TC_THREADS) {
-      const uint32_t p = s_pos[i];
-      if (p == TC_EMPTY) continue;
-      bool stats = true;
-      if (anybig) stats = !(s_flag[tc_find_bucket(s_lb, ncf, i)] & TC_BIG);
-      put_sa(out, rs + i, p);
-      if (!((s_head[i >> 5] >> (i & 31)) & 1u)) {
-        const uint64_t pk = s_key[i - 1], ck = s_key[i];
-        const uint32_t l = pl + key_common<2>(pk, ck);
-        __stcs(out.lcp + rs + i, (uint8_t)l);
-        if (pk == ck && (ck & 0xff) == 0) {                         // equal on all pl+28 bases: order still open
-          const uint32_t f = tc_find_bucket(s_lb, ncf, i);
-          s_flag[f] = s_flag[f] | TC_TIE;
-        } else if (stats) {
-          sum += l;
-          mx = max(mx, l);
-        }
-      }
-    }
-    __syncthreads();
-    // ---- per bucket: what the later kernels need to know ----
-    for (uint32_t f = threadIdx.x; f < ncf; f += TC_THREADS) {
-      const uint32_t ls = s_lb[f];
-      const uint32_t il = ((f + 1) << sb) - 1;                      // last sub-bucket of f: its counter now holds the end rank
-      const uint32_t cf = (s_cnt[il >> 1] >> 16) - (ls - s_off[f]); // regular suffixes of bucket c0+f
-      const unsigned fl = s_flag[f];
-      if (fl & TC_BIG) {
-        cursor[c0 + f] = base + ls + cf;
-        atomicAdd(&out.stats->tile_leftover, 1u);
-      } else {
-        cursor[c0 + f] = base + ls;
-        if (fl & TC_TIE) {
-          const uint64_t rel = c0 + f - mincode;
-          atomicOr(&fbbits[tieoff + (rel >> 5)], 1u << (rel & 31));
-          atomicAdd(&out.stats->fb_elems, (unsigned long long)cf);
-          atomicAdd(&out.stats->fb_buckets, 1u);
-        }
-      }
-    }
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    sum += __shfl_xor_sync(GTB_FULL, sum, o);
-    mx = max(mx, __shfl_xor_sync(GTB_FULL, mx, o));
-  }
-  if (lane == 0) {
-    if (sum) atomicAdd(&out.stats->lcpsum, sum);
-    if (mx) atomicMax(&out.stats->maxdepth, mx);
-  }
-}

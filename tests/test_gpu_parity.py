@@ -120,22 +120,20 @@ def test_tile_path_forced(case, parts, levels, monkeypatch):
     _compare(got, want, f"tile/{case}/parts{parts}/levels{levels}")
 
 
-@pytest.mark.parametrize("csort", ["1", "0"])
 @pytest.mark.parametrize("levels", ["1", "2"])
 @pytest.mark.parametrize("parts", [1, 3])
 @pytest.mark.parametrize("case", sorted(TILE_CASES))
-def test_tile_path_keyed_records(case, parts, levels, csort, monkeypatch):
+def test_tile_path_keyed_records(case, parts, levels, monkeypatch):
     """The tile path with 16-byte records that carry their sort key (what genomes larger than L2 use), forced on
     small inputs: the keys built from three text words in the level-1 partition must equal the gathered ones,
     including keys cut by specials, sparse code ranges (parts) and buckets handed to the other sorters."""
     monkeypatch.setenv("GTB200_TILE", "2")
     monkeypatch.setenv("GTB200_KEYED", "2")
-    monkeypatch.setenv("GTB200_CSORT", csort)          # 1: counting-sort tile sorter (default), 0: warp networks
     monkeypatch.setenv("GTB200_TILE_LEVELS", levels)
     enc, pl = TILE_CASES[case]()
     want = oracle.build(enc, 4, pl)
     got = sfx.suffixerator(enc, "dna", parts=parts, prefixlength=want["prefixlength"])
-    _compare(got, want, f"keyed/{case}/parts{parts}/levels{levels}/csort{csort}")
+    _compare(got, want, f"keyed/{case}/parts{parts}/levels{levels}")
 
 
 def test_tile_path_keyed_records_sliced_fetch(monkeypatch):
