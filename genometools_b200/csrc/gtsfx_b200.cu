@@ -2171,6 +2171,73 @@ static int open_impl(gtb200_ctx *c, const gtb200_seqdesc *seq) {
   return 0;
 }
 
+// A context without a sequence: alphabet and bucket-table geometry, stream (reused from closed contexts), knobs.
+static gtb200_ctx *ctx_create(int device, unsigned numofchars, uint64_t totallength, unsigned prefixlength) {
+  if (cudaSetDevice(device) != cudaSuccess) { set_error("cudaSetDevice(%d) failed", device); return nullptr; }
+  gtb200_ctx *c = new gtb200_ctx();
+  c->device = device;
+  c->n = totallength;
+  c->bits = numofchars <= 4 ? 2 : 8;
+  c->cp.sigma = numofchars;
+  c->cp.pl = prefixlength;
+  c->cp.pow2 = (numofchars == (1u << c->bits)) ? 1 : 0;
+  const unsigned maxpl = c->bits == 2 ? 16 : 8;
+  if (prefixlength > maxpl) { delete c; set_error("gtb200_open: prefixlength %u > %u unsupported", prefixlength, maxpl); return nullptr; }
+  uint64_t pw = 1;
+  for (unsigned i = 0; i < 34; ++i) {
+    c->cp.pw[i] = pw;
+    if (pw < (1ull << 40)) pw *= numofchars;
+  }
+  c->numcodes = c->cp.pw[prefixlength];
+  if (c->numcodes > (1ull << 31)) {
+    const unsigned long long nc = c->numcodes;
+    delete c;
+    set_error("gtb200_open: %llu buckets are too many", nc);
+    return nullptr;
+  }
+  c->numspecialcodes = c->cp.pw[prefixlength - 1];
+  c->numdist = 0;
+  for (unsigned i = 1; i + 1 < prefixlength; ++i) c->numdist += c->cp.pw[i];
+  {
+    std::lock_guard<std::mutex> lock(g_pool_mu);
+    if (!g_stream_pool[device].empty()) {
+      const StreamSet ss = g_stream_pool[device].back();
+      g_stream_pool[device].pop_back();
+      c->stream = ss.main;
+      c->copy_stream = ss.copy;
+      c->side_stream = ss.side;
+      for (int k = 0; k < 8; ++k) c->slice_ev[k] = ss.ev[k];
+      for (int k = 0; k < 2; ++k) c->side_ev[k] = ss.sev[k];
+    }
+  }
+  if (!c->stream && cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete c;
+    set_error("gtb200_open: cudaStreamCreate failed");
+    return nullptr;
+  }
+  c->sort_maxbucket = SORT_MAXBUCKET;
+  if (const char *e2 = getenv("GTB200_MAXBUCKET")) {   // testing knob: force buckets into the refinement path
+    const long v = atol(e2);
+    if (v >= 0 && v < SORT_MAXBUCKET) c->sort_maxbucket = (uint32_t)v;
+  }
+  c->pipeline = 1;
+  if (const char *e7 = getenv("GTB200_PIPELINE")) c->pipeline = atoi(e7);
+  c->overlap = 1;
+  if (const char *e9 = getenv("GTB200_OVERLAP")) c->overlap = atoi(e9);
+  c->fused_widen = 1;
+  if (const char *e8 = getenv("GTB200_FUSED_WIDEN")) c->fused_widen = atoi(e8);
+  c->doubling = 1;
+  if (const char *e6 = getenv("GTB200_DOUBLING")) c->doubling = atoi(e6);
+  c->tile_mode = 1;
+  if (const char *e4 = getenv("GTB200_TILE")) c->tile_mode = atoi(e4);
+  c->keyed_mode = 1;
+  if (const char *e10 = getenv("GTB200_KEYED")) c->keyed_mode = atoi(e10);
+  if (const char *e5 = getenv("GTB200_TILE_LEVELS")) c->tile_levels = atoi(e5);
+  c->twolevel_bytes = 48ull << 20;
+  if (const char *e3 = getenv("GTB200_TWOLEVEL_BYTES")) c->twolevel_bytes = strtoull(e3, nullptr, 10);   // testing knob
+  return c;
+}
+
 extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *seq, unsigned prefixlength) {
   if (!out || !seq) return set_error("gtb200_open: null argument");
   *out = nullptr;
@@ -2193,66 +2260,8 @@ extern "C" int gtb200_open(gtb200_ctx **out, int device, const gtb200_seqdesc *s
   if (seq->readmode < 0 || seq->readmode > 3) return set_error("gtb200_open: readmode %d unknown", seq->readmode);
   if ((seq->readmode == 2 || seq->readmode == 3) && seq->numofchars != 4)
     return set_error("gtb200_open: complement readmodes need the DNA alphabet");
-  CK(cudaSetDevice(device));
-  gtb200_ctx *c = new gtb200_ctx();
-  c->device = device;
-  c->n = seq->totallength;
-  c->bits = seq->numofchars <= 4 ? 2 : 8;
-  c->cp.sigma = seq->numofchars;
-  c->cp.pl = prefixlength;
-  c->cp.pow2 = (seq->numofchars == (1u << c->bits)) ? 1 : 0;
-  const unsigned maxpl = c->bits == 2 ? 16 : 8;
-  if (prefixlength > maxpl) { delete c; return set_error("gtb200_open: prefixlength %u > %u unsupported", prefixlength, maxpl); }
-  uint64_t pw = 1;
-  for (unsigned i = 0; i < 34; ++i) {
-    c->cp.pw[i] = pw;
-    if (pw < (1ull << 40)) pw *= seq->numofchars;
-  }
-  c->numcodes = c->cp.pw[prefixlength];
-  if (c->numcodes > (1ull << 31)) {
-    const unsigned long long nc = c->numcodes;
-    delete c;
-    return set_error("gtb200_open: %llu buckets are too many", nc);
-  }
-  c->numspecialcodes = c->cp.pw[prefixlength - 1];
-  c->numdist = 0;
-  for (unsigned i = 1; i + 1 < prefixlength; ++i) c->numdist += c->cp.pw[i];
-  {
-    std::lock_guard<std::mutex> lock(g_pool_mu);
-    if (!g_stream_pool[device].empty()) {
-      const StreamSet ss = g_stream_pool[device].back();
-      g_stream_pool[device].pop_back();
-      c->stream = ss.main;
-      c->copy_stream = ss.copy;
-      c->side_stream = ss.side;
-      for (int k = 0; k < 8; ++k) c->slice_ev[k] = ss.ev[k];
-      for (int k = 0; k < 2; ++k) c->side_ev[k] = ss.sev[k];
-    }
-  }
-  if (!c->stream && cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
-    delete c;
-    return set_error("gtb200_open: cudaStreamCreate failed");
-  }
-  c->sort_maxbucket = SORT_MAXBUCKET;
-  if (const char *e2 = getenv("GTB200_MAXBUCKET")) {   // testing knob: force buckets into the refinement path
-    const long v = atol(e2);
-    if (v >= 0 && v < SORT_MAXBUCKET) c->sort_maxbucket = (uint32_t)v;
-  }
-  c->pipeline = 1;
-  if (const char *e7 = getenv("GTB200_PIPELINE")) c->pipeline = atoi(e7);
-  c->overlap = 1;
-  if (const char *e9 = getenv("GTB200_OVERLAP")) c->overlap = atoi(e9);
-  c->fused_widen = 1;
-  if (const char *e8 = getenv("GTB200_FUSED_WIDEN")) c->fused_widen = atoi(e8);
-  c->doubling = 1;
-  if (const char *e6 = getenv("GTB200_DOUBLING")) c->doubling = atoi(e6);
-  c->tile_mode = 1;
-  if (const char *e4 = getenv("GTB200_TILE")) c->tile_mode = atoi(e4);
-  c->keyed_mode = 1;
-  if (const char *e10 = getenv("GTB200_KEYED")) c->keyed_mode = atoi(e10);
-  if (const char *e5 = getenv("GTB200_TILE_LEVELS")) c->tile_levels = atoi(e5);
-  c->twolevel_bytes = 48ull << 20;
-  if (const char *e3 = getenv("GTB200_TWOLEVEL_BYTES")) c->twolevel_bytes = strtoull(e3, nullptr, 10);   // testing knob
+  gtb200_ctx *c = ctx_create(device, seq->numofchars, seq->totallength, prefixlength);
+  if (!c) return -1;
   if (open_impl(c, seq)) { free_ctx(c); return -1; }
   *out = c;
   return 0;
@@ -3182,3 +3191,4 @@ extern "C" int gtb200_profile_read(gtb200_ctx *c, const char **names, double *ms
   }
   return KC_NUM;
 }
+#include "multi.cuh"

@@ -70,6 +70,9 @@ EXPORTS = [
     "gtb200_profile_enable", "gtb200_profile_read", "gtb200_profile_reset",
     "gtb200_leftborder_partialsums_noalloc", "gtb200_release_cached_memory",
     "gtb200_count_shard", "gtb200_count_finish", "gtb200_part_diag",
+    "gtb200_multi_open", "gtb200_multi_close", "gtb200_multi_count", "gtb200_multi_sort_part", "gtb200_multi_tail",
+    "gtb200_multi_devices", "gtb200_multi_ctx", "gtb200_multi_peer_bytes", "gtb200_host_register",
+    "gtb200_host_unregister", "gtb200_multi_free_memory",
 ]
 
 
@@ -110,6 +113,21 @@ def load_library() -> C.CDLL:
     L.gtb200_leftborder_partialsums_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
                                                         C.c_char_p, C.c_size_t]
     L.gtb200_part_diag.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_int]
+    L.gtb200_multi_open.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.c_int, C.POINTER(SeqDesc), C.c_uint]
+    L.gtb200_multi_close.argtypes = [C.c_void_p]
+    L.gtb200_multi_close.restype = None
+    L.gtb200_multi_count.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(CountInfo)]
+    L.gtb200_multi_sort_part.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_int, C.c_void_p,
+                                         C.c_void_p, C.c_uint64, C.POINTER(PartInfo)]
+    L.gtb200_multi_tail.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_int]
+    L.gtb200_multi_devices.argtypes = [C.c_void_p]
+    L.gtb200_multi_ctx.argtypes = [C.c_void_p, C.c_int]
+    L.gtb200_multi_ctx.restype = C.c_void_p
+    L.gtb200_multi_peer_bytes.argtypes = [C.c_void_p]
+    L.gtb200_multi_peer_bytes.restype = C.c_uint64
+    L.gtb200_host_register.argtypes = [C.c_void_p, C.c_size_t]
+    L.gtb200_host_unregister.argtypes = [C.c_void_p]
+    L.gtb200_host_unregister.restype = None
     _lib = L
     return L
 
@@ -147,10 +165,12 @@ class Sfxiterator:
                  enc: np.ndarray | int | None = None, twobit: np.ndarray | int | None = None,
                  ranges: np.ndarray | int | None = None, numofwords: int = 0, numofranges: int = 0,
                  device: int = 0, device_ptrs: bool = False, with_lcp: bool = True, suftabuint: bool = False,
-                 code_range: tuple[int, int] | None = None, readmode: int = 0):
+                 code_range: tuple[int, int] | None = None, readmode: int = 0, devices: list[int] | None = None):
         L = load_library()
         self._L = L
         self._ctx = C.c_void_p()
+        self._multi = C.c_void_p()          # devices given: gtb200_multi_* (every part is sorted by all listed GPUs)
+        self.devices = list(devices) if devices else None
         self.sigma = sigma
         self.totallength = totallength
         self.prefixlength = prefixlength or recommended_prefixlength(sigma, totallength)
@@ -179,7 +199,12 @@ class Sfxiterator:
                 e = np.ascontiguousarray(enc, dtype=np.uint8)
                 self._keep.append(e)
                 desc.encoded = e.ctypes.data
-        _check(L.gtb200_open(C.byref(self._ctx), device, C.byref(desc), self.prefixlength))
+        if self.devices:
+            devs = (C.c_int * len(self.devices))(*self.devices)
+            _check(L.gtb200_multi_open(C.byref(self._multi), devs, len(self.devices), C.byref(desc), self.prefixlength))
+            self._ctx = C.c_void_p(L.gtb200_multi_ctx(self._multi, 0))
+        else:
+            _check(L.gtb200_open(C.byref(self._ctx), device, C.byref(desc), self.prefixlength))
         # "counting prefix distribution"
         info = CountInfo()
         numcodes = sigma ** self.prefixlength
@@ -187,8 +212,12 @@ class Sfxiterator:
         self.countspecialcodes = np.zeros(sigma ** (self.prefixlength - 1), dtype=np.uint32)
         ndist = sum(sigma ** i for i in range(1, self.prefixlength - 1))
         self.distpfxidx = np.zeros(ndist, dtype=np.uint32)
-        _check(L.gtb200_count(self._ctx, self.leftborder.ctypes.data, self.countspecialcodes.ctypes.data,
-                              self.distpfxidx.ctypes.data if ndist else None, C.byref(info)))
+        if self.devices:
+            _check(L.gtb200_multi_count(self._multi, self.leftborder.ctypes.data, self.countspecialcodes.ctypes.data,
+                                        self.distpfxidx.ctypes.data if ndist else None, C.byref(info)))
+        else:
+            _check(L.gtb200_count(self._ctx, self.leftborder.ctypes.data, self.countspecialcodes.ctypes.data,
+                                  self.distpfxidx.ctypes.data if ndist else None, C.byref(info)))
         self.countinfo = info
         self.numofsuffixestosort = int(info.numofsuffixestosort)
         self.specialcharacters = int(info.specialcharacters)
@@ -252,11 +281,20 @@ class Sfxiterator:
             suf = np.empty(width, dtype=np.uint32 if self.suftabuint else np.uint64)
             lcp = np.empty(width, dtype=np.uint8)
             info = PartInfo()
-            _check(self._L.gtb200_sort_part_device(self._ctx, mincode, maxcode, C.byref(info)))
-            assert info.width == width, (info.width, width)
-            llv = np.zeros((int(info.numoflargelcpvalues), 2), dtype=np.uint64)
-            _check(self._L.gtb200_fetch_part(self._ctx, suf.ctypes.data, 1 if self.suftabuint else 0,
-                                             lcp.ctypes.data, llv.ctypes.data if llv.size else None, llv.shape[0]))
+            if self.devices:
+                llvbuf = np.empty((max(width, 1), 2), dtype=np.uint64)      # untouched pages cost nothing
+                _check(self._L.gtb200_multi_sort_part(self._multi, mincode, maxcode, suf.ctypes.data,
+                                                      1 if self.suftabuint else 0, lcp.ctypes.data, llvbuf.ctypes.data,
+                                                      llvbuf.shape[0], C.byref(info)))
+                assert info.width == width, (info.width, width)
+                llv = llvbuf[:int(info.numoflargelcpvalues)].copy()
+                del llvbuf
+            else:
+                _check(self._L.gtb200_sort_part_device(self._ctx, mincode, maxcode, C.byref(info)))
+                assert info.width == width, (info.width, width)
+                llv = np.zeros((int(info.numoflargelcpvalues), 2), dtype=np.uint64)
+                _check(self._L.gtb200_fetch_part(self._ctx, suf.ctypes.data, 1 if self.suftabuint else 0,
+                                                 lcp.ctypes.data, llv.ctypes.data if llv.size else None, llv.shape[0]))
             self._account(info)
             return suf, lcp, llv, False
         if not self._tail_done:
@@ -302,6 +340,10 @@ class Sfxiterator:
         return {names[i].decode(): (ms[i], int(ln[i])) for i in range(k)}
 
     def delete(self) -> None:
+        if self._multi:
+            self._L.gtb200_multi_close(self._multi)
+            self._multi = C.c_void_p()
+            self._ctx = C.c_void_p()
         if self._ctx:
             self._L.gtb200_close(self._ctx)
             self._ctx = C.c_void_p()
@@ -315,7 +357,7 @@ class Sfxiterator:
 
 def suffixerator(enc: np.ndarray, alphabet: str = "dna", indexname: str | None = None, parts: int = 1,
                  prefixlength: int | None = None, device: int = 0, use_twobit: bool | None = None,
-                 readmode: int = 0) -> dict:
+                 readmode: int = 0, devices: list[int] | None = None) -> dict:
     """`gt suffixerator -suf -lcp -bck` on an encoded sequence: runs the iterator to exhaustion and
     returns the byte images of .suf/.lcp/.llv/.bck plus the .prj statistics; writes the files when
     ``indexname`` is given."""
@@ -325,9 +367,9 @@ def suffixerator(enc: np.ndarray, alphabet: str = "dna", indexname: str | None =
         use_twobit = alphabet == "dna"
     if use_twobit:
         it = Sfxiterator(sigma, n, prefixlength, parts, twobit=_encseq.twobit_pack(enc),
-                         ranges=_encseq.special_ranges(enc), device=device, readmode=readmode)
+                         ranges=_encseq.special_ranges(enc), device=device, readmode=readmode, devices=devices)
     else:
-        it = Sfxiterator(sigma, n, prefixlength, parts, enc=enc, device=device, readmode=readmode)
+        it = Sfxiterator(sigma, n, prefixlength, parts, enc=enc, device=device, readmode=readmode, devices=devices)
     suf_chunks, lcp_chunks, llv_chunks = [], [], []
     try:
         while True:

@@ -207,6 +207,49 @@ int gtb200_profile_enable(gtb200_ctx *ctx, int on);
 int gtb200_profile_read(gtb200_ctx *ctx, const char **names, double *ms, uint64_t *launches, int capacity);
 void gtb200_profile_reset(gtb200_ctx *ctx);
 
+/* -- several GPUs of one box behind one handle ------------------------------------------------ */
+
+/*
+ * The multi-GPU form of the calls above ("gtb200_open(devs[], ndev, ...)", 8(e)).  It replaces
+ * the same reference code - the parts loop of gt_Sfxiterator_next / gt_sfxiterator_preparethispart
+ * (src/match/sfx-suffixer.c:1947-2204) driven by gt_suftabparts_new (src/match/sfx-partssuf.c:172-343) - with
+ * every part cut once more into ndev bucket ranges, one per GPU:
+ *   gtb200_multi_open       uploads the sequence to devices[0] and copies its device image to the other GPUs peer to
+ *                           peer (NVLink); same arguments as gtb200_open otherwise.
+ *   gtb200_multi_count      = gtb200_count; the k-mers are counted position-sharded, the tables summed over peer
+ *                           memory by the library's own kernel (replicated counting if the GPUs cannot reach each
+ *                           other's memory).
+ *   gtb200_multi_sort_part  = gtb200_sort_part for [mincode, maxcode]: the ndev ranges are sorted concurrently (one
+ *                           host thread per GPU inside the call) and land in bucket order in the caller's buffers;
+ *                           info is the merged part info.  Output is byte-identical for any number of devices.
+ *   gtb200_multi_tail       = gtb200_tail.
+ * With ndev == 1 every call is the single-GPU call.
+ */
+typedef struct gtb200_multi gtb200_multi;
+int gtb200_multi_open(gtb200_multi **m, const int *devices, int ndev, const gtb200_seqdesc *seq,
+                      unsigned prefixlength);
+void gtb200_multi_close(gtb200_multi *m);
+int gtb200_multi_count(gtb200_multi *m, uint32_t *leftborder, uint32_t *countspecialcodes,
+                       uint32_t *distpfxidx, gtb200_countinfo *info);
+int gtb200_multi_sort_part(gtb200_multi *m, uint64_t mincode, uint64_t maxcode, void *suftab,
+                           int suftab_is_uint32, uint8_t *lcptab, gtb200_largelcp *llv,
+                           uint64_t llv_capacity, gtb200_partinfo *info);
+int gtb200_multi_tail(gtb200_multi *m, uint64_t first, uint64_t count, void *suftab, int suftab_is_uint32);
+int gtb200_multi_devices(const gtb200_multi *m);
+gtb200_ctx *gtb200_multi_ctx(gtb200_multi *m, int i);        /* the i-th device's context (profiling, streams) */
+uint64_t gtb200_multi_peer_bytes(const gtb200_multi *m);     /* bytes moved between the GPUs so far */
+/* Smallest free (and total) device memory over the handle's GPUs; the host side derives the number of parts from
+ * it, as gt_suftabparts_fit_memlimit does from -memlimit (src/match/sfx-partssuf.c:449-527). */
+int gtb200_multi_free_memory(gtb200_multi *m, uint64_t *free_bytes, uint64_t *total_bytes);
+
+/*
+ * Page-locks (cudaHostRegister) / releases a host buffer the caller owns - the GtUword array of the
+ * GtSuffixsortspace (src/match/sfx-suffixgetset.c:157-167) and the lcp buffer - so that gtb200_sort_part's copies of
+ * finished slices overlap the sorting of the next ones; with pageable memory every copy is synchronous.
+ */
+int gtb200_host_register(void *ptr, size_t bytes);
+void gtb200_host_unregister(void *ptr);
+
 /* Diagnostics of the last sorted part, for the benchmark's roofline arithmetic (no reference counterpart; the
  * reference logs the analogous sorter counters at src/match/sfx-bentsedg.c:1520-1525): values[0] = 1 if the tile
  * path ran, [1] = partition levels (1 or 2), [2] = 1 if the records carried their sort keys (16-byte records),

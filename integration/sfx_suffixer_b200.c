@@ -43,9 +43,12 @@ bool gt_Outlcpinfo_b200_wantsdist(const GtOutlcpinfo *outlcpinfo);
 void gt_Outlcpinfo_b200_distadd(GtOutlcpinfo *outlcpinfo, const uint8_t *lcp, GtUword from, GtUword to,
                                 const void *llv, GtUword nllv, GtUword partoffset, GtUword *llvidx);
 
+#define B200_MAXDEV 16
+
 struct Sfxiterator
 {
-  gtb200_ctx *dev;
+  gtb200_multi *dev;               /* one or several GPUs (GTB200_DEVICES) behind one handle */
+  void *pinned_suf, *pinned_lcp;   /* host buffers page-locked for overlapped copies */
   const GtEncseq *encseq;          /* borrowed */
   GtOutlcpinfo *outlcpinfo;        /* borrowed, may be NULL */
   FILE *outfpbcktab;               /* written in _delete when parts > 1, like the reference */
@@ -65,10 +68,49 @@ struct Sfxiterator
   GtUword llvcap;
 };
 
-static int b200_device(void)
+/* GTB200_DEVICES=0,1,4-7 lists the GPUs every part is spread over (north_star: "each of the 1/2/4/8 GPUs ...
+   sorts and LCP-annotates its own disjoint bucket ranges"); GTB200_DEVICE=k is the single-GPU form. */
+static int b200_devices(int *devs)
 {
-  const char *env = getenv("GTB200_DEVICE");
-  return env != NULL ? atoi(env) : 0;
+  const char *env = getenv("GTB200_DEVICES");
+  int n = 0;
+
+  if (env == NULL || *env == '\0')
+  {
+    env = getenv("GTB200_DEVICE");
+    devs[0] = env != NULL ? atoi(env) : 0;
+    return 1;
+  }
+  while (*env != '\0' && n < B200_MAXDEV)
+  {
+    char *end;
+    long a = strtol(env, &end, 10), b;
+    if (end == env)
+    {
+      break;
+    }
+    b = a;
+    if (*end == '-')
+    {
+      env = end + 1;
+      b = strtol(env, &end, 10);
+    }
+    for (; a <= b && n < B200_MAXDEV; a++)
+    {
+      devs[n++] = (int) a;
+    }
+    env = (*end == ',') ? end + 1 : end;
+    if (*end != ',' && *end != '\0')
+    {
+      break;
+    }
+  }
+  if (n == 0)
+  {
+    devs[0] = 0;
+    n = 1;
+  }
+  return n;
 }
 
 static void *b200_rawptr(Sfxiterator *sfi)
@@ -121,9 +163,17 @@ int gt_Sfxiterator_delete(Sfxiterator *sfi, GT_UNUSED GtError *err)
     b200_bcktab_to_file(sfi, sfi->outfpbcktab);
     gt_fa_fclose(sfi->outfpbcktab);
   }
+  if (sfi->pinned_suf != NULL)
+  {
+    gtb200_host_unregister(sfi->pinned_suf);
+  }
+  if (sfi->pinned_lcp != NULL)
+  {
+    gtb200_host_unregister(sfi->pinned_lcp);
+  }
   if (sfi->dev != NULL)
   {
-    gtb200_close(sfi->dev);
+    gtb200_multi_close(sfi->dev);
   }
   if (sfi->suffixsortspace != NULL)
   {
@@ -160,7 +210,7 @@ Sfxiterator *gt_Sfxiterator_new_withadditionalvalues(const GtEncseq *encseq,
   GtUchar *encoded = NULL;
   GtUword largest = 0;
   unsigned int i;
-  int p;
+  int p, devs[B200_MAXDEV], ndev;
 
   gt_error_check(err);
   if (sfxstrategy != NULL && (sfxstrategy->spmopt_minlength > 0 || sfxstrategy->compressedoutput))
@@ -227,7 +277,8 @@ Sfxiterator *gt_Sfxiterator_new_withadditionalvalues(const GtEncseq *encseq,
   {
     gt_timer_show_progress(sfxprogress, "counting prefix distribution", stdout);
   }
-  if (gtb200_open(&sfi->dev, b200_device(), &seq, prefixlength) != 0)
+  ndev = b200_devices(devs);
+  if (gtb200_multi_open(&sfi->dev, devs, ndev, &seq, prefixlength) != 0)
   {
     gt_error_set(err, "%s", gtb200_last_error());
     gt_free(ranges);
@@ -247,20 +298,53 @@ Sfxiterator *gt_Sfxiterator_new_withadditionalvalues(const GtEncseq *encseq,
     sfi->countspecialcodes = gt_malloc(sizeof (uint32_t) * (size_t) speccodes);
     sfi->distpfxidx = gt_malloc(sizeof (uint32_t) * (size_t) (d + 1));
   }
-  if (gtb200_count(sfi->dev, sfi->leftborder, sfi->countspecialcodes, sfi->distpfxidx, &sfi->ci) != 0)
+  if (gtb200_multi_count(sfi->dev, sfi->leftborder, sfi->countspecialcodes, sfi->distpfxidx, &sfi->ci) != 0)
   {
     gt_error_set(err, "%s", gtb200_last_error());
     (void) gt_Sfxiterator_delete(sfi, NULL);
     return NULL;
   }
   gt_logger_log(logger, "largest bucket size=" GT_WU, (GtUword) sfi->ci.largestbucket);
-  if (maximumspace > 0)
-  {
-    gt_logger_log(logger, "B200 build: -memlimit is ignored, the index is built in %u part(s)", numofparts);
-  }
   if (numofparts == 0)
   {
     numofparts = 1U;
+  }
+  {
+    /* The number of parts follows from memory like gt_suftabparts_fit_memlimit does it for the reference
+       (src/match/sfx-partssuf.c:449-527): -memlimit bounds the host side (8+1 bytes per suffix of a part next to
+       the bucket table), the free HBM of the smallest GPU bounds the device side (sequence + bucket tables resident,
+       about 40 bytes per suffix of a device's share of a part).  More parts never change the output. */
+    const double nsort = (double) sfi->ci.numofsuffixestosort;
+    const double tablebytes = 4.0 * ((double) sfi->ci.numofallcodes + (double) sfi->ci.numofspecialcodes
+                                     + (double) sfi->ci.numofdistpfxidx);
+    uint64_t freeb = 0, totalb = 0;
+    unsigned int need = 1U;
+
+    if (maximumspace > 0)
+    {
+      const double room = (double) maximumspace - tablebytes;
+      const double per = (sfi->suftabuint ? 4.0 : 8.0) + (sfi->outlcpinfo != NULL ? 1.0 : 0.0);
+      need = room > per ? (unsigned int) (nsort * per / room) + 1U : 1024U;
+      gt_logger_log(logger, "B200 build: -memlimit " GT_WU " bytes -> at least %u part(s)", maximumspace, need);
+    }
+    if (gtb200_multi_free_memory(sfi->dev, &freeb, &totalb) == 0 && freeb > 0)
+    {
+      const double room = 0.92 * (double) freeb - 2.0 * tablebytes;      /* cursors mirror the leftborder table */
+      const double share = nsort / (double) ndev;
+      const unsigned int hbm = room > 40.0 ? (unsigned int) (share * 40.0 / room) + 1U : 1024U;
+      if (hbm > 1U)
+      {
+        gt_logger_log(logger, "B200 build: %.1f GB of HBM free per GPU -> at least %u part(s)", (double) freeb / 1e9, hbm);
+      }
+      if (hbm > need)
+      {
+        need = hbm;
+      }
+    }
+    if (need > numofparts)
+    {
+      numofparts = need;
+    }
   }
   sfi->mincodes = gt_malloc(sizeof (uint64_t) * numofparts);
   sfi->maxcodes = gt_malloc(sizeof (uint64_t) * numofparts);
@@ -285,10 +369,27 @@ Sfxiterator *gt_Sfxiterator_new_withadditionalvalues(const GtEncseq *encseq,
     sfi->bufentries = 1;
   }
   sfi->suffixsortspace = gt_suffixsortspace_new(sfi->bufentries, sfi->totallength, sfi->suftabuint, logger);
+  {
+    /* page-lock the part buffers (GTB200_PIN=0 leaves them pageable): the device copies finished slices while it
+       sorts the next ones, which pageable memory turns into synchronous copies */
+    const char *pin = getenv("GTB200_PIN");
+    if ((pin == NULL || atoi(pin) != 0) && sfi->bufentries >= (GtUword) (1UL << 20))
+    {
+      void *raw = b200_rawptr(sfi);
+      if (gtb200_host_register(raw, (size_t) sfi->bufentries * (sfi->suftabuint ? 4 : 8)) == 0)
+      {
+        sfi->pinned_suf = raw;
+      }
+    }
+  }
   if (sfi->outlcpinfo != NULL)
   {
     gt_Outlcpinfo_numsuffixes2output_set(sfi->outlcpinfo, sfi->totallength + 1);
     sfi->lcpbuf = gt_malloc(sizeof (uint8_t) * (size_t) (largest + 1));
+    if (sfi->pinned_suf != NULL && gtb200_host_register(sfi->lcpbuf, (size_t) (largest + 1)) == 0)
+    {
+      sfi->pinned_lcp = sfi->lcpbuf;
+    }
     sfi->llvcap = largest + 1;
     sfi->llvbuf = gt_malloc(sizeof (gtb200_largelcp) * (size_t) sfi->llvcap);
   }
@@ -320,9 +421,11 @@ const GtSuffixsortspace *gt_Sfxiterator_next(GtUword *numberofsuffixes, bool *sp
 
     if (sfi->sfxprogress != NULL)
     {
+      /* the reference's two phases of a part (src/match/sfx-suffixer.c:1964,2041) are one device pass here */
+      gt_timer_show_progress(sfi->sfxprogress, "inserting suffixes into buckets", stdout);
       gt_timer_show_progress(sfi->sfxprogress, "sorting the buckets", stdout);
     }
-    if (gtb200_sort_part(sfi->dev, sfi->mincodes[p], sfi->maxcodes[p], b200_rawptr(sfi), sfi->suftabuint ? 1 : 0,
+    if (gtb200_multi_sort_part(sfi->dev, sfi->mincodes[p], sfi->maxcodes[p], b200_rawptr(sfi), sfi->suftabuint ? 1 : 0,
                          sfi->lcpbuf, sfi->llvbuf, (uint64_t) sfi->llvcap, &pi) != 0)
     {
       fprintf(stderr, "gt suffixerator (B200): %s\n", gtb200_last_error());
@@ -378,7 +481,7 @@ const GtSuffixsortspace *gt_Sfxiterator_next(GtUword *numberofsuffixes, bool *sp
     {
       page = sfi->bufentries;
     }
-    if (gtb200_tail(sfi->dev, sfi->tail_done, page, b200_rawptr(sfi), sfi->suftabuint ? 1 : 0) != 0)
+    if (gtb200_multi_tail(sfi->dev, sfi->tail_done, page, b200_rawptr(sfi), sfi->suftabuint ? 1 : 0) != 0)
     {
       fprintf(stderr, "gt suffixerator (B200): %s\n", gtb200_last_error());
       exit(EXIT_FAILURE);
