@@ -148,6 +148,8 @@ struct gtb200_ctx {
   uint64_t scan_epoch;
   void *d_scratch;
   size_t cap_scratch;
+  void *d_tail;              // entries of the last gtb200_tail call (own buffer: no other call recycles it)
+  size_t cap_tail;
   std::vector<PoolBlock> blocks;   // every device allocation of this context
   // profiling
   bool prof_on;
@@ -3144,21 +3146,33 @@ extern "C" int gtb200_tail(gtb200_ctx *c, uint64_t first, uint64_t count, void *
   if (count == 0) return 0;
   CK(cudaSetDevice(c->device));
   const size_t esz = suftab_is_uint32 ? 4 : 8;
-  if (ensure_scratch(c, count * esz)) return -1;
+  if (count * esz > c->cap_tail) {
+    dfree(c, c->d_tail);
+    c->d_tail = nullptr;
+    c->cap_tail = 0;
+    CK(dmalloc(c, &c->d_tail, count * esz));
+    c->cap_tail = count * esz;
+  }
   {
     ProfScope ps(c, KC_TAIL);
     if (suftab_is_uint32)
       k_tail<uint32_t><<<grid_for(count, 256), 256, 0, c->stream>>>(c->d_ranges, c->d_rangeoff, c->nranges, c->specialchars,
-                                                                   c->n, first, count, (uint32_t *)c->d_scratch);
+                                                                   c->n, first, count, (uint32_t *)c->d_tail);
     else
       k_tail<uint64_t><<<grid_for(count, 256), 256, 0, c->stream>>>(c->d_ranges, c->d_rangeoff, c->nranges, c->specialchars,
-                                                                   c->n, first, count, (uint64_t *)c->d_scratch);
+                                                                   c->n, first, count, (uint64_t *)c->d_tail);
   }
   CK(cudaGetLastError());
   if (suftab) {                               // without a host buffer the call stays stream-ordered (device consumers)
-    CK(cudaMemcpyAsync(suftab, c->d_scratch, count * esz, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(suftab, c->d_tail, count * esz, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
   }
+  return 0;
+}
+
+extern "C" int gtb200_tail_device(gtb200_ctx *c, void **tail_dev) {
+  if (!c || !tail_dev) return set_error("gtb200_tail_device: null argument");
+  *tail_dev = c->d_tail;
   return 0;
 }
 

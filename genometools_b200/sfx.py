@@ -72,7 +72,7 @@ EXPORTS = [
     "gtb200_count_shard", "gtb200_count_finish", "gtb200_part_diag",
     "gtb200_multi_open", "gtb200_multi_close", "gtb200_multi_count", "gtb200_multi_sort_part", "gtb200_multi_tail",
     "gtb200_multi_devices", "gtb200_multi_ctx", "gtb200_multi_peer_bytes", "gtb200_host_register",
-    "gtb200_host_unregister", "gtb200_multi_free_memory",
+    "gtb200_host_unregister", "gtb200_multi_free_memory", "gtb200_tail_device",
 ]
 
 
@@ -357,14 +357,15 @@ class Sfxiterator:
 
 def suffixerator(enc: np.ndarray, alphabet: str = "dna", indexname: str | None = None, parts: int = 1,
                  prefixlength: int | None = None, device: int = 0, use_twobit: bool | None = None,
-                 readmode: int = 0, devices: list[int] | None = None) -> dict:
+                 readmode: int = 0, devices: list[int] | None = None, sigma: int | None = None) -> dict:
     """`gt suffixerator -suf -lcp -bck` on an encoded sequence: runs the iterator to exhaustion and
     returns the byte images of .suf/.lcp/.llv/.bck plus the .prj statistics; writes the files when
     ``indexname`` is given."""
-    sigma = _encseq.alphabet_size(alphabet)
+    if sigma is None:               # any other alphabet (a -smap symbol map): give its size, the sequence goes in as bytes
+        sigma = _encseq.alphabet_size(alphabet)
     n = int(enc.shape[0])
     if use_twobit is None:
-        use_twobit = alphabet == "dna"
+        use_twobit = alphabet == "dna" and sigma == 4
     if use_twobit:
         it = Sfxiterator(sigma, n, prefixlength, parts, twobit=_encseq.twobit_pack(enc),
                          ranges=_encseq.special_ranges(enc), device=device, readmode=readmode, devices=devices)

@@ -184,6 +184,10 @@ int gtb200_sort_part(gtb200_ctx *ctx, uint64_t mincode, uint64_t maxcode, void *
  * the entries are only produced on the device, stream-ordered on gtb200_stream (no host wait).
  */
 int gtb200_tail(gtb200_ctx *ctx, uint64_t first, uint64_t count, void *suftab, int suftab_is_uint32);
+/* Device pointer of the entries the last gtb200_tail call produced (GtUword or uint32_t as requested there), valid
+ * until the next gtb200_tail or gtb200_close and ordered after that call on gtb200_stream: the device-side
+ * counterpart of the page buffer gt_SSSPbuf_fillspecialnextpage fills (src/match/sfx-suffixgetset.c:586-690). */
+int gtb200_tail_device(gtb200_ctx *ctx, void **tail_dev);
 
 /* -- host-side helpers that mirror reference logic the iterator needs (pure C, no device) ---- */
 

@@ -108,14 +108,14 @@ def parse_prj(text: str) -> dict:
 
 def run_reference(fasta: str | list[str], alphabet: str = "dna", parts: int = 1, pl: int | None = None,
                   extra: list[str] | None = None, keep_dir: str | None = None,
-                  showtime: bool = False) -> dict:
+                  showtime: bool = False, drop_alphabet_flag: bool = False) -> dict:
     """`gt suffixerator -dna|-protein -suf -lcp -bck -tis` on the unmodified reference."""
     if not have_reference():
         raise RuntimeError("oracle/_ref/gt_ref is not built (run `make -C oracle`)")
     files = [fasta] if isinstance(fasta, str) else list(fasta)
     tmp = keep_dir or tempfile.mkdtemp(prefix="gtref_")
-    cmd = [GT_REF, "suffixerator", "-" + alphabet, "-suf", "-lcp", "-bck", "-tis", "-v",
-           "-indexname", os.path.join(tmp, "ref"), "-parts", str(parts)]
+    cmd = [GT_REF, "suffixerator"] + ([] if drop_alphabet_flag else ["-" + alphabet]) + \
+          ["-suf", "-lcp", "-bck", "-tis", "-v", "-indexname", os.path.join(tmp, "ref"), "-parts", str(parts)]
     if pl is not None:
         cmd += ["-pl", str(pl)]
     cmd += (extra or []) + ["-db"] + files

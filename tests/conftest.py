@@ -29,7 +29,7 @@ def load_golden(name):
     g["averagelcp"] = str(g["averagelcp"])
     for k in ("prefixlength", "longest", "maxbranchdepth", "largelcpvalues", "specialcharacters", "totallength"):
         g[k] = int(g[k])
-    g["sigma"] = 4 if g["alphabet"] == "dna" else 20
+    g["sigma"] = int(g["sigma"]) if "sigma" in g else (4 if g["alphabet"] == "dna" else 20)
     return g
 
 

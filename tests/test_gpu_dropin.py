@@ -45,7 +45,14 @@ CASES = {
     "dna_sat_bit": (lambda: synth.multi_dna_with_nruns(100_000, nseq=3, seed=97), "dna", ["-sat", "bit"]),
     "dna_lcpdist": (lambda: synth.genome_like_dna(60_000, seed=98), "dna", ["-lcpdist"]),
     "protein_parts2": (lambda: synth.random_protein(400, seed=85), "protein", ["-parts", "2"]),
+    # symbol maps (testsuite/gt_suffixerator_include.rb:17-56 runs its matrix with -smap TransDNA / TransProt11):
+    # sigma = 11 on byte text, and a three-letter map (sigma = 3: base-3 codes on the 2-bit text)
+    "smap_transprot11": (lambda: synth.random_protein(300, seed=99), "smap:prot11", ["-parts", "2"]),
+    "smap_three_letters": (lambda: None, "smap:abc", []),
 }
+
+TRANSPROT11 = "LVIFJ i\nKR +\nED -\nAG s\nST o\nNQ n\nYW a\nP p\nH h\nM m\nC c\nXUBZO*- x\n"   # gtdata/trans/TransProt11
+ABC_MAP = "aA\nbB\ncC\nxX\n"
 
 
 def _run(binary, args, cwd):
@@ -59,8 +66,23 @@ def test_gt_suffixerator_dropin_is_byte_identical(case, tmp_path):
     gen, alphabet, extra = CASES[case]
     enc = gen()
     fasta = str(tmp_path / "in.fna")
-    encseq.write_fasta(fasta, encseq.decode_to_fasta_bytes(enc, alphabet))
-    common = ["suffixerator", "-" + alphabet, "-suf", "-lcp", "-bck", "-tis", "-des", "-sds", "-ssp"] + extra
+    if alphabet.startswith("smap:"):
+        mapfile = str(tmp_path / "symbols.map")
+        if alphabet == "smap:prot11":
+            open(mapfile, "w").write(TRANSPROT11)
+            encseq.write_fasta(fasta, encseq.decode_to_fasta_bytes(enc, "protein"))
+        else:
+            open(mapfile, "w").write(ABC_MAP)
+            rng = np.random.default_rng(100)
+            with open(fasta, "wb") as fh:
+                for k in range(7):
+                    body = rng.choice(np.frombuffer(b"abcx", dtype=np.uint8), size=20_000 + 3_000 * k, p=[0.4, 0.3, 0.28, 0.02])
+                    fh.write(b">s%d\n" % k + body.tobytes() + b"\n")
+        alpha_args = ["-smap", mapfile]
+    else:
+        encseq.write_fasta(fasta, encseq.decode_to_fasta_bytes(enc, alphabet))
+        alpha_args = ["-" + alphabet]
+    common = ["suffixerator"] + alpha_args + ["-suf", "-lcp", "-bck", "-tis", "-des", "-sds", "-ssp"] + extra
     out_ref = _run(GT_REF, common + ["-indexname", "ref", "-db", fasta], str(tmp_path))
     out_b200 = _run(GT_B200, common + ["-indexname", "b200", "-db", fasta], str(tmp_path))
     if "-lcpdist" in extra:                    # the LCP histogram the reference prints on stdout

@@ -42,7 +42,8 @@ def _compare(got, want, label):
 
 def test_golden_vectors(golden):
     for parts in (1, 3):
-        got = sfx.suffixerator(golden["enc"], golden["alphabet"], parts=parts, prefixlength=golden["prefixlength"])
+        got = sfx.suffixerator(golden["enc"], golden["alphabet"], parts=parts, prefixlength=golden["prefixlength"],
+                               sigma=golden["sigma"])
         _compare(got, golden, f"{golden['name']}/parts{parts}")
     if golden["alphabet"] == "dna":   # byte input path (ranges derived on the device)
         got = sfx.suffixerator(golden["enc"], "dna", prefixlength=golden["prefixlength"], use_twobit=False)
@@ -52,7 +53,8 @@ def test_golden_vectors(golden):
 def test_golden_vectors_refinement_only(golden, monkeypatch):
     """Every bucket forced through the refinement path (segmented radix sort on text windows)."""
     monkeypatch.setenv("GTB200_MAXBUCKET", "0")
-    got = sfx.suffixerator(golden["enc"], golden["alphabet"], parts=2, prefixlength=golden["prefixlength"])
+    got = sfx.suffixerator(golden["enc"], golden["alphabet"], parts=2, prefixlength=golden["prefixlength"],
+                           sigma=golden["sigma"])
     _compare(got, golden, f"{golden['name']}/refine")
     if golden["maxbranchdepth"] > 0:   # some bucket holds at least two suffixes
         assert got["fallback_suffixes"] > 0
