@@ -177,7 +177,8 @@ extern "C" int gtb200_multi_count(gtb200_multi *m, uint32_t *leftborder, uint32_
     TablePtrs tp;
     for (int d = 0; d < m->ndev; ++d) {
       gtb200_ctx *c = m->ctx[d];
-      const uint64_t lo = std::min(n, (uint64_t)d * shard), hi = d == m->ndev - 1 ? n : std::min(n, (uint64_t)(d + 1) * shard);
+      uint64_t lo = std::min(n, (uint64_t)d * shard), hi = d == m->ndev - 1 ? n : std::min(n, (uint64_t)(d + 1) * shard);
+      if (lo >= hi) lo = hi = 0;                     // more devices than 64-position blocks: an empty shard
       void *tab = nullptr;
       if (gtb200_count_shard(c, lo, hi, d == 0 ? 1 : 0, &tab, nullptr)) return -1;
       tp.p[d] = (uint32_t *)tab;
