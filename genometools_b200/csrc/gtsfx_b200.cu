@@ -17,6 +17,8 @@
 #include <string.h>
 
 #include <mutex>
+#include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/gtsfx_b200.h"
@@ -112,6 +114,9 @@ struct gtb200_ctx {
   bool part_imaged;          // every range of the current part had its 64-bit image written by the sorters
   int fused_widen;           // 1 = direct path writes the 64-bit image from the sorters (GTB200_FUSED_WIDEN, testing knob)
   int pipeline;              // 1 = overlap D2H of finished slices with the sort of the next (GTB200_PIPELINE, testing knob)
+  int narrow;                // 1 = a GtUword suftab crosses PCIe as 32-bit positions and is widened by host threads
+                             //     (GTB200_NARROW; 0 copies the 64-bit image)
+  int widen_threads;
   cudaStream_t copy_stream;
   cudaEvent_t slice_ev[8];
   cudaStream_t side_stream;  // small kernels that are independent of the main chain (special-padded suffixes) run beside it
@@ -214,6 +219,11 @@ struct ProfScope {
 static std::mutex g_pool_mu;
 static std::vector<PoolBlock> g_pool[64];
 static std::vector<void *> g_pinned_pool;
+// page-locked ring of the narrow transfer (narrow_copy_run), cached like the device blocks
+#define NR_RING 4
+#define NR_CHUNK (16u << 20)          // entries per chunk: 64 MB in, 128 MB out
+struct NarrowRing { uint32_t *buf[NR_RING]; };
+static std::vector<NarrowRing> g_ring_pool;      // guarded by g_pool_mu
 struct StreamSet { cudaStream_t main, copy, side; cudaEvent_t ev[8], sev[2]; };
 static std::vector<StreamSet> g_stream_pool[64];   // streams and events of closed contexts, reused by the next open
 
@@ -283,6 +293,9 @@ extern "C" void gtb200_release_cached_memory(void) {
     }
   for (void *h : g_pinned_pool) cudaFreeHost(h);
   g_pinned_pool.clear();
+  for (auto &r : g_ring_pool)
+    for (int i = 0; i < NR_RING; ++i) cudaFreeHost(r.buf[i]);
+  g_ring_pool.clear();
   for (int d = 0; d < 64; ++d) {
     for (auto &ss : g_stream_pool[d]) {
       cudaStreamDestroy(ss.main);
@@ -2224,6 +2237,13 @@ static gtb200_ctx *ctx_create(int device, unsigned numofchars, uint64_t totallen
   }
   c->pipeline = 1;
   if (const char *e7 = getenv("GTB200_PIPELINE")) c->pipeline = atoi(e7);
+  c->narrow = 1;
+  if (const char *e12 = getenv("GTB200_NARROW")) c->narrow = atoi(e12);
+  {
+    unsigned hw = std::thread::hardware_concurrency();
+    c->widen_threads = hw == 0 ? 4 : hw > 16 ? 16 : (int)hw;
+    if (const char *e13 = getenv("GTB200_WIDEN_THREADS")) c->widen_threads = atoi(e13) > 0 ? atoi(e13) : 1;
+  }
   c->overlap = 1;
   if (const char *e9 = getenv("GTB200_OVERLAP")) c->overlap = atoi(e9);
   c->fused_widen = 1;
@@ -2957,6 +2977,102 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Narrow transfer of a part's suffix array: the 32-bit working array crosses PCIe in chunks through a small ring of
+// page-locked buffers, host threads widen every chunk into the caller's GtUword array while the next chunks are in
+// flight (csrc/host_logic.c, streaming stores).  Half the bus traffic of copying the 64-bit image, and the caller's
+// buffer may be ordinary pageable memory.  The ring is cached per process.
+// ---------------------------------------------------------------------------------------------
+extern "C" void gtb200_widen_u32_u64(const uint32_t *src, uint64_t *dst, size_t n);
+
+
+static bool ring_acquire(NarrowRing *r) {
+  {
+    std::lock_guard<std::mutex> lock(g_pool_mu);
+    if (!g_ring_pool.empty()) { *r = g_ring_pool.back(); g_ring_pool.pop_back(); return true; }
+  }
+  for (int i = 0; i < NR_RING; ++i) r->buf[i] = nullptr;
+  for (int i = 0; i < NR_RING; ++i)
+    if (cudaHostAlloc((void **)&r->buf[i], (size_t)NR_CHUNK * 4, cudaHostAllocPortable) != cudaSuccess) {
+      (void)cudaGetLastError();
+      for (int j = 0; j < i; ++j) cudaFreeHost(r->buf[j]);
+      return false;
+    }
+  return true;
+}
+static void ring_release(const NarrowRing &r) {
+  std::lock_guard<std::mutex> lock(g_pool_mu);
+  g_ring_pool.push_back(r);
+}
+
+static void widen_parallel(const uint32_t *src, uint64_t *dst, size_t n, int threads) {
+  if (threads <= 1 || n < (1u << 16)) { gtb200_widen_u32_u64(src, dst, n); return; }
+  std::vector<std::thread> pool;
+  const size_t per = ((n + threads - 1) / threads + 63) & ~(size_t)63;
+  for (int t = 1; t < threads; ++t) {
+    const size_t lo = (size_t)t * per;
+    if (lo >= n) break;
+    const size_t len = lo + per <= n ? per : n - lo;
+    pool.emplace_back([=]() { gtb200_widen_u32_u64(src + lo, dst + lo, len); });
+  }
+  gtb200_widen_u32_u64(src, dst, per < n ? per : n);
+  for (auto &t : pool) t.join();
+}
+
+struct NarrowJob {
+  gtb200_ctx *c;
+  uint64_t *h_suf;
+  uint8_t *h_lcp;
+  int S;
+  uint64_t boff[GTB_MAXSLICES + 1];
+  bool wait_events;            // slices become ready one by one (slice_ev[k] on the compute stream)
+  cudaStream_t stream;         // the stream the copies run on
+  int rc;
+  std::string err;
+};
+
+static void narrow_copy_run(NarrowJob *j) {
+  gtb200_ctx *c = j->c;
+  j->rc = -1;
+  if (cudaSetDevice(c->device) != cudaSuccess) { j->err = "cudaSetDevice failed in the copy thread"; return; }
+  NarrowRing ring;
+  if (!ring_acquire(&ring)) { j->err = "cudaHostAlloc of the transfer ring failed"; return; }
+  cudaEvent_t rev[NR_RING];
+  for (int i = 0; i < NR_RING; ++i) cudaEventCreateWithFlags(&rev[i], cudaEventDisableTiming);
+  struct Chunk { int slice; uint64_t off; uint32_t len; bool first, last; };
+  std::vector<Chunk> chunks;
+  for (int k = 0; k < j->S; ++k) {
+    const uint64_t lo = j->boff[k], hi = j->boff[k + 1];
+    for (uint64_t o = lo; o < hi; o += NR_CHUNK) {
+      const uint32_t len = (uint32_t)(hi - o < NR_CHUNK ? hi - o : NR_CHUNK);
+      chunks.push_back({k, o, len, o == lo, o + len == hi});
+    }
+  }
+  cudaError_t e = cudaSuccess;
+  auto issue = [&](size_t i) {
+    const Chunk &ch = chunks[i];
+    if (ch.first && j->wait_events && e == cudaSuccess) e = cudaStreamWaitEvent(j->stream, c->slice_ev[ch.slice], 0);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(ring.buf[i % NR_RING], c->d_sa + ch.off, (size_t)ch.len * 4, cudaMemcpyDeviceToHost, j->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(rev[i % NR_RING], j->stream);
+    if (ch.last && j->h_lcp && e == cudaSuccess) {
+      const uint64_t lo = j->boff[ch.slice], hi = j->boff[ch.slice + 1];
+      e = cudaMemcpyAsync(j->h_lcp + lo, c->d_lcp + lo, hi - lo, cudaMemcpyDeviceToHost, j->stream);
+    }
+  };
+  for (size_t i = 0; i < chunks.size() && i < NR_RING; ++i) issue(i);
+  for (size_t i = 0; i < chunks.size() && e == cudaSuccess; ++i) {
+    e = cudaEventSynchronize(rev[i % NR_RING]);
+    if (e != cudaSuccess) break;
+    widen_parallel(ring.buf[i % NR_RING], j->h_suf + chunks[i].off, chunks[i].len, c->widen_threads);
+    if (i + NR_RING < chunks.size()) issue(i + NR_RING);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(j->stream);
+  for (int i = 0; i < NR_RING; ++i) cudaEventDestroy(rev[i]);
+  ring_release(ring);
+  if (e != cudaSuccess) { j->err = std::string("narrow transfer: ") + cudaGetErrorString(e); return; }
+  j->rc = 0;
+}
+
 template <int BITS>
 static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb200_partinfo *info, void *h_suf,
                           int h_suf_u32, uint8_t *h_lcp) {
@@ -3029,7 +3145,16 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
       return -1;
     if (S > 1) CK(cudaEventRecord(c->slice_ev[k], c->stream));
   }
-  if (S > 1) {
+  // a GtUword suftab of a large part: 32-bit positions over the bus, widened on the host (see narrow_copy_run)
+  const bool narrow = h_suf != nullptr && !h_suf_u32 && c->narrow && width >= (4u << 20);
+  NarrowJob job;
+  std::thread copier;
+  if (S > 1 && narrow) {
+    job.c = c; job.h_suf = (uint64_t *)h_suf; job.h_lcp = h_lcp; job.S = S; job.wait_events = true;
+    job.stream = c->copy_stream;
+    for (int k = 0; k <= S; ++k) job.boff[k] = boff[k];
+    copier = std::thread(narrow_copy_run, &job);
+  } else if (S > 1) {
     for (int k = 0; k < S; ++k) {
       const uint64_t o = boff[k], w = boff[k + 1] - boff[k];
       if (w == 0) continue;
@@ -3041,7 +3166,12 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
       if (h_lcp) CK(cudaMemcpyAsync(h_lcp + o, c->d_lcp + o, w, cudaMemcpyDeviceToHost, c->copy_stream));
     }
   }
-  if (sync_stats(c)) return -1;
+  const int rc_stats = sync_stats(c);
+  if (copier.joinable()) {
+    copier.join();
+    if (job.rc) return set_error("%s", job.err.c_str());
+  }
+  if (rc_stats) return -1;
   bool copied = S > 1;
   if (S > 1) CK(cudaStreamSynchronize(c->copy_stream));
   if (c->h_stats->fb_elems != 0) {
@@ -3066,7 +3196,13 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
     if (sync_stats(c)) return -1;
     copied = false;
   }
-  if (to_host && !copied) {
+  if (to_host && !copied && narrow) {
+    job.c = c; job.h_suf = (uint64_t *)h_suf; job.h_lcp = h_lcp; job.S = 1; job.wait_events = false;
+    job.stream = c->stream;
+    job.boff[0] = 0; job.boff[1] = width;
+    narrow_copy_run(&job);
+    if (job.rc) return set_error("%s", job.err.c_str());
+  } else if (to_host && !copied) {
     if (h_suf) {
       if (h_suf_u32) CK(cudaMemcpyAsync(h_suf, c->d_sa, width * 4, cudaMemcpyDeviceToHost, c->stream));
       else CK(cudaMemcpyAsync(h_suf, c->d_suf64, width * 8, cudaMemcpyDeviceToHost, c->stream));

@@ -93,3 +93,36 @@ int gtb200_suftabparts(unsigned numofparts, const uint32_t *leftborder, uint64_t
   if (kept) maxcodes[kept - 1] = numofallcodes - 1;
   return (int) kept;
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * Host half of the narrow transfer (gtb200_sort_part with a GtUword suftab): positions cross PCIe as the 32-bit
+ * values the device sorts (totallength < 2^32 - 1) and are widened here into the GtUword entries
+ * gt_suffixsortspace_to_file writes (src/match/sfx-suffixgetset.c:462-478) - half the bytes on the bus.
+ * Streaming stores: the .suf image is written once and not read again by this code.
+ * --------------------------------------------------------------------------------------------- */
+#include <stddef.h>
+#if defined(__x86_64__)
+#include <immintrin.h>
+__attribute__((target("avx2"))) static void widen_avx2(const uint32_t *src, uint64_t *dst, size_t n)
+{
+  size_t i = 0;
+  while (i < n && ((uintptr_t) (dst + i) & 31) != 0) { dst[i] = src[i]; i++; }
+  for (; i + 8 <= n; i += 8)
+  {
+    const __m128i lo = _mm_loadu_si128((const __m128i *) (src + i));
+    const __m128i hi = _mm_loadu_si128((const __m128i *) (src + i + 4));
+    _mm256_stream_si256((__m256i *) (dst + i), _mm256_cvtepu32_epi64(lo));
+    _mm256_stream_si256((__m256i *) (dst + i + 4), _mm256_cvtepu32_epi64(hi));
+  }
+  for (; i < n; i++) dst[i] = src[i];
+  _mm_sfence();
+}
+#endif
+
+void gtb200_widen_u32_u64(const uint32_t *src, uint64_t *dst, size_t n)
+{
+#if defined(__x86_64__)
+  if (__builtin_cpu_supports("avx2")) { widen_avx2(src, dst, n); return; }
+#endif
+  for (size_t i = 0; i < n; i++) dst[i] = src[i];
+}

@@ -373,6 +373,21 @@ def test_sharded_count_equals_replicated_count():
         it.delete()
 
 
+@pytest.mark.parametrize("narrow", ["1", "0"])
+def test_narrow_transfer_matches(narrow, monkeypatch):
+    """A GtUword suftab of a large part crosses PCIe as 32-bit positions and is widened by host threads
+    (GTB200_NARROW=1, the default) - same bytes as copying the 64-bit image, also when refinement redoes the part
+    and with an odd thread count."""
+    monkeypatch.setenv("GTB200_NARROW", narrow)
+    monkeypatch.setenv("GTB200_WIDEN_THREADS", "3")
+    enc = synth.multi_dna_with_nruns(6_000_000, nseq=5, seed=191)
+    _compare(sfx.suffixerator(enc, "dna"), oracle.build(enc, 4), f"narrow{narrow}/plain")
+    rep = synth.genome_like_dna(5_500_000, seed=192)
+    got = sfx.suffixerator(rep, "dna", parts=1)
+    _compare(got, oracle.build(rep, 4), f"narrow{narrow}/repeats")
+    assert got["fallback_suffixes"] > 0
+
+
 @pytest.mark.parametrize("pipeline", ["0", "1"])
 def test_pipelined_fetch_matches(pipeline, monkeypatch):
     """gtb200_sort_part cuts a large part into code ranges and copies finished slices while the next range is
