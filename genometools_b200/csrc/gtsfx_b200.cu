@@ -3005,18 +3005,68 @@ static void ring_release(const NarrowRing &r) {
   g_ring_pool.push_back(r);
 }
 
+// Persistent host workers for the widening (spawning threads per 64 MB chunk cost a quarter of the widening time).
+// One pool per process; a job is split into equal 64-entry-aligned shares, callers are serialised by the job mutex.
+#include <condition_variable>
+struct WidenPool {
+  std::mutex job_mu;                    // one widening job at a time
+  std::mutex mu;
+  std::condition_variable cv_work, cv_done;
+  std::vector<std::thread> workers;
+  const uint32_t *src = nullptr;
+  uint64_t *dst = nullptr;
+  size_t n = 0, per = 0;
+  int shares = 0, next_share = 0, done = 0;
+  uint64_t generation = 0;
+  void worker() {
+    uint64_t seen = 0;
+    for (;;) {
+      std::unique_lock<std::mutex> lk(mu);
+      cv_work.wait(lk, [&] { return generation != seen && next_share < shares; });
+      while (next_share < shares) {
+        const int sh = next_share++;
+        const uint64_t gen = generation;
+        lk.unlock();
+        const size_t lo = (size_t)sh * per;
+        gtb200_widen_u32_u64(src + lo, dst + lo, lo + per <= n ? per : n - lo);
+        lk.lock();
+        if (gen == generation && ++done == shares) cv_done.notify_all();
+      }
+      seen = generation;
+    }
+  }
+  void run(const uint32_t *s, uint64_t *d, size_t count, int threads) {
+    std::lock_guard<std::mutex> job(job_mu);
+    {
+      std::unique_lock<std::mutex> lk(mu);
+      while ((int)workers.size() < threads - 1) {
+        workers.emplace_back([this] { worker(); });
+        workers.back().detach();
+      }
+      src = s; dst = d; n = count;
+      per = ((count + threads - 1) / threads + 63) & ~(size_t)63;
+      shares = (int)((count + per - 1) / per);
+      next_share = 0; done = 0;
+      ++generation;
+    }
+    cv_work.notify_all();
+    std::unique_lock<std::mutex> lk(mu);
+    while (next_share < shares) {                     // the calling thread takes shares too
+      const int sh = next_share++;
+      lk.unlock();
+      const size_t lo = (size_t)sh * per;
+      gtb200_widen_u32_u64(src + lo, dst + lo, lo + per <= n ? per : n - lo);
+      lk.lock();
+      if (++done == shares) cv_done.notify_all();
+    }
+    cv_done.wait(lk, [&] { return done == shares; });
+  }
+};
+static WidenPool *g_widen_pool = new WidenPool();     // never destroyed: its detached workers outlive static teardown
+
 static void widen_parallel(const uint32_t *src, uint64_t *dst, size_t n, int threads) {
   if (threads <= 1 || n < (1u << 16)) { gtb200_widen_u32_u64(src, dst, n); return; }
-  std::vector<std::thread> pool;
-  const size_t per = ((n + threads - 1) / threads + 63) & ~(size_t)63;
-  for (int t = 1; t < threads; ++t) {
-    const size_t lo = (size_t)t * per;
-    if (lo >= n) break;
-    const size_t len = lo + per <= n ? per : n - lo;
-    pool.emplace_back([=]() { gtb200_widen_u32_u64(src + lo, dst + lo, len); });
-  }
-  gtb200_widen_u32_u64(src, dst, per < n ? per : n);
-  for (auto &t : pool) t.join();
+  g_widen_pool->run(src, dst, n, threads);
 }
 
 struct NarrowJob {

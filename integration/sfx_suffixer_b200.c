@@ -55,7 +55,7 @@ struct Sfxiterator
   GtSuffixsortspace *suffixsortspace;
   GtTimer *sfxprogress;
   GtLogger *logger;
-  bool suftabuint, bck_written;
+  bool suftabuint, bck_written, pin;
   unsigned int prefixlength;
   uint32_t *leftborder, *countspecialcodes, *distpfxidx;
   gtb200_countinfo ci;
@@ -370,10 +370,13 @@ Sfxiterator *gt_Sfxiterator_new_withadditionalvalues(const GtEncseq *encseq,
   }
   sfi->suffixsortspace = gt_suffixsortspace_new(sfi->bufentries, sfi->totallength, sfi->suftabuint, logger);
   {
-    /* page-lock the part buffers (GTB200_PIN=0 leaves them pageable): the device copies finished slices while it
-       sorts the next ones, which pageable memory turns into synchronous copies */
-    const char *pin = getenv("GTB200_PIN");
-    if ((pin == NULL || atoi(pin) != 0) && sfi->bufentries >= (GtUword) (1UL << 20))
+    /* Page-lock what the device copies into directly (GTB200_PIN=0 leaves everything pageable): the lcp buffer, and
+       the suftab only when its entries are copied as they are (-suftabuint, or GTB200_NARROW=0).  A GtUword suftab
+       is otherwise filled by the library's host threads from a page-locked ring (narrow transfer) and can stay
+       pageable - registering 8 bytes per suffix would cost more than it saves. */
+    const char *pin = getenv("GTB200_PIN"), *narrow = getenv("GTB200_NARROW");
+    sfi->pin = (pin == NULL || atoi(pin) != 0) && sfi->bufentries >= (GtUword) (1UL << 20);
+    if (sfi->pin && (sfi->suftabuint || (narrow != NULL && atoi(narrow) == 0)))
     {
       void *raw = b200_rawptr(sfi);
       if (gtb200_host_register(raw, (size_t) sfi->bufentries * (sfi->suftabuint ? 4 : 8)) == 0)
@@ -386,7 +389,7 @@ Sfxiterator *gt_Sfxiterator_new_withadditionalvalues(const GtEncseq *encseq,
   {
     gt_Outlcpinfo_numsuffixes2output_set(sfi->outlcpinfo, sfi->totallength + 1);
     sfi->lcpbuf = gt_malloc(sizeof (uint8_t) * (size_t) (largest + 1));
-    if (sfi->pinned_suf != NULL && gtb200_host_register(sfi->lcpbuf, (size_t) (largest + 1)) == 0)
+    if (sfi->pin && gtb200_host_register(sfi->lcpbuf, (size_t) (largest + 1)) == 0)
     {
       sfi->pinned_lcp = sfi->lcpbuf;
     }
