@@ -2818,7 +2818,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
     if (keyed) {
       // ---- keyed records (keyed.cuh): 16 bytes per suffix, the key travels with the record ----
       CK(cudaFuncSetAttribute(k_keyed_partition_dense, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
-      CK(cudaFuncSetAttribute(k_keyed_partition_text<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
+      CK(cudaFuncSetAttribute(k_keyed_partition_sparse, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
       CK(cudaFuncSetAttribute(k_keyed_partition_rec, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
       const unsigned textblocks = grid_for(c->n, (uint64_t)KP_CHUNK * reps);
       const int whole = (lo == 0 && hi == c->numcodes - 1) ? 1 : 0;
@@ -2834,8 +2834,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
         ulonglong2 *dst = nb1 ? recX : recY;
         if (nb1) k_bins_init<<<grid_for(nb1, 256), 256, 0, c->stream>>>(c->d_lb, lo, shift1, nb1, out.partoffset, gcur1, start1);
         if (reps > 1)
-          k_keyed_partition_text<false><<<textblocks, 256, KP_SMEM, c->stream>>>(T2, c->cp.pl, c->n, lo, hi, whole, sh, nb, reps,
-                                                                                 gc, dst);
+          k_keyed_partition_sparse<<<textblocks, 256, KP_SMEM, c->stream>>>(T2, c->cp.pl, c->n, lo, hi, sh, nb, reps, gc, dst);
         else
           k_keyed_partition_dense<<<textblocks, 256, KP_SMEM, c->stream>>>(T2, c->cp.pl, c->n, lo, hi, whole, sh, nb, gc, dst);
         if (nb1) {

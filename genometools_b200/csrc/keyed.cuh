@@ -11,9 +11,9 @@
 // records.  Against the 8-byte records of tiles.cuh this adds 32 bytes of streaming per suffix and removes one
 // random 64-byte DRAM access per suffix (3.1 Gbp: the text is 775 MB, L2 126 MB).
 //
-//   k_keyed_partition_text   block = 256 threads x 16 positions (x reps when the code range selects only a
-//                            fraction of the suffixes); counts per bin in shared memory, one global reservation
-//                            per block and bin, records staged bin by bin and written as contiguous runs.
+//   k_keyed_partition_dense / _sparse   block = 256 threads x 16 positions (x reps when the code range selects
+//                            only a fraction of the suffixes); counts per bin in shared memory, one global
+//                            reservation per block and bin, records staged bin by bin, written as contiguous runs.
 //   k_keyed_partition_rec    block = 512 threads x 8 records of one level-1 bin, same scheme.
 //   k_tile_sort_keyed        tiles.cuh's tile sorter with the gather removed.
 // Included by gtsfx_b200.cu after tiles.cuh.
@@ -127,14 +127,16 @@ __device__ __forceinline__ ulonglong2 kp_record(const KpWin &k, int i, uint64_t 
   return r;
 }
 
-// Level 1, from the text.  Block b scans positions [b*reps*4096, (b+1)*reps*4096); bin = (code-mincode)>>shift.
-// DENSE (reps == 1, every block stages at most 4096 records): the thread's text window stays in registers
-// between the counting and the staging pass.
-template <bool DENSE>
-__global__ void __launch_bounds__(256) k_keyed_partition_text(Text<2> T, unsigned pl, uint64_t n, uint64_t mincode,
-                                                               uint64_t maxcode, int whole, int shift, uint32_t nbins,
-                                                               int reps, uint32_t *__restrict__ gcursor,
-                                                               ulonglong2 *__restrict__ rec_out) {
+// Level 1 when the code range selects only a fraction of the suffixes (one of P parts, one of N GPUs, one slice of
+// the pipelined fetch): block b scans positions [b*reps*4096, (b+1)*reps*4096), reps <= 8, so that it still collects
+// about 4096 records; bin = (code-mincode)>>shift.  Same funnel-shift extraction as the dense kernel below for
+// windows without specials; only the selected positions (about 16/reps per thread and repetition) reach the
+// shared-memory atomics.  A block that collects more than the staging buffer holds writes its records straight to
+// their reserved ranges (correct, just not coalesced).
+__global__ void __launch_bounds__(256) k_keyed_partition_sparse(Text<2> T, unsigned pl, uint64_t n, uint64_t mincode,
+                                                                 uint64_t maxcode, int shift, uint32_t nbins, int reps,
+                                                                 uint32_t *__restrict__ gcursor,
+                                                                 ulonglong2 *__restrict__ rec_out) {
   extern __shared__ __align__(16) unsigned char kp_raw[];
   ulonglong2 *stage = (ulonglong2 *)kp_raw;
   uint32_t *h = (uint32_t *)(stage + KP_CHUNK);
@@ -142,28 +144,37 @@ __global__ void __launch_bounds__(256) k_keyed_partition_text(Text<2> T, unsigne
   uint32_t *misc = lstart + SP_MAXBINS;
   for (uint32_t i = threadIdx.x; i < nbins; i += 256) h[i] = 0;
   __syncthreads();
-  if (DENSE) reps = 1;
   const uint64_t pbase = (uint64_t)blockIdx.x * reps * KP_CHUNK + (uint64_t)threadIdx.x * KP_PPT;
-  uint32_t selbits[DENSE ? 1 : KP_MAXREPS / 2];          // 16 selection bits per repetition, two repetitions per word
-  KpWin kd;                                               // DENSE: the one window of this thread
-  kd.w0 = kd.w1 = kd.w2 = 0; kd.mw = kd.mw1 = ~0ull; kd.o0 = 0;
+  const unsigned cs = 32u - 2u * pl;
+  const uint32_t min32 = (uint32_t)mincode, max32 = (uint32_t)maxcode;
+  uint64_t sb0 = 0, sb1 = 0;                             // 16 selection bits per repetition
+#pragma unroll 1
+  for (int rep = 0; rep < reps; ++rep) {
+    const uint64_t p0 = pbase + (uint64_t)rep * KP_CHUNK;
+    if (p0 >= n) break;
+    const KpWin k = kp_load(T, p0);
+    uint32_t sel = 0;
+    if (k.mw == 0ull && (k.mw1 & 0x7fffull) == 0ull) {
+      const uint32_t u0 = k.o0 == 0 ? (uint32_t)(k.w0 >> 32) : (uint32_t)k.w0;
+      const uint32_t u1 = k.o0 == 0 ? (uint32_t)k.w0 : (uint32_t)(k.w1 >> 32);
 #pragma unroll
-  for (int rep = 0; rep < (DENSE ? 1 : KP_MAXREPS); ++rep) {
-    if ((rep & 1) == 0) selbits[rep >> 1] = 0;
-    if (rep < reps) {
-      const uint64_t p0 = pbase + (uint64_t)rep * KP_CHUNK;
-      if (p0 < n) {
-        const KpWin k = kp_load(T, p0);
-        if (DENSE) kd = k;
-        uint32_t sel = kp_select(k, pl, mincode, maxcode, whole != 0);
-        selbits[rep >> 1] |= sel << ((rep & 1) * 16);
-        while (sel) {
-          const int i = __ffs(sel) - 1;
-          sel &= sel - 1;
-          atomicAdd(&h[(uint32_t)((kp_code(k, i, pl) - mincode) >> shift)], 1u);
+      for (int i = 0; i < KP_PPT; ++i) {
+        const uint32_t code = (i ? __funnelshift_l(u1, u0, 2 * i) : u0) >> cs;
+        if (code >= min32 && code <= max32) {
+          sel |= 1u << i;
+          atomicAdd(&h[(code - min32) >> shift], 1u);
         }
       }
+    } else {
+      sel = kp_select(k, pl, mincode, maxcode, false);
+      uint32_t s2 = sel;
+      while (s2) {
+        const int i = __ffs(s2) - 1;
+        s2 &= s2 - 1;
+        atomicAdd(&h[(uint32_t)((kp_code(k, i, pl) - mincode) >> shift)], 1u);
+      }
     }
+    if (rep < 4) sb0 |= (uint64_t)sel << (16 * rep); else sb1 |= (uint64_t)sel << (16 * (rep - 4));
   }
   __syncthreads();
   const uint32_t total = kp_scan_bins<256>(h, lstart, nbins, misc);
@@ -174,15 +185,37 @@ __global__ void __launch_bounds__(256) k_keyed_partition_text(Text<2> T, unsigne
   }
   __syncthreads();
   const bool staged = total <= KP_CHUNK;
+#pragma unroll 1
+  for (int rep = 0; rep < reps; ++rep) {
+    const uint32_t sel = (uint32_t)((rep < 4 ? sb0 >> (16 * rep) : sb1 >> (16 * (rep - 4))) & 0xffffull);
+    if (!sel) continue;
+    const uint64_t p0 = pbase + (uint64_t)rep * KP_CHUNK;
+    const KpWin k = kp_load(T, p0);
+    if (k.mw == 0ull && (k.mw1 & 0x7fffull) == 0ull) {
+      uint32_t u0, u1, u2, u3;
+      if (k.o0 == 0) { u0 = (uint32_t)(k.w0 >> 32); u1 = (uint32_t)k.w0; u2 = (uint32_t)(k.w1 >> 32); u3 = (uint32_t)k.w1; }
+      else           { u0 = (uint32_t)k.w0; u1 = (uint32_t)(k.w1 >> 32); u2 = (uint32_t)k.w1; u3 = (uint32_t)(k.w2 >> 32); }
+      const unsigned ks = 2u * pl;
+      const uint32_t v0 = __funnelshift_l(u1, u0, ks), v1 = __funnelshift_l(u2, u1, ks), v2 = __funnelshift_l(u3, u2, ks);
 #pragma unroll
-  for (int rep = 0; rep < (DENSE ? 1 : KP_MAXREPS); ++rep) {
-    uint32_t sel = (selbits[rep >> 1] >> ((rep & 1) * 16)) & 0xffffu;
-    if (sel) {
-      const uint64_t p0 = pbase + (uint64_t)rep * KP_CHUNK;
-      const KpWin k = DENSE ? kd : kp_load(T, p0);
-      while (sel) {
-        const int i = __ffs(sel) - 1;
-        sel &= sel - 1;
+      for (int i = 0; i < KP_PPT; ++i) {
+        if ((sel >> i) & 1u) {
+          const uint32_t code = (i ? __funnelshift_l(u1, u0, 2 * i) : u0) >> cs;
+          const uint32_t bin = (code - min32) >> shift;
+          ulonglong2 rec;
+          rec.x = ((uint64_t)((63u << 26) | code) << 32) | (uint64_t)(uint32_t)(p0 + i);
+          rec.y = ((uint64_t)(i ? __funnelshift_l(v1, v0, 2 * i) : v0) << 32) |
+                  (uint64_t)((i ? __funnelshift_l(v2, v1, 2 * i) : v1) & 0xffffff00u);
+          const uint32_t r = atomicAdd(&lstart[bin], 1u);
+          if (staged) stage[r] = rec;
+          else rec_out[h[bin] + r] = rec;
+        }
+      }
+    } else {
+      uint32_t s2 = sel;
+      while (s2) {
+        const int i = __ffs(s2) - 1;
+        s2 &= s2 - 1;
         const uint64_t code = kp_code(k, i, pl);
         const uint32_t bin = (uint32_t)((code - mincode) >> shift);
         const ulonglong2 rec = kp_record(k, i, p0, pl, code);
@@ -196,7 +229,7 @@ __global__ void __launch_bounds__(256) k_keyed_partition_text(Text<2> T, unsigne
   __syncthreads();
   for (uint32_t i = threadIdx.x; i < total; i += 256) {
     const ulonglong2 r = stage[i];
-    const uint32_t bin = (uint32_t)((((r.x >> 32) & REC_CODE_MASK) - mincode) >> shift);
+    const uint32_t bin = (((uint32_t)(r.x >> 32) & (uint32_t)REC_CODE_MASK) - min32) >> shift;
     __stcs(rec_out + h[bin] + i, r);
   }
 }

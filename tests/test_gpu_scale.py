@@ -33,10 +33,13 @@ def _build_and_hash(name, parts):
     n = int(enc.shape[0])
     sigma = encseq.alphabet_size(alphabet)
     enc_sha = hashlib.sha256(enc.data).hexdigest()
+    # GTB200_TEST_DEVICES=0,1,...: the same check through gtb200_multi_* (every part spread over the listed GPUs)
+    devices = [int(x) for x in os.environ["GTB200_TEST_DEVICES"].split(",")] if os.environ.get("GTB200_TEST_DEVICES") else None
     if alphabet == "dna":
-        it = sfx.Sfxiterator(sigma, n, None, parts, twobit=encseq.twobit_pack(enc), ranges=encseq.special_ranges(enc))
+        it = sfx.Sfxiterator(sigma, n, None, parts, twobit=encseq.twobit_pack(enc), ranges=encseq.special_ranges(enc),
+                             devices=devices)
     else:
-        it = sfx.Sfxiterator(sigma, n, None, parts, enc=enc)
+        it = sfx.Sfxiterator(sigma, n, None, parts, enc=enc, devices=devices)
     del enc
     h = {k: hashlib.sha256() for k in ("suf", "lcp", "llv")}
     size = {k: 0 for k in ("suf", "lcp", "llv")}
