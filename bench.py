@@ -282,6 +282,10 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
+    if world > 1:
+        # one PCIe link per rank: the host cores that would widen 32-bit positions are the narrower resource then
+        # (the library's own multi-GPU handle makes the same choice, csrc/multi.cuh)
+        os.environ.setdefault("GTB200_NARROW", "0")
     L = sfx.load_library()
     alphabet = "protein" if args.workload == "protein" else "dna"
     sigma = encseq.alphabet_size(alphabet)
