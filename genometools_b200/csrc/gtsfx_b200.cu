@@ -2839,7 +2839,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
           k_keyed_partition_dense<<<textblocks, 256, KP_SMEM, c->stream>>>(T2, c->cp.pl, c->n, lo, hi, whole, sh, nb, gc, dst);
         if (nb1) {
           k_keyed_chunk_table<<<1, 256, 0, c->stream>>>(start1, gcur1, nb1, blkfirst);
-          const unsigned recblocks = (unsigned)(rwidth / KP_CHUNK + nb1 + 1);
+          const unsigned recblocks = (unsigned)(rwidth / (KP_CHUNK * KP_SUPER) + nb1 + 1);
           k_keyed_partition_rec<<<recblocks, 512, KP_SMEM, c->stream>>>(lo, shiftF, 1u << (shift1 - shiftF), recX, start1, gcur1,
                                                                         blkfirst, nb1, shift1, gcurF, recY);
         }

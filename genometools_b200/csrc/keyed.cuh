@@ -290,9 +290,13 @@ __global__ void __launch_bounds__(256) k_keyed_partition_dense(Text<2> T, unsign
   __syncthreads();
   const uint32_t total = kp_scan_bins<256>(h, lstart, nbins, misc);
   __syncthreads();
-  for (uint32_t i = threadIdx.x; i < nbins; i += 256) {
-    const uint32_t cnt = h[i];
-    h[i] = cnt ? atomicAdd(&gcursor[i], cnt) - lstart[i] : 0u;      // global index = h[bin] + local index
+  // reservations first (four bins per thread); their round trip hides behind the staging below
+  uint32_t res[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const uint32_t i = threadIdx.x + q * 256;
+    const uint32_t cnt = i < nbins ? h[i] : 0u;
+    res[q] = cnt ? atomicAdd(&gcursor[i], cnt) : 0u;
   }
   if (clean) {
     // the stream advanced by pl bases: the key of position p0+i is the 56 bits at bit offset 2 i of v0 v1 v2
@@ -320,6 +324,11 @@ __global__ void __launch_bounds__(256) k_keyed_partition_dense(Text<2> T, unsign
       }
     }
   }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const uint32_t i = threadIdx.x + q * 256;
+    if (i < nbins) h[i] = res[q] - lstart[i];             // global index = h[bin] + local index (own bins only)
+  }
   __syncthreads();
   for (uint32_t i = threadIdx.x; i < total; i += 256) {
     const ulonglong2 r = stage[i];
@@ -328,9 +337,13 @@ __global__ void __launch_bounds__(256) k_keyed_partition_dense(Text<2> T, unsign
   }
 }
 
-// Level 2, from the records of one level-1 bin.  Block b handles one 4096-record chunk (blk_first = prefix sums of
-// the parents' chunk counts, chunk size KP_CHUNK); bin = child index inside the parent.
-__global__ void __launch_bounds__(512) k_keyed_partition_rec(uint64_t mincode, int shift, uint32_t nbins,
+// Level 2, from the records of one level-1 bin.  Block b handles KP_SUPER consecutive 4096-record chunks of one
+// parent (blk_first = prefix sums of the parents' block counts); bin = child index inside the parent.  Two things
+// keep the memory pipe busy although only two such blocks fit an SM: the records of chunk j+1 are requested before
+// chunk j is written out, and the global reservations of a chunk are issued before its records are staged, so their
+// round trip is hidden behind the staging.
+#define KP_SUPER 4
+__global__ void __launch_bounds__(512, 2) k_keyed_partition_rec(uint64_t mincode, int shift, uint32_t nbins,
                                                               const ulonglong2 *__restrict__ rec_in,
                                                               const uint32_t *__restrict__ seg_start,
                                                               const uint32_t *__restrict__ seg_end,
@@ -341,8 +354,7 @@ __global__ void __launch_bounds__(512) k_keyed_partition_rec(uint64_t mincode, i
   ulonglong2 *stage = (ulonglong2 *)kp_raw;
   uint32_t *h = (uint32_t *)(stage + KP_CHUNK);
   uint32_t *lstart = h + SP_MAXBINS;
-  uint32_t *misc = lstart + SP_MAXBINS;                // [0..15] scan scratch, [8] parent, [9] chunk (read before the scan)
-  for (uint32_t i = threadIdx.x; i < nbins; i += 512) h[i] = 0;
+  uint32_t *misc = lstart + SP_MAXBINS;                // [0..15] scan scratch, [8] parent, [9] block inside the parent
   if (threadIdx.x == 0) {
     uint32_t lo2 = 0, hi2 = nparents;                  // blk_first[lo2] <= blockIdx.x < blk_first[hi2]
     if (blockIdx.x >= blk_first[nparents]) {
@@ -360,51 +372,80 @@ __global__ void __launch_bounds__(512) k_keyed_partition_rec(uint64_t mincode, i
   const uint32_t parent = misc[8];
   if (parent == 0xffffffffu) return;
   const uint32_t sbeg = seg_start[parent], send = seg_end[parent];
-  const uint32_t rbeg = sbeg + misc[9] * KP_CHUNK;
-  const uint32_t rcnt = send - rbeg < KP_CHUNK ? send - rbeg : KP_CHUNK;
+  const uint32_t rbeg0 = sbeg + misc[9] * (KP_CHUNK * KP_SUPER);
+  const uint32_t rend = send - rbeg0 < KP_CHUNK * KP_SUPER ? send : rbeg0 + KP_CHUNK * KP_SUPER;
   const uint64_t binbase = (uint64_t)parent << (parent_shift - shift);
+  const uint32_t c0 = (uint32_t)mincode;
   ulonglong2 r8[8];
-  uint32_t rk[4];
+  {
+    const uint32_t rcnt = rend - rbeg0 < KP_CHUNK ? rend - rbeg0 : KP_CHUNK;
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const uint32_t j = k * 512 + threadIdx.x;
-    r8[k] = j < rcnt ? __ldcs(rec_in + rbeg + j) : make_ulonglong2(0ull, 0ull);
-  }
-#pragma unroll
-  for (int k = 0; k < 4; ++k) rk[k] = 0;
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const uint32_t j = k * 512 + threadIdx.x;
-    if (j < rcnt) {
-      const uint32_t bin = (uint32_t)(((((r8[k].x >> 32) & REC_CODE_MASK) - mincode) >> shift) - binbase);
-      const uint32_t q = atomicAdd(&h[bin], 1u);
-      rk[k >> 1] |= q << ((k & 1) * 16);
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t j = k * 512 + threadIdx.x;
+      r8[k] = j < rcnt ? __ldcs(rec_in + rbeg0 + j) : make_ulonglong2(0ull, 0ull);
     }
   }
-  __syncthreads();
-  const uint32_t total = kp_scan_bins<512>(h, lstart, nbins, misc);
-  __syncthreads();
-  for (uint32_t i = threadIdx.x; i < nbins; i += 512) {
-    const uint32_t cnt = h[i];
-    h[i] = cnt ? atomicAdd(&gcursor[binbase + i], cnt) - lstart[i] : 0u;
-  }
+  for (uint32_t rbeg = rbeg0; rbeg < rend; rbeg += KP_CHUNK) {
+    const uint32_t rcnt = rend - rbeg < KP_CHUNK ? rend - rbeg : KP_CHUNK;
+    __syncthreads();                                   // scan scratch read / previous chunk written out
+    for (uint32_t i = threadIdx.x; i < nbins; i += 512) h[i] = 0;
+    __syncthreads();
+    uint32_t rk[4];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const uint32_t j = k * 512 + threadIdx.x;
-    if (j < rcnt) {
-      const uint32_t bin = (uint32_t)(((((r8[k].x >> 32) & REC_CODE_MASK) - mincode) >> shift) - binbase);
-      stage[lstart[bin] + ((rk[k >> 1] >> ((k & 1) * 16)) & 0xffffu)] = r8[k];
+    for (int k = 0; k < 4; ++k) rk[k] = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t j = k * 512 + threadIdx.x;
+      if (j < rcnt) {
+        const uint32_t bin = (uint32_t)(((((uint32_t)(r8[k].x >> 32) & (uint32_t)REC_CODE_MASK) - c0) >> shift) - binbase);
+        const uint32_t q = atomicAdd(&h[bin], 1u);
+        rk[k >> 1] |= q << ((k & 1) * 16);
+      }
     }
-  }
-  __syncthreads();
-  for (uint32_t i = threadIdx.x; i < total; i += 512) {
-    const ulonglong2 r = stage[i];
-    const uint32_t bin = (uint32_t)(((((r.x >> 32) & REC_CODE_MASK) - mincode) >> shift) - binbase);
-    __stcs(rec_out + h[bin] + i, r);
+    __syncthreads();
+    const uint32_t total = kp_scan_bins<512>(h, lstart, nbins, misc);
+    __syncthreads();
+    // reservations first (two bins per thread), their results are needed only after the staging
+    uint32_t res[2];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const uint32_t i = threadIdx.x + q * 512;
+      const uint32_t cnt = i < nbins ? h[i] : 0u;
+      res[q] = cnt ? atomicAdd(&gcursor[binbase + i], cnt) : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t j = k * 512 + threadIdx.x;
+      if (j < rcnt) {
+        const uint32_t bin = (uint32_t)(((((uint32_t)(r8[k].x >> 32) & (uint32_t)REC_CODE_MASK) - c0) >> shift) - binbase);
+        stage[lstart[bin] + ((rk[k >> 1] >> ((k & 1) * 16)) & 0xffffu)] = r8[k];
+      }
+    }
+    __syncthreads();                                   // every h[] was read by the reservation, every record is staged
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const uint32_t i = threadIdx.x + q * 512;
+      if (i < nbins) h[i] = res[q] - lstart[i];        // global index = h[bin] + local index
+    }
+    if (rbeg + KP_CHUNK < rend) {                      // next chunk's records: in flight during the write-out
+      const uint32_t nb = rbeg + KP_CHUNK;
+      const uint32_t ncnt = rend - nb < KP_CHUNK ? rend - nb : KP_CHUNK;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const uint32_t j = k * 512 + threadIdx.x;
+        r8[k] = j < ncnt ? __ldcs(rec_in + nb + j) : make_ulonglong2(0ull, 0ull);
+      }
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < total; i += 512) {
+      const ulonglong2 r = stage[i];
+      const uint32_t bin = (uint32_t)(((((uint32_t)(r.x >> 32) & (uint32_t)REC_CODE_MASK) - c0) >> shift) - binbase);
+      __stcs(rec_out + h[bin] + i, r);
+    }
   }
 }
 
-// blk_first[0..nparents]: prefix sums of ceil(records/KP_CHUNK) per level-1 bin (single block)
+// blk_first[0..nparents]: prefix sums of ceil(records/(KP_SUPER*KP_CHUNK)) per level-1 bin (single block)
 __global__ void __launch_bounds__(256) k_keyed_chunk_table(const uint32_t *__restrict__ seg_start,
                                                            const uint32_t *__restrict__ seg_end, uint32_t nparents,
                                                            uint32_t *blk_first) {
@@ -412,7 +453,7 @@ __global__ void __launch_bounds__(256) k_keyed_chunk_table(const uint32_t *__res
   uint32_t carry = 0;
   for (uint32_t base = 0; base < nparents; base += 256) {
     const uint32_t i = base + threadIdx.x;
-    const uint32_t v = i < nparents ? (seg_end[i] - seg_start[i] + KP_CHUNK - 1) / KP_CHUNK : 0;
+    const uint32_t v = i < nparents ? (seg_end[i] - seg_start[i] + KP_CHUNK * KP_SUPER - 1) / (KP_CHUNK * KP_SUPER) : 0;
     uint32_t tot;
     const uint32_t ex = block_excl_scan256(v, &tot, sm);
     if (i < nparents) blk_first[i] = carry + ex;
