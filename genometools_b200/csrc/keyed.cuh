@@ -148,11 +148,17 @@ __global__ void __launch_bounds__(256) k_keyed_partition_sparse(Text<2> T, unsig
   const unsigned cs = 32u - 2u * pl;
   const uint32_t min32 = (uint32_t)mincode, max32 = (uint32_t)maxcode;
   uint64_t sb0 = 0, sb1 = 0;                             // 16 selection bits per repetition
+  // the window of repetition r+1 is requested before repetition r is processed: one memory round trip per pass
+  // instead of one per repetition (the scan is latency-, not bandwidth-bound: a rank reads the text once)
+  KpWin knext;
+  knext.w0 = knext.w1 = knext.w2 = 0; knext.mw = knext.mw1 = ~0ull; knext.o0 = 0;
+  if (pbase < n) knext = kp_load(T, pbase);
 #pragma unroll 1
   for (int rep = 0; rep < reps; ++rep) {
     const uint64_t p0 = pbase + (uint64_t)rep * KP_CHUNK;
     if (p0 >= n) break;
-    const KpWin k = kp_load(T, p0);
+    const KpWin k = knext;
+    if (rep + 1 < reps && p0 + KP_CHUNK < n) knext = kp_load(T, p0 + KP_CHUNK);
     uint32_t sel = 0;
     if (k.mw == 0ull && (k.mw1 & 0x7fffull) == 0ull) {
       const uint32_t u0 = k.o0 == 0 ? (uint32_t)(k.w0 >> 32) : (uint32_t)k.w0;
@@ -185,12 +191,15 @@ __global__ void __launch_bounds__(256) k_keyed_partition_sparse(Text<2> T, unsig
   }
   __syncthreads();
   const bool staged = total <= KP_CHUNK;
+  if (pbase < n) knext = kp_load(T, pbase);
 #pragma unroll 1
   for (int rep = 0; rep < reps; ++rep) {
     const uint32_t sel = (uint32_t)((rep < 4 ? sb0 >> (16 * rep) : sb1 >> (16 * (rep - 4))) & 0xffffull);
-    if (!sel) continue;
     const uint64_t p0 = pbase + (uint64_t)rep * KP_CHUNK;
-    const KpWin k = kp_load(T, p0);
+    if (p0 >= n) break;
+    const KpWin k = knext;
+    if (rep + 1 < reps && p0 + KP_CHUNK < n) knext = kp_load(T, p0 + KP_CHUNK);
+    if (!sel) continue;
     if (k.mw == 0ull && (k.mw1 & 0x7fffull) == 0ull) {
       uint32_t u0, u1, u2, u3;
       if (k.o0 == 0) { u0 = (uint32_t)(k.w0 >> 32); u1 = (uint32_t)k.w0; u2 = (uint32_t)(k.w1 >> 32); u3 = (uint32_t)k.w1; }

@@ -278,8 +278,21 @@ class Sfxiterator:
         if self._part < len(self.parts):
             mincode, maxcode, width = self.parts[self._part]
             self._part += 1
-            suf = np.empty(width, dtype=np.uint32 if self.suftabuint else np.uint64)
-            lcp = np.empty(width, dtype=np.uint8)
+            if self.devices and len(self.devices) > 1:
+                # several GPUs copy straight into the part buffers: one page-locked pair for all parts (the returned
+                # arrays are views, valid until the next call - gt_Sfxiterator_next's own contract)
+                if getattr(self, "_sufbuf", None) is None:
+                    largest = max(w for _, _, w in self.parts)
+                    self._sufbuf = np.empty(max(largest, 1), dtype=np.uint32 if self.suftabuint else np.uint64)
+                    self._lcpbuf = np.empty(max(largest, 1), dtype=np.uint8)
+                    self._registered = []
+                    for b in (self._sufbuf, self._lcpbuf):
+                        if self._L.gtb200_host_register(b.ctypes.data, b.nbytes) == 0:
+                            self._registered.append(b)
+                suf, lcp = self._sufbuf[:width], self._lcpbuf[:width]
+            else:
+                suf = np.empty(width, dtype=np.uint32 if self.suftabuint else np.uint64)
+                lcp = np.empty(width, dtype=np.uint8)
             info = PartInfo()
             if self.devices:
                 llvbuf = np.empty((max(width, 1), 2), dtype=np.uint64)      # untouched pages cost nothing
@@ -340,6 +353,9 @@ class Sfxiterator:
         return {names[i].decode(): (ms[i], int(ln[i])) for i in range(k)}
 
     def delete(self) -> None:
+        for b in getattr(self, "_registered", []):
+            self._L.gtb200_host_unregister(b.ctypes.data)
+        self._registered = []
         if self._multi:
             self._L.gtb200_multi_close(self._multi)
             self._multi = C.c_void_p()

@@ -371,12 +371,12 @@ Sfxiterator *gt_Sfxiterator_new_withadditionalvalues(const GtEncseq *encseq,
   sfi->suffixsortspace = gt_suffixsortspace_new(sfi->bufentries, sfi->totallength, sfi->suftabuint, logger);
   {
     /* Page-lock what the device copies into directly (GTB200_PIN=0 leaves everything pageable): the lcp buffer, and
-       the suftab only when its entries are copied as they are (-suftabuint, or GTB200_NARROW=0).  A GtUword suftab
+       the suftab only when its entries are copied as they are (-suftabuint, several GPUs, GTB200_NARROW=0).  A GtUword suftab
        is otherwise filled by the library's host threads from a page-locked ring (narrow transfer) and can stay
        pageable - registering 8 bytes per suffix would cost more than it saves. */
     const char *pin = getenv("GTB200_PIN"), *narrow = getenv("GTB200_NARROW");
     sfi->pin = (pin == NULL || atoi(pin) != 0) && sfi->bufentries >= (GtUword) (1UL << 20);
-    if (sfi->pin && (sfi->suftabuint || (narrow != NULL && atoi(narrow) == 0)))
+    if (sfi->pin && (sfi->suftabuint || ndev > 1 || (narrow != NULL && atoi(narrow) == 0)))
     {
       void *raw = b200_rawptr(sfi);
       if (gtb200_host_register(raw, (size_t) sfi->bufentries * (sfi->suftabuint ? 4 : 8)) == 0)
