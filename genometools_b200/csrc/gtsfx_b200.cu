@@ -2343,7 +2343,8 @@ static int count_impl(gtb200_ctx *c, bool need_host_values, uint64_t pos_lo, uin
   if (pos_hi > pos_lo) {
     // A table larger than L2 is filled slice by slice (64 MB of counters per pass over the text), so
     // that the RED.ADDs always hit L2-resident lines; the text scan itself is cheap (n/4 bytes).
-    const uint64_t slice = 1ull << 24;
+    uint64_t slice = 1ull << 24;
+    if (const char *es = getenv("GTB200_COUNT_SLICE_LOG2")) slice = 1ull << atoi(es);     // testing knob
     if (c->numcodes * 4 <= (96ull << 20)) {
       ProfScope ps(c, KC_COUNT);
       k_kmers<BITS, 0><<<grid_for((pos_hi - pos_lo + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, pos_lo, pos_hi, c->d_lb, nullptr, 0, 0, 0);

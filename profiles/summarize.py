@@ -1,6 +1,7 @@
 """Turns the ncu exports under gpurun_out/ into the small tracked summaries in profiles/.
     python profiles/summarize.py launches gpurun_out/r1_launches_ecoli.csv > profiles/r1_launches_ecoli_summary.txt
     python profiles/summarize.py raw gpurun_out/r1_prof_ecoli.ncu-rep > profiles/r1_ncu_full_ecoli.txt
+    python profiles/summarize.py traffic gpurun_out/r2_launches_human.csv human     # -> profiles/ncu_traffic.json
 """
 import collections
 import csv
@@ -49,5 +50,46 @@ def raw(path):
                 print(f"   {k} = {r[hdr.index(k)]} {units[hdr.index(k)]}")
 
 
+# kernel name -> bench.py kernel class (the ProfScope classes of csrc/gtsfx_b200.cu)
+CLASS_OF = [("k_kmers<2, 0>", "count"), ("k_kmers<2, 2>", "count"), ("k_kmers<8, 0>", "count"), ("k_kmers<8, 2>", "count"),
+            ("k_kmers<2, 1>", "scatter"), ("k_kmers<8, 1>", "scatter"), ("k_keyed_partition", "scatter"),
+            ("k_stage_partition", "scatter"), ("k_partition", "scatter"), ("k_scatter_", "scatter"), ("k_bins_init", "scatter"),
+            ("k_keyed_chunk_table", "scatter"), ("k_chunk_table", "scatter"), ("k_tile_sort", "sort_lcp"),
+            ("k_sort_buckets", "sort_lcp"), ("k_sort_medium", "sort_medium"), ("k_boundary", "boundary"),
+            ("k_part_first", "boundary"), ("k_widen", "widen"), ("k_tail", "tail"), ("k_part_init", "part_init"),
+            ("k_padded", "padded"), ("k_place_padded", "padded")]
+
+
+def traffic(path, workload, out="profiles/ncu_traffic.json"):
+    """dram bytes (read + write) per step and kernel class from a launch list taken with
+    --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum; steps = launches of k_part_init."""
+    import json
+    import os
+    lines = [l for l in open(path) if not l.startswith("==")]
+    per = collections.defaultdict(float)
+    steps = 0
+    for row in csv.DictReader(lines):
+        name = row["Kernel Name"]
+        if row["Metric Name"] == "gpu__time_duration.sum" and name.startswith("k_part_init"):
+            steps += 1
+        if not row["Metric Name"].startswith("dram__bytes"):
+            continue
+        unit = row.get("Metric Unit", "byte")
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1.0)
+        for key, cls in CLASS_OF:
+            if key in name:
+                per[cls] += float(row["Metric Value"].replace(",", "")) * scale
+                break
+    db = json.load(open(out)) if os.path.exists(out) else {}
+    db[workload] = {k: v / max(steps, 1) for k, v in per.items()}
+    db[workload]["source"] = os.path.basename(path)
+    db[workload]["steps_in_capture"] = steps
+    json.dump(db, open(out, "w"), indent=1, sort_keys=True)
+    print(json.dumps(db[workload], indent=1))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "raw": raw}[sys.argv[1]](sys.argv[2])
+    if sys.argv[1] == "traffic":
+        traffic(sys.argv[2], sys.argv[3])
+    else:
+        {"launches": launches, "raw": raw}[sys.argv[1]](sys.argv[2])
