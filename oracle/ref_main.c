@@ -5,6 +5,9 @@
  *   gt_ref suffixerator <args>   -> gt_parseargsandcallsuffixerator (src/match/sfx-run.c:719),
  *                                   what `gt suffixerator` runs (src/tools/gt_suffixerator.c:22-26)
  *   gt_ref sfxmap <args>         -> the checker tool `gt dev sfxmap` (src/tools/gt_sfxmap.c)
+ *   gt_ref packedindex <args>    -> `gt packedindex` (src/tools/gt_packedindex.c): `mkindex` builds the packed (FM) index
+ *                                   THROUGH the Sfxiterator (src/match/eis-suffixerator-interface.c:254,400), the second
+ *                                   in-tree caller of the interface the drop-in replaces
  *
  * It is compiled by oracle/Makefile against the reference sources where they lie; nothing of the
  * reference is copied into this repository. Only tests/, __graft_entry__.smoke() and bench.py's
@@ -17,6 +20,7 @@
 #include "core/tool_api.h"
 #include "match/sfx-run.h"
 #include "tools/gt_sfxmap.h"
+#include "tools/gt_packedindex.h"
 
 int main(int argc, const char **argv)
 {
@@ -24,7 +28,7 @@ int main(int argc, const char **argv)
   int had_err = 0;
 
   if (argc < 2) {
-    fprintf(stderr, "usage: %s suffixerator|sfxmap [options]\n", argv[0]);
+    fprintf(stderr, "usage: %s suffixerator|sfxmap|packedindex [options]\n", argv[0]);
     return 2;
   }
   gt_lib_init();
@@ -34,6 +38,10 @@ int main(int argc, const char **argv)
     had_err = gt_parseargsandcallsuffixerator(true, argc - 1, argv + 1, err);
   } else if (strcmp(argv[1], "sfxmap") == 0) {
     GtTool *tool = gt_sfxmap();
+    had_err = gt_tool_run(tool, argc - 1, argv + 1, err);
+    gt_tool_delete(tool);
+  } else if (strcmp(argv[1], "packedindex") == 0) {
+    GtTool *tool = gt_packedindex();
     had_err = gt_tool_run(tool, argc - 1, argv + 1, err);
     gt_tool_delete(tool);
   } else {

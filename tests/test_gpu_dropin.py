@@ -104,3 +104,20 @@ def test_dropin_reports_device_errors_through_gterror(tmp_path):
     p = subprocess.run([GT_B200, "suffixerator", "-dna", "-suf", "-indexname", "x", "-db", fasta], cwd=str(tmp_path),
                        capture_output=True, text=True, env=env)
     assert p.returncode != 0 and "device 99 out of range" in p.stderr
+
+
+@pytest.mark.parametrize("extra", [[], ["-parts", "3"]])
+def test_packedindex_builds_through_the_dropin(extra, tmp_path):
+    """The second in-tree caller of the Sfxiterator API: `gt packedindex mkindex` builds the packed (FM) index by
+    iterating over the suffix array part by part (src/match/eis-suffixerator-interface.c:254,400).  With the drop-in
+    behind it the block-compressed index (.bdx) and the project file must come out byte-identical."""
+    enc = synth.multi_dna_with_nruns(400_000, nseq=5, seed=131)
+    fasta = str(tmp_path / "in.fna")
+    encseq.write_fasta(fasta, encseq.decode_to_fasta_bytes(enc, "dna"))
+    args = ["packedindex", "mkindex", "-dna", "-tis", "-db", fasta] + extra
+    _run(GT_REF, args + ["-indexname", "ref"], str(tmp_path))
+    _run(GT_B200, args + ["-indexname", "b200"], str(tmp_path))
+    for ext in ("bdx", "prj", "esq"):
+        a = open(tmp_path / f"ref.{ext}", "rb").read()
+        b = open(tmp_path / f"b200.{ext}", "rb").read()
+        assert a == b, f"packedindex .{ext} differs between the reference and the B200 drop-in"
