@@ -88,8 +88,41 @@ def traffic(path, workload, out="profiles/ncu_traffic.json"):
     print(json.dumps(db[workload], indent=1))
 
 
+def source(path, kernel_regex, top=30):
+    """Instructions executed and stall samples per CUDA source line of one kernel (needs -lineinfo, --import-source on)."""
+    out = subprocess.run(["ncu", "-i", path, "--page", "source", "--csv", "--print-source", "cuda,sass", "-k",
+                          "regex:" + kernel_regex], capture_output=True, text=True).stdout
+    cur, hdr = None, None
+    agg, samp, src = collections.Counter(), collections.Counter(), {}
+    for r in csv.reader(out.splitlines()):
+        if not r:
+            continue
+        if r[0] == "File Path":
+            cur = r[1].split("/")[-1]
+            continue
+        if r[0] == "Line No":
+            hdr = r
+            continue
+        if r[0] == "Function Name" or hdr is None:
+            continue
+        try:
+            ln = int(r[0])
+        except ValueError:
+            continue
+        if r[2] in ("-", ""):
+            agg[(cur, ln)] += int(r[hdr.index("Instructions Executed")] or 0)
+            samp[(cur, ln)] += int(r[hdr.index("# Samples")] or 0)
+            src[(cur, ln)] = r[1].strip()[:100]
+    tot, ts = sum(agg.values()), sum(samp.values())
+    print(f"== {kernel_regex}: {tot} warp instructions, {ts} stall samples")
+    for k, v in agg.most_common(int(top)):
+        print(f"{v / max(tot, 1) * 100:5.1f}% inst {samp[k] / max(ts, 1) * 100:5.1f}% samples  {k[0]}:{k[1]}  {src[k]}")
+
+
 if __name__ == "__main__":
-    if sys.argv[1] == "traffic":
+    if sys.argv[1] == "source":
+        source(sys.argv[2], sys.argv[3], *(sys.argv[4:5]))
+    elif sys.argv[1] == "traffic":
         traffic(sys.argv[2], sys.argv[3])
     else:
         {"launches": launches, "raw": raw}[sys.argv[1]](sys.argv[2])

@@ -70,3 +70,25 @@ def test_noalloc_rejects_tables_beyond_its_fixed_scratch():
     assert rc == -1 and "exceed" in msg and "67108864" in msg
     rc, msg = _noalloc(t, t, 0, 0)
     assert rc == -1
+
+
+def test_noalloc_on_a_second_gpu():
+    """The fixed scratch array exists once per GPU and its address is resolved per device: the same call on device 1
+    (after device 0 has been used) must give device 1's table, not touch device 0's array."""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs a second GPU")
+    enc = synth.multi_dna_with_nruns(1_000_000, nseq=4, seed=73)
+    want = _table_from_regular_path(enc, 8)
+    for d in (0, 1, 0):
+        dev = torch.device("cuda", d)
+        torch.cuda.set_device(dev)
+        cin = torch.from_numpy(np.diff(want.astype(np.int64)).astype(np.int32)).to(dev)
+        cout = torch.full((want.shape[0],), -1, dtype=torch.int32, device=dev)
+        torch.cuda.synchronize(dev)
+        rc, msg = _noalloc(cin, cout, 4 ** 8, torch.cuda.current_stream(dev).cuda_stream)
+        assert rc == 0, msg
+        torch.cuda.synchronize(dev)
+        assert np.array_equal(cout.cpu().numpy().view(np.uint32), want), f"device {d}"
+    torch.cuda.set_device(0)
