@@ -477,7 +477,11 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_s = float(t.item())
     h2d = (words_h.numel() * words_h.element_size() + ranges_h.numel() * 8) if rank == 0 else 0
-    d2h = suf_h.numel() * 8 + width + (numcodes + 1) * 4 + csc_h.numel() * 4 + int(it.countinfo.numofdistpfxidx) * 4
+    # the library ships 32-bit positions and widens them on the host when one GPU feeds one PCIe link (narrow transfer)
+    narrow = os.environ.get("GTB200_NARROW", "1") != "0" and width >= (4 << 20)
+    suf_bus_bytes = 4 if narrow else 8
+    d2h = width * suf_bus_bytes + (suf_h.numel() - width) * 8 + width + (numcodes + 1) * 4 + csc_h.numel() * 4 \
+        + int(it.countinfo.numofdistpfxidx) * 4
     tb = torch.tensor([h2d, d2h], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(tb)
@@ -545,7 +549,9 @@ def main():
                                               "transform): kernel class prep; e2e includes it"},
             "e2e": None if args.skip_e2e else
                    {"value": (n + 1) / e2e_s, "unit": "suffixes/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "steps": e2e_steps},
+                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_s * 1e3, "steps": e2e_steps,
+                    "suf_entry_bytes_on_the_bus": suf_bus_bytes,
+                    "host_result": "GtUword[suffixes] .suf entries + uint8 lcp + .bck tables in host memory"},
             "gpu_launches": int(sum(v[1] for v in kern.values())),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -614,6 +614,39 @@ __global__ void __launch_bounds__(256) k_kmers(Text<BITS> T, CodeParams cp, uint
   }
 }
 
+// Counting for large DNA texts: k_kmers spends ~37 instructions per position on 64-bit variable shifts, and a table
+// that is filled in code slices pays them once per slice (3.1 Gbp: 4 passes, issue-active 72 %: instruction-, not
+// atomic-bound).  Here a thread owns 16 positions that start on a 32-bit boundary of the packed text, so with the
+// loop unrolled every code is one funnel shift by a constant plus a shift; ~6 instructions per position.
+// sliced: only codes in [lo, hi] are counted in this pass.
+__global__ void __launch_bounds__(256) k_count_dna(Text<2> T, unsigned pl, uint64_t pbase, uint64_t pend,
+                                                   uint32_t *__restrict__ table, uint32_t lo, uint32_t hi) {
+  const uint64_t p0 = pbase + ((uint64_t)blockIdx.x * 256 + threadIdx.x) * 16;
+  if (p0 >= pend) return;
+  const uint64_t t = p0 >> 5;
+  const uint64_t w0 = __ldg(T.w + t), w1 = __ldg(T.w + t + 1);
+  const uint32_t u0 = (p0 & 16) ? (uint32_t)w0 : (uint32_t)(w0 >> 32);
+  const uint32_t u1 = (p0 & 16) ? (uint32_t)(w1 >> 32) : (uint32_t)w0;
+  const uint64_t mw = T.maskwin(p0);
+  const unsigned cs = 32u - 2u * pl;                  // pl <= 15
+  const uint32_t span = hi - lo;
+  const uint32_t plmask = (1u << pl) - 1u;
+  const uint32_t m32 = (uint32_t)mw;                  // positions p0 .. p0+31: covers i + pl - 1 <= 29
+  if ((m32 & ((1u << (15 + pl)) - 1u)) == 0u) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const uint32_t code = (i ? __funnelshift_l(u1, u0, 2 * i) : u0) >> cs;
+      if (code - lo <= span) atomicAdd(&table[code], 1u);
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const uint32_t code = (i ? __funnelshift_l(u1, u0, 2 * i) : u0) >> cs;
+      if (((m32 >> i) & plmask) == 0u && code - lo <= span) atomicAdd(&table[code], 1u);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Two-level insertion for parts whose suffix array does not fit L2.  A direct scatter writes 4
 // bytes to a random place in a multi-GB array: every store evicts a partially filled sector.
@@ -2345,14 +2378,28 @@ static int count_impl(gtb200_ctx *c, bool need_host_values, uint64_t pos_lo, uin
     // that the RED.ADDs always hit L2-resident lines; the text scan itself is cheap (n/4 bytes).
     uint64_t slice = 1ull << 24;
     if (const char *es = getenv("GTB200_COUNT_SLICE_LOG2")) slice = 1ull << atoi(es);     // testing knob
+    // large DNA texts: the funnel-shift scanner (the per-position cost is what bounds the sliced count)
+    int fastmode = 1;                                  // GTB200_FASTCOUNT: 0 never, 2 always (testing knob)
+    if (const char *ef = getenv("GTB200_FASTCOUNT")) fastmode = atoi(ef);
+    const bool fast = BITS == 2 && c->cp.pow2 && c->cp.pl <= 15 && fastmode != 0 &&
+                      (fastmode == 2 || (pos_hi - pos_lo) >= (32ull << 20));
+    const Text<2> T2 = text_of<2>(c);
     if (c->numcodes * 4 <= (96ull << 20)) {
       ProfScope ps(c, KC_COUNT);
-      k_kmers<BITS, 0><<<grid_for((pos_hi - pos_lo + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, pos_lo, pos_hi, c->d_lb, nullptr, 0, 0, 0);
+      if (fast)
+        k_count_dna<<<grid_for((pos_hi - pos_lo + 15) / 16, 256), 256, 0, c->stream>>>(T2, c->cp.pl, pos_lo, pos_hi, c->d_lb, 0u,
+                                                                                     (uint32_t)(c->numcodes - 1));
+      else
+        k_kmers<BITS, 0><<<grid_for((pos_hi - pos_lo + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, pos_lo, pos_hi, c->d_lb, nullptr, 0, 0, 0);
     } else {
       for (uint64_t lo = 0; lo < c->numcodes; lo += slice) {
         const uint64_t hi = lo + slice - 1 < c->numcodes - 1 ? lo + slice - 1 : c->numcodes - 1;
         ProfScope ps(c, KC_COUNT);
-        k_kmers<BITS, 2><<<grid_for((pos_hi - pos_lo + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, pos_lo, pos_hi, c->d_lb, nullptr, lo, hi, 0);
+        if (fast)
+          k_count_dna<<<grid_for((pos_hi - pos_lo + 15) / 16, 256), 256, 0, c->stream>>>(T2, c->cp.pl, pos_lo, pos_hi, c->d_lb,
+                                                                                       (uint32_t)lo, (uint32_t)hi);
+        else
+          k_kmers<BITS, 2><<<grid_for((pos_hi - pos_lo + KM_PPT - 1) / KM_PPT, 256), 256, 0, c->stream>>>(T, c->cp, pos_lo, pos_hi, c->d_lb, nullptr, lo, hi, 0);
       }
     }
   }

@@ -373,6 +373,17 @@ def test_sharded_count_equals_replicated_count():
         it.delete()
 
 
+@pytest.mark.parametrize("case", ["dna_nruns_300k", "dna_nruns_300k_pl3", "dna_tiny_special_ends", "dna_all_special", "dna_single", "dna_polyT"])
+def test_funnel_shift_counting_kernel(case, monkeypatch):
+    """k_count_dna (16 positions per thread, codes by funnel shifts; what genomes of >= 32 M positions use) forced on
+    small inputs: windows with specials, sequence ends inside a thread's positions, sharded counting (parts)."""
+    monkeypatch.setenv("GTB200_FASTCOUNT", "2")
+    enc, alphabet, pl = CASES[case]()
+    want = oracle.build(enc, 4, pl)
+    for parts in (1, 3):
+        _compare(sfx.suffixerator(enc, "dna", parts=parts, prefixlength=want["prefixlength"]), want, f"fastcount/{case}/{parts}")
+
+
 @pytest.mark.parametrize("narrow", ["1", "0"])
 def test_narrow_transfer_matches(narrow, monkeypatch):
     """A GtUword suftab of a large part crosses PCIe as 32-bit positions and is widened by host threads
