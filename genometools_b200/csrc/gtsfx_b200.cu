@@ -1360,7 +1360,8 @@ template <int BITS>
 __global__ void __launch_bounds__(256) k_sort_medium(Text<BITS> T, PartOut out, const uint32_t *__restrict__ lb,
                                                      const uint32_t *__restrict__ cursor,
                                                      const uint32_t *__restrict__ medlist, uint64_t mincode,
-                                                     unsigned pl, uint32_t *__restrict__ fbbits, uint64_t tieoff) {
+                                                     unsigned pl, uint32_t *__restrict__ fbbits, uint64_t tieoff,
+                                                     const uint64_t *__restrict__ keys_in) {
   extern __shared__ __align__(16) unsigned char sm_raw[];
   uint64_t *skey = (uint64_t *)sm_raw;                 // full keys by slot
   uint32_t *spos = (uint32_t *)(skey + MED_MAX);       // positions by slot
@@ -1378,7 +1379,8 @@ __global__ void __launch_bounds__(256) k_sort_medium(Text<BITS> T, PartOut out, 
     for (uint32_t i = threadIdx.x; i < P; i += 256) {
       if (i < cnt) {
         const uint32_t p = out.sa[start + i];
-        const uint64_t key = make_key<BITS>(T, (uint64_t)p + pl);
+        // keys_in: the keyed tile path left the key beside the position (no text access)
+        const uint64_t key = keys_in ? __ldcs(keys_in + start + i) : make_key<BITS>(T, (uint64_t)p + pl);
         skey[i] = key;
         spos[i] = p;
         s32[i] = (key_prefix20<BITS>(key) << 12) | i;
@@ -2835,7 +2837,8 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
   }
   // records carry min(real length, 63) in their top 6 bits when the code leaves room for it
   const int recL = (c->numcodes <= (1ull << 26) && c->cp.pl + Text<BITS>::W <= 63) ? 1 : 0;
-  const bool keyed = tile && keyed_ok && BITS == 2 && recL;
+  const bool keyed = tile && keyed_ok && recL;
+  uint64_t *medkeys = nullptr;               // byte text, keyed: keys of the buckets the tile sorter only inserts
   if (tile) {
     c->diag[0] = 1; c->diag[1] = nb1 ? 2 : 1; c->diag[2] = keyed ? 1 : 0;
     const uint64_t binwords = (uint64_t)nbinsF + 3 * SP_MAXBINS + 64;
@@ -2867,11 +2870,14 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
       // ---- keyed records (keyed.cuh): 16 bytes per suffix, the key travels with the record ----
       CK(cudaFuncSetAttribute(k_keyed_partition_dense, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
       CK(cudaFuncSetAttribute(k_keyed_partition_sparse, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
+      CK(cudaFuncSetAttribute(k_keyed_partition_bytes, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
       CK(cudaFuncSetAttribute(k_keyed_partition_rec, cudaFuncAttributeMaxDynamicSharedMemorySize, KP_SMEM));
       const unsigned textblocks = grid_for(c->n, (uint64_t)KP_CHUNK * reps);
       const int whole = (lo == 0 && hi == c->numcodes - 1) ? 1 : 0;
       ulonglong2 *recX = (ulonglong2 *)c->d_suf64, *recY = (ulonglong2 *)c->d_recB;
       const Text<2> T2 = text_of<2>(c);
+      const Text<8> T8 = text_of<8>(c);
+      if (BITS == 8) medkeys = c->d_suf64 + (c->part_width + 1);      // second half of the 16-byte-per-suffix buffer
       {
         ProfScope ps(c, KC_SCATTER, nb1 ? 5 : 2);
         k_bins_init<<<grid_for(nbinsF, 256), 256, 0, c->stream>>>(c->d_lb, lo, shiftF, nbinsF, out.partoffset, gcurF,
@@ -2881,7 +2887,9 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
         const uint32_t nb = nb1 ? nb1 : nbinsF;
         ulonglong2 *dst = nb1 ? recX : recY;
         if (nb1) k_bins_init<<<grid_for(nb1, 256), 256, 0, c->stream>>>(c->d_lb, lo, shift1, nb1, out.partoffset, gcur1, start1);
-        if (reps > 1)
+        if (BITS == 8)
+          k_keyed_partition_bytes<<<textblocks, 256, KP_SMEM, c->stream>>>(T8, c->cp, c->n, lo, hi, sh, nb, reps, gc, dst);
+        else if (reps > 1)
           k_keyed_partition_sparse<<<textblocks, 256, KP_SMEM, c->stream>>>(T2, c->cp.pl, c->n, lo, hi, sh, nb, reps, gc, dst);
         else
           k_keyed_partition_dense<<<textblocks, 256, KP_SMEM, c->stream>>>(T2, c->cp.pl, c->n, lo, hi, whole, sh, nb, gc, dst);
@@ -2895,11 +2903,11 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
       {
         ProfScope ps(c, KC_SORT);
         const unsigned tb = nbinsF < 148u * 2 ? nbinsF : 148u * 2;
-        CK(cudaFuncSetAttribute(k_tile_sort_keyed, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM));
+        CK(cudaFuncSetAttribute(k_tile_sort_keyed<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM));
         PartOut tfin = out;
         if (c->fused_widen) tfin.sa64 = c->d_suf64;          // the level-1 records in it are dead by now
-        k_tile_sort_keyed<<<tb, TS_THREADS, TS_SMEM, c->stream>>>(T2, tfin, c->d_lb, c->d_cursor, recY, gcurF, lo, hi, shiftF,
-                                                                  nbinsF, c->cp.pl, fbb, fbwords);
+        k_tile_sort_keyed<BITS><<<tb, TS_THREADS, TS_SMEM, c->stream>>>(T, tfin, c->d_lb, c->d_cursor, recY, gcurF, lo, hi,
+                                                                        shiftF, nbinsF, c->cp.pl, fbb, fbwords, medkeys);
       }
       CK(cudaGetLastError());
     } else {
@@ -3006,7 +3014,7 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
     const size_t smem = MED_SMEM;
     CK(cudaFuncSetAttribute(k_sort_medium<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_sort_medium<BITS><<<148 * 8, 256, smem, c->stream>>>(T, fin, c->d_lb, c->d_cursor, c->d_medlist, lo, c->cp.pl,
-                                                          fbb, fbwords);
+                                                          fbb, fbwords, medkeys);
   }
   if (padded_beside && side_join(c)) return -1;
   {
@@ -3196,7 +3204,8 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
   if (width == 0) return 0;
   // keyed records once the packed text (and its bitmap) no longer fit L2 beside the streams passing through:
   // the tile sorter's one random text access per suffix is then a 64-byte DRAM access
-  const bool keyed_ok = BITS == 2 && c->cp.pow2 && c->cp.pl <= 15 && c->keyed_mode != 0 &&
+  const bool keyed_ok = ((BITS == 2 && c->cp.pow2 && c->cp.pl <= 15) || (BITS == 8 && c->cp.pl <= 8)) &&
+                        c->numcodes <= (1ull << 26) && c->keyed_mode != 0 &&
                         (c->keyed_mode == 2 || (c->ntextwords + c->nmaskwords) * 8 > (96ull << 20));
   memset(c->diag, 0, sizeof c->diag);
   if (ensure_part_buffers(c, width, ncodes, keyed_ok)) return -1;

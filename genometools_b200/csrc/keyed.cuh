@@ -471,13 +471,17 @@ __global__ void __launch_bounds__(256) k_keyed_chunk_table(const uint32_t *__res
   if (threadIdx.x == 0) blk_first[nparents] = carry;
 }
 
-// tiles.cuh's k_tile_sort for keyed records: insertion only moves (position, key) into the bucket's slots
-__global__ void __launch_bounds__(TS_THREADS, 2) k_tile_sort_keyed(Text<2> T, PartOut out, const uint32_t *__restrict__ lb,
+// tiles.cuh's k_tile_sort for keyed records: insertion only moves (position, key) into the bucket's slots.
+// keys_out (byte text): buckets the tile does not sort itself (more than 128 suffixes: the rule on protein) leave
+// their keys beside their positions, keys_out[r] for out.sa[r], for k_sort_medium.
+template <int BITS>
+__global__ void __launch_bounds__(TS_THREADS, 2) k_tile_sort_keyed(Text<BITS> T, PartOut out, const uint32_t *__restrict__ lb,
                                                                    uint32_t *__restrict__ cursor,
                                                                    const ulonglong2 *__restrict__ rec,
                                                                    const uint32_t *__restrict__ gcursor, uint64_t mincode,
                                                                    uint64_t maxcode, int shift, uint32_t nbins, unsigned pl,
-                                                                   uint32_t *__restrict__ fbbits, uint64_t tieoff) {
+                                                                   uint32_t *__restrict__ fbbits, uint64_t tieoff,
+                                                                   uint64_t *__restrict__ keys_out) {
   extern __shared__ __align__(16) unsigned char ts_raw[];
   uint64_t *s_key = (uint64_t *)ts_raw;
   uint32_t *s_pos = (uint32_t *)(s_key + TILE_CAP);
@@ -505,9 +509,11 @@ __global__ void __launch_bounds__(TS_THREADS, 2) k_tile_sort_keyed(Text<2> T, Pa
     if (slots > TILE_CAP) {
       // too many suffixes for shared memory: plain insertion, the global kernels sort these buckets
       for (uint32_t i = threadIdx.x; i < cnt; i += TS_THREADS) {
-        const uint64_t a = __ldcs(&rec[rs + i].x);
+        const ulonglong2 a2 = __ldcs(rec + rs + i);
+        const uint64_t a = a2.x;
         const uint32_t slot = atomicAdd(&s_cur[(uint32_t)(((a >> 32) & REC_CODE_MASK) - c0)], 1u);
         out.sa[rs + slot] = (uint32_t)a;
+        if (keys_out) keys_out[rs + slot] = a2.y;
       }
       __syncthreads();
       for (uint32_t i = threadIdx.x; i < ncf; i += TS_THREADS) cursor[c0 + i] = base + s_cur[i];
@@ -543,12 +549,15 @@ __global__ void __launch_bounds__(TS_THREADS, 2) k_tile_sort_keyed(Text<2> T, Pa
         const uint32_t *src = s_pos + ls;
         const uint64_t *keys = s_key + ls;
         bool clean = true;                              // sorted and free of ties
-        if (cf <= 32) clean = warp_sort_any<2, 1>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
-        else if (cf <= 64) clean = warp_sort_any<2, 2>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
-        else if (cf <= 96) clean = warp_sort_any<2, 3>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
-        else if (cf <= SORT_MAXBUCKET) clean = warp_sort_any<2, 4>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        if (cf <= 32) clean = warp_sort_any<BITS, 1>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else if (cf <= 64) clean = warp_sort_any<BITS, 2>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else if (cf <= 96) clean = warp_sort_any<BITS, 3>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else if (cf <= SORT_MAXBUCKET) clean = warp_sort_any<BITS, 4>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
         else {                                          // too large for a warp: leave it to the global sorters
-          for (uint32_t i = lane; i < cf; i += 32) out.sa[start + i] = src[i];
+          for (uint32_t i = lane; i < cf; i += 32) {
+            out.sa[start + i] = src[i];
+            if (keys_out) keys_out[start + i] = keys[i];
+          }
           done = false;
           if (lane == 0) atomicAdd(&out.stats->tile_leftover, 1u);
         }
@@ -570,5 +579,147 @@ __global__ void __launch_bounds__(TS_THREADS, 2) k_tile_sort_keyed(Text<2> T, Pa
   if (lane == 0) {
     if (sum) atomicAdd(&out.stats->lcpsum, sum);
     if (mx) atomicMax(&out.stats->maxdepth, mx);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Keyed records for byte text (sigma > 4: protein).  The block sorter k_sort_medium - where 98 % of a protein
+// index's suffixes end up - fetched its keys from the 1 GB text at random: 125 GB of DRAM reads for 25 GB
+// algorithmic at 1 G residues (profiles/r2_ncu_full_protein.txt).  Here too the level-1 partition has the 7 residues
+// after the prefix in registers, so the key travels with the record; the tile sorter hands the keys of the buckets it
+// only inserts to k_sort_medium through a key array beside the suffix array.
+//   thread = 16 positions = 2 text words (+2 for the windows); codes are base-sigma numbers: Horner for the first
+//   position, then one multiply-add per position (the identity holds modulo 2^32 whatever the digits are, so a
+//   special only spoils the codes whose window contains it, and those are masked out).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t kb_special_bits(uint64_t w) {      // bit j = byte j (big-endian order) is >= 0xfe
+  const uint64_t z = ((~w) >> 1) & 0x7f7f7f7f7f7f7f7full;
+  const uint64_t real = (z + 0x7f7f7f7f7f7f7f7full) & 0x8080808080808080ull;
+  const uint64_t t = (real ^ 0x8080808080808080ull) >> 7;
+  return (uint32_t)((t * 0x8040201008040201ull) >> 56);
+}
+
+struct KbWin {
+  uint64_t w0, w1, w2, w3;
+  uint32_t sp;                 // special flags of the 32 bytes from p0 on
+};
+
+__device__ __forceinline__ KbWin kb_load(const Text<8> &T, uint64_t p0) {
+  KbWin k;
+  const uint64_t t = p0 >> 3;
+  k.w0 = __ldg(T.w + t);
+  k.w1 = __ldg(T.w + t + 1);
+  k.w2 = __ldg(T.w + t + 2);
+  k.w3 = __ldg(T.w + t + 3);
+  k.sp = kb_special_bits(k.w0) | (kb_special_bits(k.w1) << 8) | (kb_special_bits(k.w2) << 16) | (kb_special_bits(k.w3) << 24);
+  return k;
+}
+
+// byte j (0..31, compile-time constant after unrolling) of the window
+__device__ __forceinline__ uint32_t kb_byte(const KbWin &k, int j) {
+  const uint64_t w = j < 8 ? k.w0 : j < 16 ? k.w1 : j < 24 ? k.w2 : k.w3;
+  return (uint32_t)(w >> (56 - 8 * (j & 7))) & 0xffu;
+}
+
+// codes of the 16 positions (garbage where the window holds a special: masked by the caller)
+__device__ __forceinline__ void kb_codes(const KbWin &k, unsigned pl, uint32_t sigma, uint32_t top /* sigma^(pl-1) */,
+                                         uint64_t v0, uint64_t v1, uint32_t (&code)[KP_PPT]) {
+  uint32_t c = 0;
+#pragma unroll
+  for (int t = 0; t < 8; ++t)
+    if ((unsigned)t < pl) c = c * sigma + kb_byte(k, t);
+  code[0] = c;
+#pragma unroll
+  for (int i = 1; i < KP_PPT; ++i) {
+    // leaves: digit i-1; enters: digit i-1+pl = byte i-1 of the stream advanced by pl bytes (v0 v1)
+    const uint32_t in = (uint32_t)((i - 1 < 8 ? v0 : v1) >> (56 - 8 * ((i - 1) & 7))) & 0xffu;
+    c = (c - kb_byte(k, i - 1) * top) * sigma + in;
+    code[i] = c;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_keyed_partition_bytes(Text<8> T, CodeParams cp, uint64_t n, uint64_t mincode,
+                                                                uint64_t maxcode, int shift, uint32_t nbins, int reps,
+                                                                uint32_t *__restrict__ gcursor,
+                                                                ulonglong2 *__restrict__ rec_out) {
+  extern __shared__ __align__(16) unsigned char kp_raw[];
+  ulonglong2 *stage = (ulonglong2 *)kp_raw;
+  uint32_t *h = (uint32_t *)(stage + KP_CHUNK);
+  uint32_t *lstart = h + SP_MAXBINS;                     // local bin starts, then the staging cursors
+  uint32_t *misc = lstart + SP_MAXBINS;
+  for (uint32_t i = threadIdx.x; i < nbins; i += 256) h[i] = 0;
+  __syncthreads();
+  const unsigned pl = cp.pl;                              // <= 8
+  const uint32_t sigma = cp.sigma, top = (uint32_t)cp.pw[pl - 1];
+  const uint32_t min32 = (uint32_t)mincode, span = (uint32_t)(maxcode - mincode), plmask = (1u << pl) - 1u;
+  const uint64_t pbase = (uint64_t)blockIdx.x * reps * KP_CHUNK + (uint64_t)threadIdx.x * KP_PPT;
+  uint64_t sb0 = 0, sb1 = 0;                             // 16 selection bits per repetition
+#pragma unroll 1
+  for (int rep = 0; rep < reps; ++rep) {
+    const uint64_t p0 = pbase + (uint64_t)rep * KP_CHUNK;
+    if (p0 >= n) break;
+    const KbWin k = kb_load(T, p0);
+    const unsigned sh = 8u * pl;
+    const uint64_t v0 = pl == 8 ? k.w1 : (k.w0 << sh) | (k.w1 >> (64 - sh));
+    const uint64_t v1 = pl == 8 ? k.w2 : (k.w1 << sh) | (k.w2 >> (64 - sh));
+    uint32_t code[KP_PPT];
+    kb_codes(k, pl, sigma, top, v0, v1, code);
+    uint32_t sel = 0;
+#pragma unroll
+    for (int i = 0; i < KP_PPT; ++i) {
+      if (((k.sp >> i) & plmask) == 0u && code[i] - min32 <= span) {
+        sel |= 1u << i;
+        atomicAdd(&h[(code[i] - min32) >> shift], 1u);
+      }
+    }
+    if (rep < 4) sb0 |= (uint64_t)sel << (16 * rep); else sb1 |= (uint64_t)sel << (16 * (rep - 4));
+  }
+  __syncthreads();
+  const uint32_t total = kp_scan_bins<256>(h, lstart, nbins, misc);
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < nbins; i += 256) {
+    const uint32_t cnt = h[i];
+    h[i] = cnt ? atomicAdd(&gcursor[i], cnt) - lstart[i] : 0u;      // global index = h[bin] + local index
+  }
+  __syncthreads();
+  const bool staged = total <= KP_CHUNK;
+#pragma unroll 1
+  for (int rep = 0; rep < reps; ++rep) {
+    const uint32_t sel = (uint32_t)((rep < 4 ? sb0 >> (16 * rep) : sb1 >> (16 * (rep - 4))) & 0xffffull);
+    if (!sel) continue;
+    const uint64_t p0 = pbase + (uint64_t)rep * KP_CHUNK;
+    const KbWin k = kb_load(T, p0);
+    const unsigned sh = 8u * pl;
+    const uint64_t v0 = pl == 8 ? k.w1 : (k.w0 << sh) | (k.w1 >> (64 - sh));
+    const uint64_t v1 = pl == 8 ? k.w2 : (k.w1 << sh) | (k.w2 >> (64 - sh));
+    const uint64_t v2 = pl == 8 ? k.w3 : (k.w2 << sh) | (k.w3 >> (64 - sh));
+    uint32_t code[KP_PPT];
+    kb_codes(k, pl, sigma, top, v0, v1, code);
+#pragma unroll
+    for (int i = 0; i < KP_PPT; ++i) {
+      if ((sel >> i) & 1u) {
+        // the 8 bytes at position p0+i+pl; 7 of them are key symbols (make_key<8>, common.cuh)
+        const uint64_t hi = i < 8 ? v0 : v1, lo = i < 8 ? v1 : v2;
+        const uint64_t kw = (i & 7) ? (hi << (8 * (i & 7))) | (lo >> (64 - 8 * (i & 7))) : hi;
+        const uint32_t a = (k.sp >> (i + pl)) & 0x7fu;
+        const unsigned avail = a ? (unsigned)(__ffs(a) - 1) : 7u;
+        uint64_t x = kw >> 8;
+        if (avail < 7u) x |= (~0ull) >> (64 - (7u - avail) * 8u);
+        ulonglong2 rec;
+        rec.x = ((uint64_t)((63u << 26) | code[i]) << 32) | (uint64_t)(uint32_t)(p0 + i);
+        rec.y = (x << 8) | (uint64_t)(7u - avail);
+        const uint32_t bin = (code[i] - min32) >> shift;
+        const uint32_t r = atomicAdd(&lstart[bin], 1u);
+        if (staged) stage[r] = rec;
+        else rec_out[h[bin] + r] = rec;
+      }
+    }
+  }
+  if (!staged) return;
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < total; i += 256) {
+    const ulonglong2 r = stage[i];
+    const uint32_t bin = (((uint32_t)(r.x >> 32) & (uint32_t)REC_CODE_MASK) - min32) >> shift;
+    __stcs(rec_out + h[bin] + i, r);
   }
 }

@@ -163,6 +163,24 @@ def test_tile_path_forced_protein(levels, monkeypatch):
 
 
 @pytest.mark.parametrize("levels", ["1", "2"])
+def test_tile_path_keyed_records_protein(levels, monkeypatch):
+    """Keyed records on byte text: base-20 codes rolled along 16 positions per thread, 7-residue keys cut by
+    separators/wildcards, and the keys of buckets the tile only inserts handed to the block sorter beside the positions."""
+    monkeypatch.setenv("GTB200_TILE", "2")
+    monkeypatch.setenv("GTB200_KEYED", "2")
+    monkeypatch.setenv("GTB200_TILE_LEVELS", levels)
+    for nseq, pl, parts in ((1500, 3, 1), (3000, 2, 2), (400, 4, 1), (900, 2, 1), (500, 2, 3), (2500, 5, 1)):
+        prot = synth.random_protein(nseq, seed=160 + nseq % 7)
+        want = oracle.build(prot, 20, pl)
+        got = sfx.suffixerator(prot, "protein", prefixlength=pl, parts=parts)
+        _compare(got, want, f"keyed/protein/{nseq}/pl{pl}/levels{levels}")
+    g = load_golden_by_name("protein_filelist_transprot11")       # sigma = 11
+    z = np.load(__import__("os").path.join(__import__("os").path.dirname(__file__), "golden", "protein_filelist_transprot11.npz"))
+    want = oracle.build(z["enc"], 11, 3)
+    _compare(sfx.suffixerator(z["enc"], "smap", prefixlength=3, sigma=11), want, f"keyed/transprot11/levels{levels}")
+
+
+@pytest.mark.parametrize("levels", ["1", "2"])
 def test_tile_path_medium_buckets_dna(levels, monkeypatch):
     """Buckets of 129..1024 suffixes inside a tile are sorted by one warp with shared-memory merges
     (warp_sort_medium): all chunk counts, equal-prefix runs (fix-up), runs too long for the fix-up (handed to the
