@@ -127,6 +127,7 @@ struct gtb200_ctx {
   uint64_t *d_recB;          // second record buffer of the tile path (two partition levels); 16-byte records when keyed
   int keyed_mode;            // 0 never, 1 automatic (text larger than L2's share), 2 always (GTB200_KEYED, testing knob)
   uint64_t cap_suf64_bytes;
+  int subsort;               // byte text, keyed tiles: split buckets by the first key symbol (GTB200_SUBSORT=0: testing knob)
   uint64_t diag[8];          // last part: [0] tile path, [1] partition levels, [2] keyed records, [3] suffixes in medium buckets
   uint32_t *d_isa;           // rank array of the prefix-doubling refinement (n+1 entries)
   uint64_t cap_isa;
@@ -2288,6 +2289,8 @@ static gtb200_ctx *ctx_create(int device, unsigned numofchars, uint64_t totallen
   c->tile_mode = 1;
   if (const char *e4 = getenv("GTB200_TILE")) c->tile_mode = atoi(e4);
   c->keyed_mode = 1;
+  c->subsort = 1;
+  if (const char *e14 = getenv("GTB200_SUBSORT")) c->subsort = atoi(e14);
   if (const char *e10 = getenv("GTB200_KEYED")) c->keyed_mode = atoi(e10);
   if (const char *e5 = getenv("GTB200_TILE_LEVELS")) c->tile_levels = atoi(e5);
   c->twolevel_bytes = 48ull << 20;
@@ -2906,6 +2909,12 @@ static int enqueue_range(gtb200_ctx *c, const Text<BITS> &T, const PartOut &out,
         CK(cudaFuncSetAttribute(k_tile_sort_keyed<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM));
         PartOut tfin = out;
         if (c->fused_widen) tfin.sa64 = c->d_suf64;          // the level-1 records in it are dead by now
+        if (BITS == 8 && c->subsort && (((uint64_t)c->cp.sigma + 1) << shiftF) <= TSUB_MAX) {
+          // byte text: buckets split once more by the first key symbol inside the tile, warp networks on the groups
+          CK(cudaFuncSetAttribute(k_tile_subsort, cudaFuncAttributeMaxDynamicSharedMemorySize, TSUB_SMEM));
+          k_tile_subsort<<<tb, TS_THREADS, TSUB_SMEM, c->stream>>>(T8, tfin, c->d_lb, c->d_cursor, recY, gcurF, lo, hi, shiftF,
+                                                                   nbinsF, c->cp.pl, c->cp.sigma, fbb, fbwords, medkeys);
+        } else
         k_tile_sort_keyed<BITS><<<tb, TS_THREADS, TS_SMEM, c->stream>>>(T, tfin, c->d_lb, c->d_cursor, recY, gcurF, lo, hi,
                                                                         shiftF, nbinsF, c->cp.pl, fbb, fbwords, medkeys);
       }

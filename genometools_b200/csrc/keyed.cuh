@@ -723,3 +723,186 @@ __global__ void __launch_bounds__(256) k_keyed_partition_bytes(Text<8> T, CodePa
     __stcs(rec_out + h[bin] + i, r);
   }
 }
+
+// ---------------------------------------------------------------------------------------------
+// Tile sorter for keyed records on byte text.  With sigma = 20 and pl = 5 a bucket holds ~300 suffixes - too many
+// for one warp network, and the block sorter that took them needs 22 warp instructions per suffix.  Inside the tile
+// every bucket is therefore split once more by the first key symbol (sigma + 1 sub-buckets: the last one collects
+// keys that start with a special), which brings the groups down to ~15 suffixes, and the warp networks sort those
+// from the keys in shared memory.  Neighbours in different sub-buckets differ in their first symbol after the
+// prefix, so the LCP at a sub-bucket border is exactly pl.
+//   P1 histogram over (bucket, first symbol) - P2 prefix per bucket - P3 scatter (second read of the records: L2) -
+//   P4 one warp per sub-bucket.  A bucket with a sub-bucket of more than 128 suffixes is left to the global sorters
+//   (positions and keys written out unsorted), like every bucket of a tile that does not fit shared memory.
+// ---------------------------------------------------------------------------------------------
+#define TSUB_MAX 4096                    // (bucket, symbol) counters per tile
+// dynamic shared memory: key[TILE_CAP] u64 | pos[TILE_CAP] | lb[TILE_MAXCODES+1] | sub[TSUB_MAX] | cur[TSUB_MAX] | big[TILE_MAXCODES] u8
+#define TSUB_SMEM (TILE_CAP * 12 + (TILE_MAXCODES + 1) * 4 + 2 * TSUB_MAX * 4 + TILE_MAXCODES + 12)
+
+__global__ void __launch_bounds__(TS_THREADS, 2) k_tile_subsort(Text<8> T, PartOut out, const uint32_t *__restrict__ lb,
+                                                                uint32_t *__restrict__ cursor,
+                                                                const ulonglong2 *__restrict__ rec,
+                                                                const uint32_t *__restrict__ gcursor, uint64_t mincode,
+                                                                uint64_t maxcode, int shift, uint32_t nbins, unsigned pl,
+                                                                uint32_t sigma, uint32_t *__restrict__ fbbits, uint64_t tieoff,
+                                                                uint64_t *__restrict__ keys_out) {
+  extern __shared__ __align__(16) unsigned char ts_raw[];
+  uint64_t *s_key = (uint64_t *)ts_raw;
+  uint32_t *s_pos = (uint32_t *)(s_key + TILE_CAP);
+  uint32_t *s_lb = s_pos + TILE_CAP;
+  uint32_t *s_sub = s_lb + TILE_MAXCODES + 1;           // start slot of every (bucket, symbol) group
+  uint32_t *s_cur = s_sub + TSUB_MAX;                   // counters, then cursors, then end slots
+  unsigned char *s_big = (unsigned char *)(s_cur + TSUB_MAX);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const uint32_t S1 = sigma + 1;
+  unsigned long long sum = 0;
+  uint32_t mx = 0;
+  for (uint32_t g = blockIdx.x; g < nbins; g += gridDim.x) {
+    const uint64_t c0 = mincode + ((uint64_t)g << shift);
+    uint64_t c1 = c0 + (1ull << shift);
+    if (c1 > maxcode + 1) c1 = maxcode + 1;
+    const uint32_t ncf = (uint32_t)(c1 - c0);
+    const uint32_t base = lb[c0];
+    const uint32_t slots = lb[c1] - base;
+    const uint32_t rs = base - out.partoffset;
+    const uint32_t cnt = gcursor[g] - rs;
+    const uint32_t nsub = ncf * S1;
+    __syncthreads();                                    // previous tile fully consumed
+    for (uint32_t i = threadIdx.x; i <= ncf; i += TS_THREADS) s_lb[i] = lb[c0 + i] - base;
+    for (uint32_t i = threadIdx.x; i < nsub; i += TS_THREADS) s_cur[i] = 0;
+    for (uint32_t i = threadIdx.x; i < ncf; i += TS_THREADS) s_big[i] = 0;
+    __syncthreads();
+    if (slots > TILE_CAP) {
+      // too many suffixes for shared memory: plain insertion, the global kernels sort these buckets
+      for (uint32_t i = threadIdx.x; i < ncf; i += TS_THREADS) s_sub[i] = s_lb[i];
+      __syncthreads();
+      for (uint32_t i = threadIdx.x; i < cnt; i += TS_THREADS) {
+        const ulonglong2 a = __ldcs(rec + rs + i);
+        const uint32_t slot = atomicAdd(&s_sub[(uint32_t)(((a.x >> 32) & REC_CODE_MASK) - c0)], 1u);
+        out.sa[rs + slot] = (uint32_t)a.x;
+        keys_out[rs + slot] = a.y;
+      }
+      __syncthreads();
+      for (uint32_t i = threadIdx.x; i < ncf; i += TS_THREADS) cursor[c0 + i] = base + s_sub[i];
+      if (threadIdx.x == 0) atomicAdd(&out.stats->tile_leftover, 1u);
+      continue;
+    }
+    // ---- P1: histogram over (bucket, first key symbol) ----
+    for (uint32_t i0 = threadIdx.x; i0 < cnt; i0 += TS_THREADS * TS_BATCH) {
+      ulonglong2 r[TS_BATCH];
+#pragma unroll
+      for (int u = 0; u < TS_BATCH; ++u) {
+        const uint32_t i = i0 + u * TS_THREADS;
+        r[u] = i < cnt ? __ldg(rec + rs + i) : make_ulonglong2(0ull, 0ull);
+      }
+#pragma unroll
+      for (int u = 0; u < TS_BATCH; ++u) {
+        const uint32_t i = i0 + u * TS_THREADS;
+        if (i < cnt) {
+          const uint32_t f = ((uint32_t)(r[u].x >> 32) & (uint32_t)REC_CODE_MASK) - (uint32_t)c0;
+          const uint32_t sy = min((uint32_t)(r[u].y >> 56), sigma);
+          atomicAdd(&s_cur[f * S1 + sy], 1u);
+        }
+      }
+    }
+    __syncthreads();
+    // ---- P2: start slot of every group; a bucket with a group too large for a warp is given up as a whole ----
+    for (uint32_t f = threadIdx.x; f < ncf; f += TS_THREADS) {
+      uint32_t run = s_lb[f];
+      bool big = false;
+      for (uint32_t sy = 0; sy < S1; ++sy) {
+        const uint32_t c = s_cur[f * S1 + sy];
+        s_sub[f * S1 + sy] = run;
+        s_cur[f * S1 + sy] = run;
+        run += c;
+        big |= c > SORT_MAXBUCKET;
+      }
+      s_big[f] = big ? 1 : 0;
+    }
+    __syncthreads();
+    // ---- P3: scatter into the groups ----
+    for (uint32_t i0 = threadIdx.x; i0 < cnt; i0 += TS_THREADS * TS_BATCH) {
+      ulonglong2 r[TS_BATCH];
+#pragma unroll
+      for (int u = 0; u < TS_BATCH; ++u) {
+        const uint32_t i = i0 + u * TS_THREADS;
+        r[u] = i < cnt ? __ldcs(rec + rs + i) : make_ulonglong2(0ull, 0ull);
+      }
+#pragma unroll
+      for (int u = 0; u < TS_BATCH; ++u) {
+        const uint32_t i = i0 + u * TS_THREADS;
+        if (i < cnt) {
+          const uint32_t f = ((uint32_t)(r[u].x >> 32) & (uint32_t)REC_CODE_MASK) - (uint32_t)c0;
+          const uint32_t sy = min((uint32_t)(r[u].y >> 56), sigma);
+          const uint32_t slot = atomicAdd(&s_cur[f * S1 + sy], 1u);
+          s_pos[slot] = (uint32_t)r[u].x;
+          s_key[slot] = r[u].y;
+        }
+      }
+    }
+    __syncthreads();
+    // ---- P4: one warp per group ----
+    for (uint32_t q = wid; q < nsub; q += TS_WARPS) {
+      const uint32_t f = q / S1;
+      if (s_big[f]) continue;
+      const uint32_t ls = s_sub[q];
+      const uint32_t cf = s_cur[q] - ls;
+      if (cf == 0) continue;
+      const uint32_t start = rs + ls;
+      bool clean = true;
+      if (cf == 1) {
+        if (lane == 0) put_sa(out, start, s_pos[ls]);
+      } else {
+        const uint32_t *src = s_pos + ls;
+        const uint64_t *keys = s_key + ls;
+        if (cf <= 32) clean = warp_sort_any<8, 1>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else if (cf <= 64) clean = warp_sort_any<8, 2>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else if (cf <= 96) clean = warp_sort_any<8, 3>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+        else clean = warp_sort_any<8, 4>(T, out, src, nullptr, nullptr, keys, start, cf, pl, lane, nullptr, nullptr, sum, mx);
+      }
+      if (lane == 0) {
+        if (ls != s_lb[f]) {                            // first entry of a group that is not the bucket's first
+          __stcs(out.lcp + start, (uint8_t)pl);
+          sum += pl;
+          mx = max(mx, (uint32_t)pl);
+        }
+        if (!clean) {                                   // sorted on pl+7 symbols, tie groups go to refinement
+          const uint64_t rel = c0 + f - mincode;
+          const uint32_t bit = 1u << (rel & 31);
+          const uint32_t old = atomicOr(&fbbits[tieoff + (rel >> 5)], bit);
+          if (!(old & bit)) {
+            atomicAdd(&out.stats->fb_elems, (unsigned long long)(s_cur[f * S1 + sigma] - s_lb[f]));
+            atomicAdd(&out.stats->fb_buckets, 1u);
+          }
+        }
+      }
+    }
+    // ---- per bucket: what the later kernels need to know ----
+    __syncthreads();
+    for (uint32_t f = wid; f < ncf; f += TS_WARPS) {
+      const uint32_t ls = s_lb[f];
+      const uint32_t cf = s_cur[f * S1 + sigma] - ls;   // the last group's end = the bucket's regular suffixes
+      if (s_big[f]) {
+        for (uint32_t i = lane; i < cf; i += 32) {
+          out.sa[rs + ls + i] = s_pos[ls + i];
+          keys_out[rs + ls + i] = s_key[ls + i];
+        }
+        if (lane == 0) {
+          cursor[c0 + f] = base + ls + cf;
+          atomicAdd(&out.stats->tile_leftover, 1u);
+        }
+      } else if (lane == 0) {
+        cursor[c0 + f] = base + ls;
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sum += __shfl_xor_sync(GTB_FULL, sum, o);
+    mx = max(mx, __shfl_xor_sync(GTB_FULL, mx, o));
+  }
+  if (lane == 0) {
+    if (sum) atomicAdd(&out.stats->lcpsum, sum);
+    if (mx) atomicMax(&out.stats->maxdepth, mx);
+  }
+}

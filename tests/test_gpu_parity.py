@@ -162,12 +162,14 @@ def test_tile_path_forced_protein(levels, monkeypatch):
         _compare(got, want, f"tile/protein/{nseq}/pl{pl}/levels{levels}")
 
 
+@pytest.mark.parametrize("subsort", ["1", "0"])
 @pytest.mark.parametrize("levels", ["1", "2"])
-def test_tile_path_keyed_records_protein(levels, monkeypatch):
+def test_tile_path_keyed_records_protein(levels, subsort, monkeypatch):
     """Keyed records on byte text: base-20 codes rolled along 16 positions per thread, 7-residue keys cut by
     separators/wildcards, and the keys of buckets the tile only inserts handed to the block sorter beside the positions."""
     monkeypatch.setenv("GTB200_TILE", "2")
     monkeypatch.setenv("GTB200_KEYED", "2")
+    monkeypatch.setenv("GTB200_SUBSORT", subsort)      # 1: buckets split by the first key symbol inside the tile (default)
     monkeypatch.setenv("GTB200_TILE_LEVELS", levels)
     for nseq, pl, parts in ((1500, 3, 1), (3000, 2, 2), (400, 4, 1), (900, 2, 1), (500, 2, 3), (2500, 5, 1)):
         prot = synth.random_protein(nseq, seed=160 + nseq % 7)
