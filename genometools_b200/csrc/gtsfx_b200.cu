@@ -1119,6 +1119,20 @@ struct WarpSorter32 {
   }
 };
 
+// 20 leading key bits: 10 bases, or 4 symbols squeezed to 5 bits each (values >= 31, padding included, collapse
+// to 31: a monotone map, so the order of the prefixes never contradicts the order of the keys)
+template <int BITS>
+__device__ __forceinline__ uint32_t key_prefix20(uint64_t key) {
+  if (BITS == 2) return (uint32_t)(key >> 44);
+  uint32_t r = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t b = (uint32_t)(key >> (56 - 8 * j)) & 0xffu;
+    r = (r << 5) | (b < 31u ? b : 31u);
+  }
+  return r;
+}
+
 #define GTB_MAXSLICES 8
 #define SORT_MAXBUCKET 128   // warp path: 4 elements per lane keep the kernel at 64 registers (32 warps/SM)
 #define SORT_WARPS 8
@@ -1132,8 +1146,10 @@ template <int BITS, int E>
 __device__ __forceinline__ int warp_sort_bucket32(const Text<BITS> &T, const PartOut &out, const uint32_t *src,
                                                   const uint32_t *pre, const uint8_t *srcL, const uint64_t *pkeys,
                                                   uint32_t start, uint32_t cnt, unsigned pl, int lane, uint64_t *skey_w,
-                                                  uint32_t *spos_w, unsigned long long &sum, uint32_t &mx) {
+                                                  uint32_t *spos_w, unsigned long long &sum, uint32_t &mx, int keyskip) {
   // pkeys: the bucket's full keys are already in shared memory next to its positions (src); nothing is staged
+  // byte text: the network orders by four symbols squeezed to 5 bits each, after skipping keyskip leading key bits
+  // (a group whose first key symbol is known to be equal skips it)
   const uint64_t *skey = pkeys ? pkeys : skey_w;
   const uint32_t *spos = pkeys ? src : spos_w;
   uint32_t k[E];
@@ -1152,7 +1168,7 @@ __device__ __forceinline__ int warp_sort_bucket32(const Text<BITS> &T, const Par
         skey_w[i] = fk;
         spos_w[i] = p;
       }
-      k[e] = ((uint32_t)(fk >> 40) << 8) | i;
+      k[e] = BITS == 2 ? (((uint32_t)(fk >> 40) << 8) | i) : ((key_prefix20<BITS>(fk << keyskip) << 8) | i);
     }
   }
   if (!pkeys) __syncwarp();
@@ -1197,11 +1213,13 @@ template <int BITS, int E>
 __device__ __forceinline__ bool warp_sort_any(const Text<BITS> &T, const PartOut &out, const uint32_t *src,
                                               const uint32_t *pre, const uint8_t *srcL, const uint64_t *pkeys,
                                               uint32_t start, uint32_t cnt, unsigned pl, int lane, uint64_t *skey,
-                                              uint32_t *spos, unsigned long long &sum, uint32_t &mx) {
+                                              uint32_t *spos, unsigned long long &sum, uint32_t &mx, int keyskip = -1) {
   // pre: the bucket's positions already in registers (element e*32+lane in pre[e]), loaded one bucket ahead
   // pkeys: the bucket's keys already in shared memory (element i in pkeys[i], its position in src[i])
-  if (BITS == 2) {
-    if (warp_sort_bucket32<BITS, E>(T, out, src, pre, srcL, pkeys, start, cnt, pl, lane, skey, spos, sum, mx) == 0) return true;
+  // keyskip >= 0 (byte text with the keys in shared memory): 32-bit network first, like DNA
+  if (BITS == 2 || (keyskip >= 0 && pkeys != nullptr)) {
+    if (warp_sort_bucket32<BITS, E>(T, out, src, pre, srcL, pkeys, start, cnt, pl, lane, skey, spos, sum, mx,
+                                    keyskip < 0 ? 0 : keyskip) == 0) return true;
   }
   return warp_sort_bucket<BITS, (E == 3 ? 4 : E)>(T, out, src, pre, srcL, pkeys, start, cnt, pl, lane, sum, mx);
 }
@@ -1312,20 +1330,6 @@ __global__ void __launch_bounds__(256) k_sort_buckets(Text<BITS> T, PartOut out,
 // LCP and tie detection as in the warp sorter.
 #define MED_MAX 1024          // 16 KB of shared memory per block: eight blocks per SM hide the gathers and barriers
 #define MED_SMEM ((size_t)MED_MAX * 16)
-
-// 20 leading key bits: 10 bases, or 4 symbols squeezed to 5 bits each (values >= 31, padding included, collapse
-// to 31: a monotone map, so the order of the prefixes never contradicts the order of the keys)
-template <int BITS>
-__device__ __forceinline__ uint32_t key_prefix20(uint64_t key) {
-  if (BITS == 2) return (uint32_t)(key >> 44);
-  uint32_t r = 0;
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const uint32_t b = (uint32_t)(key >> (56 - 8 * j)) & 0xffu;
-    r = (r << 5) | (b < 31u ? b : 31u);
-  }
-  return r;
-}
 
 template <int E>
 __device__ __forceinline__ void med_chunks(uint32_t *s32, uint32_t P, int wid, int lane, bool full_sort) {
@@ -2389,7 +2393,12 @@ static int count_impl(gtb200_ctx *c, bool need_host_values, uint64_t pos_lo, uin
     const bool fast = BITS == 2 && c->cp.pow2 && c->cp.pl <= 15 && fastmode != 0 &&
                       (fastmode == 2 || (pos_hi - pos_lo) >= (32ull << 20));
     const Text<2> T2 = text_of<2>(c);
-    if (c->numcodes * 4 <= (96ull << 20)) {
+    const bool fastbytes = BITS == 8 && c->cp.pl <= 8 && c->numcodes * 4 <= (96ull << 20) && fastmode != 0 &&
+                           (fastmode == 2 || (pos_hi - pos_lo) >= (32ull << 20));
+    if (fastbytes) {
+      ProfScope ps(c, KC_COUNT);
+      k_count_bytes<<<grid_for((pos_hi - pos_lo + 15) / 16, 256), 256, 0, c->stream>>>(text_of<8>(c), c->cp, pos_lo, pos_hi, c->d_lb);
+    } else if (c->numcodes * 4 <= (96ull << 20)) {
       ProfScope ps(c, KC_COUNT);
       if (fast)
         k_count_dna<<<grid_for((pos_hi - pos_lo + 15) / 16, 256), 256, 0, c->stream>>>(T2, c->cp.pl, pos_lo, pos_hi, c->d_lb, 0u,

@@ -393,15 +393,16 @@ def test_sharded_count_equals_replicated_count():
         it.delete()
 
 
-@pytest.mark.parametrize("case", ["dna_nruns_300k", "dna_nruns_300k_pl3", "dna_tiny_special_ends", "dna_all_special", "dna_single", "dna_polyT"])
+@pytest.mark.parametrize("case", ["dna_nruns_300k", "dna_nruns_300k_pl3", "dna_tiny_special_ends", "dna_all_special", "dna_single", "dna_polyT",
+                                  "protein_60k", "protein_60k_pl3"])
 def test_funnel_shift_counting_kernel(case, monkeypatch):
     """k_count_dna (16 positions per thread, codes by funnel shifts; what genomes of >= 32 M positions use) forced on
     small inputs: windows with specials, sequence ends inside a thread's positions, sharded counting (parts)."""
     monkeypatch.setenv("GTB200_FASTCOUNT", "2")
     enc, alphabet, pl = CASES[case]()
-    want = oracle.build(enc, 4, pl)
+    want = oracle.build(enc, encseq.alphabet_size(alphabet), pl)
     for parts in (1, 3):
-        _compare(sfx.suffixerator(enc, "dna", parts=parts, prefixlength=want["prefixlength"]), want, f"fastcount/{case}/{parts}")
+        _compare(sfx.suffixerator(enc, alphabet, parts=parts, prefixlength=want["prefixlength"]), want, f"fastcount/{case}/{parts}")
 
 
 @pytest.mark.parametrize("narrow", ["1", "0"])
