@@ -2393,12 +2393,7 @@ static int count_impl(gtb200_ctx *c, bool need_host_values, uint64_t pos_lo, uin
     const bool fast = BITS == 2 && c->cp.pow2 && c->cp.pl <= 15 && fastmode != 0 &&
                       (fastmode == 2 || (pos_hi - pos_lo) >= (32ull << 20));
     const Text<2> T2 = text_of<2>(c);
-    const bool fastbytes = BITS == 8 && c->cp.pl <= 8 && c->numcodes * 4 <= (96ull << 20) && fastmode != 0 &&
-                           (fastmode == 2 || (pos_hi - pos_lo) >= (32ull << 20));
-    if (fastbytes) {
-      ProfScope ps(c, KC_COUNT);
-      k_count_bytes<<<grid_for((pos_hi - pos_lo + 15) / 16, 256), 256, 0, c->stream>>>(text_of<8>(c), c->cp, pos_lo, pos_hi, c->d_lb);
-    } else if (c->numcodes * 4 <= (96ull << 20)) {
+    if (c->numcodes * 4 <= (96ull << 20)) {
       ProfScope ps(c, KC_COUNT);
       if (fast)
         k_count_dna<<<grid_for((pos_hi - pos_lo + 15) / 16, 256), 256, 0, c->stream>>>(T2, c->cp.pl, pos_lo, pos_hi, c->d_lb, 0u,

@@ -906,22 +906,3 @@ __global__ void __launch_bounds__(TS_THREADS, 2) k_tile_subsort(Text<8> T, PartO
     if (mx) atomicMax(&out.stats->maxdepth, mx);
   }
 }
-
-// Counting on byte text with the same rolled base-sigma codes (k_kmers<8,0> recomputes pl multiply-adds and an
-// unaligned 64-bit window per position): 16 positions per thread, one RED per suffix with pl real symbols ahead.
-__global__ void __launch_bounds__(256) k_count_bytes(Text<8> T, CodeParams cp, uint64_t pbase, uint64_t pend,
-                                                     uint32_t *__restrict__ table) {
-  const uint64_t p0 = pbase + ((uint64_t)blockIdx.x * 256 + threadIdx.x) * KP_PPT;
-  if (p0 >= pend) return;
-  const unsigned pl = cp.pl;
-  const KbWin k = kb_load(T, p0);
-  const unsigned sh = 8u * pl;
-  const uint64_t v0 = pl == 8 ? k.w1 : (k.w0 << sh) | (k.w1 >> (64 - sh));
-  const uint64_t v1 = pl == 8 ? k.w2 : (k.w1 << sh) | (k.w2 >> (64 - sh));
-  uint32_t code[KP_PPT];
-  kb_codes(k, pl, cp.sigma, (uint32_t)cp.pw[pl - 1], v0, v1, code);
-  const uint32_t plmask = (1u << pl) - 1u;
-#pragma unroll
-  for (int i = 0; i < KP_PPT; ++i)
-    if (((k.sp >> i) & plmask) == 0u) atomicAdd(&table[code[i]], 1u);
-}

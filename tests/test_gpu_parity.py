@@ -393,8 +393,7 @@ def test_sharded_count_equals_replicated_count():
         it.delete()
 
 
-@pytest.mark.parametrize("case", ["dna_nruns_300k", "dna_nruns_300k_pl3", "dna_tiny_special_ends", "dna_all_special", "dna_single", "dna_polyT",
-                                  "protein_60k", "protein_60k_pl3"])
+@pytest.mark.parametrize("case", ["dna_nruns_300k", "dna_nruns_300k_pl3", "dna_tiny_special_ends", "dna_all_special", "dna_single", "dna_polyT"])
 def test_funnel_shift_counting_kernel(case, monkeypatch):
     """k_count_dna (16 positions per thread, codes by funnel shifts; what genomes of >= 32 M positions use) forced on
     small inputs: windows with specials, sequence ends inside a thread's positions, sharded counting (parts)."""
