@@ -478,7 +478,7 @@ def main():
     e2e_s = float(t.item())
     h2d = (words_h.numel() * words_h.element_size() + ranges_h.numel() * 8) if rank == 0 else 0
     # the library ships 32-bit positions and widens them on the host when one GPU feeds one PCIe link (narrow transfer)
-    narrow = os.environ.get("GTB200_NARROW", "1") != "0" and width >= (4 << 20)
+    narrow = os.environ.get("GTB200_NARROW", "1") != "0" and width >= (32 << 20)
     suf_bus_bytes = 4 if narrow else 8
     d2h = width * suf_bus_bytes + (suf_h.numel() - width) * 8 + width + (numcodes + 1) * 4 + csc_h.numel() * 4 \
         + int(it.countinfo.numofdistpfxidx) * 4
