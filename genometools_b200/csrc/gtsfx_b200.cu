@@ -3463,3 +3463,4 @@ extern "C" int gtb200_profile_read(gtb200_ctx *c, const char **names, double *ms
   return KC_NUM;
 }
 #include "multi.cuh"
+#include "fasta.cuh"

@@ -56,6 +56,11 @@ class CountInfo(C.Structure):
                 ("specialcharacters", C.c_uint64), ("largestbucket", C.c_uint64)]
 
 
+class FastaInfo(C.Structure):
+    _fields_ = [("totallength", C.c_uint64), ("numofsequences", C.c_uint64), ("specialcharacters", C.c_uint64),
+                ("prefixlength", C.c_uint)]
+
+
 class PartInfo(C.Structure):
     _fields_ = [("partoffset", C.c_uint64), ("width", C.c_uint64),
                 ("numoflargelcpvalues", C.c_uint64), ("maxbranchdepth", C.c_uint64),
@@ -72,7 +77,7 @@ EXPORTS = [
     "gtb200_count_shard", "gtb200_count_finish", "gtb200_part_diag",
     "gtb200_multi_open", "gtb200_multi_close", "gtb200_multi_count", "gtb200_multi_sort_part", "gtb200_multi_tail",
     "gtb200_multi_devices", "gtb200_multi_ctx", "gtb200_multi_peer_bytes", "gtb200_host_register",
-    "gtb200_host_unregister", "gtb200_multi_free_memory", "gtb200_tail_device",
+    "gtb200_host_unregister", "gtb200_multi_free_memory", "gtb200_tail_device", "gtb200_open_fasta",
 ]
 
 
@@ -113,6 +118,8 @@ def load_library() -> C.CDLL:
     L.gtb200_leftborder_partialsums_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
                                                         C.c_char_p, C.c_size_t]
     L.gtb200_part_diag.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_int]
+    L.gtb200_open_fasta.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_void_p, C.c_uint64, C.c_int, C.c_uint,
+                                    C.POINTER(FastaInfo)]
     L.gtb200_multi_open.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.c_int, C.POINTER(SeqDesc), C.c_uint]
     L.gtb200_multi_close.argtypes = [C.c_void_p]
     L.gtb200_multi_close.restype = None
@@ -165,7 +172,8 @@ class Sfxiterator:
                  enc: np.ndarray | int | None = None, twobit: np.ndarray | int | None = None,
                  ranges: np.ndarray | int | None = None, numofwords: int = 0, numofranges: int = 0,
                  device: int = 0, device_ptrs: bool = False, with_lcp: bool = True, suftabuint: bool = False,
-                 code_range: tuple[int, int] | None = None, readmode: int = 0, devices: list[int] | None = None):
+                 code_range: tuple[int, int] | None = None, readmode: int = 0, devices: list[int] | None = None,
+                 fasta: bytes | None = None):
         L = load_library()
         self._L = L
         self._ctx = C.c_void_p()
@@ -176,13 +184,26 @@ class Sfxiterator:
         self.prefixlength = prefixlength or recommended_prefixlength(sigma, totallength)
         self.suftabuint = suftabuint
         self.with_lcp = with_lcp
+        self.fastainfo = None
+        if fasta is not None:
+            # FASTA text straight to the device (gtb200_open_fasta): description lines, white space, symbol map and
+            # separators are handled there; totallength and the automatic prefix length come back
+            buf = np.frombuffer(fasta, dtype=np.uint8)
+            fi = FastaInfo()
+            _check(L.gtb200_open_fasta(C.byref(self._ctx), device, buf.ctypes.data, buf.shape[0], 1 if sigma == 20 else 0,
+                                       prefixlength or 0, C.byref(fi)))
+            self.fastainfo = fi
+            self.totallength = totallength = int(fi.totallength)
+            self.prefixlength = int(fi.prefixlength)
         desc = SeqDesc()
         desc.numofchars = sigma
         desc.totallength = totallength
         desc.memory = 1 if device_ptrs else 0
         desc.readmode = readmode
         self._keep = []
-        if twobit is not None:
+        if fasta is not None:
+            pass                                    # already open
+        elif twobit is not None:
             if device_ptrs:
                 desc.twobitencoding, desc.numofwords = int(twobit), numofwords
                 desc.specialranges, desc.numofspecialranges = int(ranges or 0), numofranges
@@ -199,7 +220,9 @@ class Sfxiterator:
                 e = np.ascontiguousarray(enc, dtype=np.uint8)
                 self._keep.append(e)
                 desc.encoded = e.ctypes.data
-        if self.devices:
+        if fasta is not None:
+            pass
+        elif self.devices:
             devs = (C.c_int * len(self.devices))(*self.devices)
             _check(L.gtb200_multi_open(C.byref(self._multi), devs, len(self.devices), C.byref(desc), self.prefixlength))
             self._ctx = C.c_void_p(L.gtb200_multi_ctx(self._multi, 0))
@@ -371,18 +394,22 @@ class Sfxiterator:
             pass
 
 
-def suffixerator(enc: np.ndarray, alphabet: str = "dna", indexname: str | None = None, parts: int = 1,
+def suffixerator(enc: np.ndarray | None, alphabet: str = "dna", indexname: str | None = None, parts: int = 1,
                  prefixlength: int | None = None, device: int = 0, use_twobit: bool | None = None,
-                 readmode: int = 0, devices: list[int] | None = None, sigma: int | None = None) -> dict:
+                 readmode: int = 0, devices: list[int] | None = None, sigma: int | None = None,
+                 fasta: bytes | None = None) -> dict:
     """`gt suffixerator -suf -lcp -bck` on an encoded sequence: runs the iterator to exhaustion and
     returns the byte images of .suf/.lcp/.llv/.bck plus the .prj statistics; writes the files when
     ``indexname`` is given."""
     if sigma is None:               # any other alphabet (a -smap symbol map): give its size, the sequence goes in as bytes
         sigma = _encseq.alphabet_size(alphabet)
-    n = int(enc.shape[0])
+    n = int(enc.shape[0]) if fasta is None else 0
     if use_twobit is None:
         use_twobit = alphabet == "dna" and sigma == 4
-    if use_twobit:
+    if fasta is not None:            # FASTA text in, everything from the parse on happens on the device
+        it = Sfxiterator(sigma, 0, prefixlength, parts, device=device, fasta=fasta)
+        n = it.totallength
+    elif use_twobit:
         it = Sfxiterator(sigma, n, prefixlength, parts, twobit=_encseq.twobit_pack(enc),
                          ranges=_encseq.special_ranges(enc), device=device, readmode=readmode, devices=devices)
     else:

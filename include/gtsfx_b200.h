@@ -112,6 +112,22 @@ void gtb200_release_cached_memory(void);
  * time with CUDA events or order their own copies after the kernels. */
 void *gtb200_stream(gtb200_ctx *ctx);
 
+/*
+ * The same set-up straight from FASTA text (for the index path): the scan that
+ * gt_sequence_buffer_fasta_advance (src/core/sequence_buffer_fasta.c:40-170) performs character by character inside
+ * gt_encseq_encoder_encode (src/core/encseq.c:8523) - descriptions from '>' to the end of the line, white space
+ * skipped, one separator between sequences, symbols mapped as gt_alphabet_new_dna/_protein do
+ * (src/core/alphabet.c:84-91) - runs on the device; the text of several files is passed concatenated.
+ * prefixlength 0 = gt_recommendedprefixlength.  The on-disk .esq/.ssp/.des files remain the host encoder's job.
+ * An illegal character or a text without '>' is an error, as in the reference.
+ */
+typedef struct {
+  uint64_t totallength, numofsequences, specialcharacters;
+  unsigned prefixlength;
+} gtb200_fastainfo;
+int gtb200_open_fasta(gtb200_ctx **ctx, int device, const uint8_t *fasta, uint64_t nbytes, int protein,
+                      unsigned prefixlength, gtb200_fastainfo *info);
+
 /* -- phase 1: "counting prefix distribution" ------------------------------------------------- */
 
 /*
