@@ -51,7 +51,7 @@ def raw(path):
 
 
 # kernel name -> bench.py kernel class (the ProfScope classes of csrc/gtsfx_b200.cu)
-CLASS_OF = [("k_kmers<2, 0>", "count"), ("k_kmers<2, 2>", "count"), ("k_kmers<8, 0>", "count"), ("k_kmers<8, 2>", "count"),
+CLASS_OF = [("k_count_dna", "count"), ("k_tile_subsort", "sort_lcp"), ("k_kmers<2, 0>", "count"), ("k_kmers<2, 2>", "count"), ("k_kmers<8, 0>", "count"), ("k_kmers<8, 2>", "count"),
             ("k_kmers<2, 1>", "scatter"), ("k_kmers<8, 1>", "scatter"), ("k_keyed_partition", "scatter"),
             ("k_stage_partition", "scatter"), ("k_partition", "scatter"), ("k_scatter_", "scatter"), ("k_bins_init", "scatter"),
             ("k_keyed_chunk_table", "scatter"), ("k_chunk_table", "scatter"), ("k_tile_sort", "sort_lcp"),
