@@ -126,3 +126,45 @@ void gtb200_widen_u32_u64(const uint32_t *src, uint64_t *dst, size_t n)
 #endif
   for (size_t i = 0; i < n; i++) dst[i] = src[i];
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * The per-GPU cut of one part (gtb200_multi_sort_part): [mincode, maxcode] into at most nshards code ranges of about
+ * equal suffix count.  Same rule as gt_suftabparts_new applies to the whole table (src/match/sfx-partssuf.c:172-343,
+ * gt_bcktab_findfirstlarger src/match/bcktab.c:1322-1381): shard d ends at the first bucket whose END offset reaches
+ * base + width * d / nshards; ranges without suffixes are merged into their successor.  leftborder = bucket START
+ * offsets (numofallcodes + 1 entries).  Returns the number of ranges written to lo[] / hi[] (inclusive codes).
+ * --------------------------------------------------------------------------------------------- */
+int gtb200_split_range(const uint32_t *leftborder, uint64_t mincode, uint64_t maxcode, int nshards,
+                       uint64_t *lo, uint64_t *hi)
+{
+  const uint64_t base = leftborder[mincode], width = (uint64_t) leftborder[maxcode + 1] - base;
+  uint64_t start = mincode;
+  int k = 0, d;
+
+  for (d = 1; d <= nshards && start <= maxcode; d++)
+  {
+    uint64_t end;
+    if (d == nshards)
+    {
+      end = maxcode;
+    } else
+    {
+      const uint64_t target = base + width * (uint64_t) d / (uint64_t) nshards;
+      uint64_t a = start + 1, b = maxcode + 2;          /* first index i in [a,b) with leftborder[i] >= target */
+      while (a < b)
+      {
+        const uint64_t mid = a + (b - a) / 2;
+        if ((uint64_t) leftborder[mid] < target) a = mid + 1; else b = mid;
+      }
+      end = a - 1;
+      if (end > maxcode) end = maxcode;
+      if (leftborder[end + 1] == leftborder[start]) continue;     /* nothing to sort yet: extend with the next target */
+    }
+    lo[k] = start;
+    hi[k] = end;
+    k++;
+    start = end + 1;
+  }
+  if (k > 0 && hi[k - 1] != maxcode) hi[k - 1] = maxcode;
+  return k;
+}

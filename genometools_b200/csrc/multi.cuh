@@ -219,32 +219,11 @@ extern "C" int gtb200_multi_count(gtb200_multi *m, uint32_t *leftborder, uint32_
   return 0;
 }
 
-// Cuts [mincode, maxcode] into at most ndev code ranges of about equal suffix count (same rule as the reference's
-// parts: a range ends at the first bucket whose end offset reaches the target, src/match/sfx-partssuf.c:172-343).
+// the per-GPU cut of a part: pure host logic, csrc/host_logic.c (tested on the CPU)
+extern "C" int gtb200_split_range(const uint32_t *leftborder, uint64_t mincode, uint64_t maxcode, int nshards,
+                                  uint64_t *lo, uint64_t *hi);
 static int multi_split(const gtb200_multi *m, uint64_t mincode, uint64_t maxcode, uint64_t *lo, uint64_t *hi) {
-  const uint32_t *lb = m->h_lb.data();
-  const uint64_t base = lb[mincode], W = (uint64_t)lb[maxcode + 1] - base;
-  int k = 0;
-  uint64_t start = mincode;
-  for (int d = 1; d <= m->ndev && start <= maxcode; ++d) {
-    uint64_t end;                                   // last code of this range
-    if (d == m->ndev) {
-      end = maxcode;
-    } else {
-      const uint64_t target = base + W * (uint64_t)d / (uint64_t)m->ndev;
-      // first code c >= start whose END offset lb[c+1] >= target
-      const uint32_t *p = std::lower_bound(lb + start + 1, lb + maxcode + 2, (uint32_t)target);
-      end = (uint64_t)(p - lb) - 1;
-      if (end > maxcode) end = maxcode;
-    }
-    if (lb[end + 1] == lb[start] && d != m->ndev) continue;      // nothing to sort yet: extend with the next target
-    lo[k] = start;
-    hi[k] = end;
-    ++k;
-    start = end + 1;
-  }
-  if (k > 0 && hi[k - 1] != maxcode) hi[k - 1] = maxcode;
-  return k;
+  return gtb200_split_range(m->h_lb.data(), mincode, maxcode, m->ndev, lo, hi);
 }
 
 extern "C" int gtb200_multi_sort_part(gtb200_multi *m, uint64_t mincode, uint64_t maxcode, void *suftab,

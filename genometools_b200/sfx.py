@@ -77,7 +77,7 @@ EXPORTS = [
     "gtb200_count_shard", "gtb200_count_finish", "gtb200_part_diag",
     "gtb200_multi_open", "gtb200_multi_close", "gtb200_multi_count", "gtb200_multi_sort_part", "gtb200_multi_tail",
     "gtb200_multi_devices", "gtb200_multi_ctx", "gtb200_multi_peer_bytes", "gtb200_host_register",
-    "gtb200_host_unregister", "gtb200_multi_free_memory", "gtb200_tail_device", "gtb200_open_fasta",
+    "gtb200_host_unregister", "gtb200_multi_free_memory", "gtb200_tail_device", "gtb200_open_fasta", "gtb200_split_range",
 ]
 
 
@@ -118,6 +118,7 @@ def load_library() -> C.CDLL:
     L.gtb200_leftborder_partialsums_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
                                                         C.c_char_p, C.c_size_t]
     L.gtb200_part_diag.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_int]
+    L.gtb200_split_range.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]
     L.gtb200_open_fasta.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_void_p, C.c_uint64, C.c_int, C.c_uint,
                                     C.POINTER(FastaInfo)]
     L.gtb200_multi_open.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.c_int, C.POINTER(SeqDesc), C.c_uint]
@@ -158,6 +159,14 @@ def suftabparts(numofparts: int, leftborder: np.ndarray, prefixlength: int):
     k = L.gtb200_suftabparts(numofparts, leftborder.ctypes.data, numcodes, prefixlength,
                              mn.ctypes.data, mx.ctypes.data, wd.ctypes.data)
     return [(int(mn[i]), int(mx[i]), int(wd[i])) for i in range(k)]
+
+
+def split_range(leftborder: np.ndarray, mincode: int, maxcode: int, nshards: int):
+    """[(lo, hi)] - the per-GPU cut of one part (gtb200_split_range)."""
+    lo = np.zeros(nshards, dtype=np.uint64)
+    hi = np.zeros(nshards, dtype=np.uint64)
+    k = load_library().gtb200_split_range(leftborder.ctypes.data, mincode, maxcode, nshards, lo.ctypes.data, hi.ctypes.data)
+    return [(int(lo[i]), int(hi[i])) for i in range(k)]
 
 
 class Sfxiterator:

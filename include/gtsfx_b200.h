@@ -221,6 +221,14 @@ int gtb200_suftabparts(unsigned numofparts, const uint32_t *leftborder, uint64_t
                        unsigned prefixlength, uint64_t *mincodes, uint64_t *maxcodes,
                        uint64_t *widths);
 
+/*
+ * The per-GPU cut of one part, as gtb200_multi_sort_part applies it: [mincode, maxcode] into at most nshards code
+ * ranges of about equal suffix count, by the rule gt_suftabparts_new applies to the whole table
+ * (src/match/sfx-partssuf.c:172-343).  lo/hi have room for nshards entries (inclusive codes); returns their number.
+ */
+int gtb200_split_range(const uint32_t *leftborder, uint64_t mincode, uint64_t maxcode, int nshards,
+                       uint64_t *lo, uint64_t *hi);
+
 /* Per-kernel-class device time (ms, CUDA events on the context's stream) accumulated since the
  * last gtb200_profile_reset; names[i] are static strings.  Returns the number of classes. */
 int gtb200_profile_enable(gtb200_ctx *ctx, int on);

@@ -74,3 +74,34 @@ def test_no_cpu_fallback_without_gpu():
     with pytest.raises(sfx.Gtb200Error) as ei:
         sfx.suffixerator(enc, "dna")
     assert "no CPU fallback" in str(ei.value) or "CUDA" in str(ei.value)
+
+
+def test_split_range_covers_the_part_in_balanced_contiguous_ranges():
+    """gtb200_split_range (the per-GPU cut inside gtb200_multi_sort_part) is host logic: every code of the part lies in
+    exactly one range, ranges are ordered, none is without suffixes, and no range exceeds its fair share by more than
+    the bucket that crosses the target."""
+    rng = np.random.default_rng(7)
+    for trial in range(40):
+        ncodes = int(rng.integers(1, 5000))
+        sizes = rng.integers(0, 50, size=ncodes).astype(np.uint32)
+        sizes[rng.random(ncodes) < 0.3] = 0
+        if trial % 5 == 0:
+            sizes[:] = 0
+            sizes[int(rng.integers(0, ncodes))] = 1000          # everything in one bucket
+        lb = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint32)
+        mincode = int(rng.integers(0, ncodes))
+        maxcode = int(rng.integers(mincode, ncodes))
+        for nshards in (1, 2, 3, 8, 16):
+            ranges = sfx.split_range(lb, mincode, maxcode, nshards)
+            total = int(lb[maxcode + 1]) - int(lb[mincode])
+            if total == 0:
+                assert len(ranges) <= 1
+                continue
+            assert 1 <= len(ranges) <= nshards
+            assert ranges[0][0] == mincode and ranges[-1][1] == maxcode
+            for (a, b), (c, d) in zip(ranges, ranges[1:]):
+                assert c == b + 1
+            widths = [int(lb[b + 1]) - int(lb[a]) for a, b in ranges]
+            assert sum(widths) == total and all(w > 0 for w in widths[:-1])
+            fair = total / nshards
+            assert max(widths) <= 2 * fair + int(sizes.max()) + 1
