@@ -3236,6 +3236,10 @@ static int sort_part_impl(gtb200_ctx *c, uint64_t mincode, uint64_t maxcode, gtb
   int S = 1;
   if (to_host && c->pipeline && width >= (2u << 20) && ncodes >= 4096) {
     S = width >= (64u << 20) ? GTB_MAXSLICES : width >= (16u << 20) ? 4 : 2;
+    // every slice of a tile-path part scans the whole text for its code range: a part that is itself a small share of
+    // the suffix array (one of many parts, one GPU's range of a part) is cut into fewer slices or none
+    const uint64_t fair = c->nsort ? width * 16 / c->nsort : 16;
+    if ((uint64_t)S > fair) S = fair < 2 ? 1 : (int)fair;
   }
   uint64_t blo[GTB_MAXSLICES + 1], boff[GTB_MAXSLICES + 1];
   blo[0] = mincode; boff[0] = 0;

@@ -131,8 +131,27 @@ extern "C" int gtb200_multi_open(gtb200_multi **out, const int *devices, int nde
       (void)cudaGetLastError();
     }
   }
-  for (int d = 1; d < ndev; ++d) {
-    if (ctx_clone(m->ctx[0], devices[d], &m->ctx[d], &m->peer_bytes)) { gtb200_multi_close(m); return -1; }
+  {
+    // the copies to the other GPUs run concurrently (context creation and the first allocations on a fresh device
+    // take longer than the 1.2 GB copy itself)
+    std::vector<std::thread> workers;
+    int rcs[GTB200_MAXDEV] = {0};
+    uint64_t moved[GTB200_MAXDEV] = {0};
+    std::string msg[GTB200_MAXDEV];
+    for (int d = 1; d < ndev; ++d)
+      workers.emplace_back([&, d]() {
+        rcs[d] = ctx_clone(m->ctx[0], devices[d], &m->ctx[d], &moved[d]);
+        if (rcs[d]) msg[d] = gtb200_last_error();
+      });
+    for (auto &w : workers) w.join();
+    for (int d = 1; d < ndev; ++d) {
+      m->peer_bytes += moved[d];
+      if (rcs[d]) {
+        set_error("%s", msg[d].c_str());
+        gtb200_multi_close(m);
+        return -1;
+      }
+    }
   }
   // Several GPUs bring several PCIe links, and the host cores that widen 32-bit positions are then the narrower
   // resource (measured: 2 GPUs, 3.1 Gbp, 429 ms narrow against 401 ms on one GPU): copy the 64-bit image directly.
