@@ -257,6 +257,16 @@ class Sfxiterator:
         if code_range is not None:  # one shard of a multi-GPU run: a single, externally chosen part
             lo, hi = code_range
             self.parts = [(lo, hi, int(self.leftborder[hi + 1]) - int(self.leftborder[lo]))]
+        self._sufbuf = self._lcpbuf = None
+        self._registered = []
+        if self.devices and len(self.devices) > 1 and self.parts:
+            # like the drop-in's constructor: page-lock the part buffers once (seconds for tens of GB, not per part)
+            largest = max(w for _, _, w in self.parts)
+            self._sufbuf = np.empty(max(largest, 1), dtype=np.uint32 if self.suftabuint else np.uint64)
+            self._lcpbuf = np.empty(max(largest, 1), dtype=np.uint8)
+            for b in (self._sufbuf, self._lcpbuf):
+                if L.gtb200_host_register(b.ctypes.data, b.nbytes) == 0:
+                    self._registered.append(b)
         self._part = 0
         self._tail_done = False
         self._longest = None
@@ -311,16 +321,8 @@ class Sfxiterator:
             mincode, maxcode, width = self.parts[self._part]
             self._part += 1
             if self.devices and len(self.devices) > 1:
-                # several GPUs copy straight into the part buffers: one page-locked pair for all parts (the returned
-                # arrays are views, valid until the next call - gt_Sfxiterator_next's own contract)
-                if getattr(self, "_sufbuf", None) is None:
-                    largest = max(w for _, _, w in self.parts)
-                    self._sufbuf = np.empty(max(largest, 1), dtype=np.uint32 if self.suftabuint else np.uint64)
-                    self._lcpbuf = np.empty(max(largest, 1), dtype=np.uint8)
-                    self._registered = []
-                    for b in (self._sufbuf, self._lcpbuf):
-                        if self._L.gtb200_host_register(b.ctypes.data, b.nbytes) == 0:
-                            self._registered.append(b)
+                # several GPUs copy straight into the part buffers: one page-locked pair for all parts, set up by the
+                # constructor (the returned arrays are views, valid until the next call - gt_Sfxiterator_next's contract)
                 suf, lcp = self._sufbuf[:width], self._lcpbuf[:width]
             else:
                 suf = np.empty(width, dtype=np.uint32 if self.suftabuint else np.uint64)
