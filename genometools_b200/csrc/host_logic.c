@@ -168,3 +168,31 @@ int gtb200_split_range(const uint32_t *leftborder, uint64_t mincode, uint64_t ma
   if (k > 0 && hi[k - 1] != maxcode) hi[k - 1] = maxcode;
   return k;
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * "0,1,4-7" -> {0,1,4,5,6,7}: the device list of GTB200_DEVICES (integration/sfx_suffixer_b200.c).  Stops at the
+ * first character that is neither a number, ',' nor '-'; returns the number of devices written (<= capacity), or 0.
+ * --------------------------------------------------------------------------------------------- */
+#include <stdlib.h>
+int gtb200_parse_devices(const char *text, int *devices, int capacity)
+{
+  int n = 0;
+  if (text == NULL) return 0;
+  while (*text != '\0' && n < capacity)
+  {
+    char *end;
+    long a = strtol(text, &end, 10), b;
+    if (end == text || a < 0) break;
+    b = a;
+    if (*end == '-')
+    {
+      text = end + 1;
+      b = strtol(text, &end, 10);
+      if (end == text || b < a) break;
+    }
+    for (; a <= b && n < capacity; a++) devices[n++] = (int) a;
+    if (*end != ',') break;
+    text = end + 1;
+  }
+  return n;
+}

@@ -77,7 +77,7 @@ EXPORTS = [
     "gtb200_count_shard", "gtb200_count_finish", "gtb200_part_diag",
     "gtb200_multi_open", "gtb200_multi_close", "gtb200_multi_count", "gtb200_multi_sort_part", "gtb200_multi_tail",
     "gtb200_multi_devices", "gtb200_multi_ctx", "gtb200_multi_peer_bytes", "gtb200_host_register",
-    "gtb200_host_unregister", "gtb200_multi_free_memory", "gtb200_tail_device", "gtb200_open_fasta", "gtb200_split_range",
+    "gtb200_host_unregister", "gtb200_multi_free_memory", "gtb200_tail_device", "gtb200_open_fasta", "gtb200_split_range", "gtb200_parse_devices", "gtb200_widen_u32_u64",
 ]
 
 

@@ -229,6 +229,14 @@ int gtb200_suftabparts(unsigned numofparts, const uint32_t *leftborder, uint64_t
 int gtb200_split_range(const uint32_t *leftborder, uint64_t mincode, uint64_t maxcode, int nshards,
                        uint64_t *lo, uint64_t *hi);
 
+/* "0,1,4-7" -> {0,1,4,5,6,7}: the device list a B200 build of libgenometools reads from GTB200_DEVICES (no reference
+ * counterpart: the reference has no devices; its analogue is `gt -j`, src/gtr.c:181).  Returns the count, 0 if none. */
+int gtb200_parse_devices(const char *text, int *devices, int capacity);
+
+/* Host half of the narrow transfer: widens 32-bit positions to the GtUword entries gt_suffixsortspace_to_file writes
+ * (src/match/sfx-suffixgetset.c:462-478), streaming stores. */
+void gtb200_widen_u32_u64(const uint32_t *src, uint64_t *dst, size_t n);
+
 /* Per-kernel-class device time (ms, CUDA events on the context's stream) accumulated since the
  * last gtb200_profile_reset; names[i] are static strings.  Returns the number of classes. */
 int gtb200_profile_enable(gtb200_ctx *ctx, int on);

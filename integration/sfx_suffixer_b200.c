@@ -81,30 +81,7 @@ static int b200_devices(int *devs)
     devs[0] = env != NULL ? atoi(env) : 0;
     return 1;
   }
-  while (*env != '\0' && n < B200_MAXDEV)
-  {
-    char *end;
-    long a = strtol(env, &end, 10), b;
-    if (end == env)
-    {
-      break;
-    }
-    b = a;
-    if (*end == '-')
-    {
-      env = end + 1;
-      b = strtol(env, &end, 10);
-    }
-    for (; a <= b && n < B200_MAXDEV; a++)
-    {
-      devs[n++] = (int) a;
-    }
-    env = (*end == ',') ? end + 1 : end;
-    if (*end != ',' && *end != '\0')
-    {
-      break;
-    }
-  }
+  n = gtb200_parse_devices(env, devs, B200_MAXDEV);
   if (n == 0)
   {
     devs[0] = 0;

@@ -105,3 +105,30 @@ def test_split_range_covers_the_part_in_balanced_contiguous_ranges():
             assert sum(widths) == total and all(w > 0 for w in widths[:-1])
             fair = total / nshards
             assert max(widths) <= 2 * fair + int(sizes.max()) + 1
+
+
+def test_device_list_parser():
+    import ctypes as C
+    L = sfx.load_library()
+    L.gtb200_parse_devices.argtypes = [C.c_char_p, C.POINTER(C.c_int), C.c_int]
+    out = (C.c_int * 16)()
+    for text, want in ((b"0", [0]), (b"0,1,4-7", [0, 1, 4, 5, 6, 7]), (b"3-3", [3]), (b"0-15", list(range(16))),
+                       (b"0-99", list(range(16))), (b"", []), (b"x", []), (b"1,", [1]), (b"2,x", [2]), (b"5-2", [])):
+        k = L.gtb200_parse_devices(text, out, 16)
+        assert [out[i] for i in range(k)] == want, (text, [out[i] for i in range(k)])
+
+
+def test_widening_of_positions_is_exact_for_every_alignment():
+    import ctypes as C
+    L = sfx.load_library()
+    L.gtb200_widen_u32_u64.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+    L.gtb200_widen_u32_u64.restype = None
+    rng = np.random.default_rng(3)
+    src = rng.integers(0, 2 ** 32, size=5000, dtype=np.uint64).astype(np.uint32)
+    for off_s in (0, 1, 3):
+        for off_d in (0, 1, 2, 3):
+            for n in (0, 1, 7, 8, 9, 31, 1000, 4093):
+                dst = np.full(n + 8, 0xdeadbeefdeadbeef, dtype=np.uint64)
+                L.gtb200_widen_u32_u64(src[off_s:].ctypes.data, dst[off_d:].ctypes.data, n)
+                assert np.array_equal(dst[off_d:off_d + n], src[off_s:off_s + n].astype(np.uint64))
+                assert (dst[:off_d] == 0xdeadbeefdeadbeef).all() and (dst[off_d + n:] == 0xdeadbeefdeadbeef).all()
