@@ -132,6 +132,7 @@ struct gtb200_ctx {
   uint32_t *d_isa;           // rank array of the prefix-doubling refinement (n+1 entries)
   uint64_t cap_isa;
   int doubling;              // 1 = prefix doubling when the part is the whole array (GTB200_DOUBLING, testing knob)
+  int extend;                // 1 = text-window rounds skip the windows a whole group shares (GTB200_EXTEND, testing knob)
   uint32_t *d_bins;          // bin cursors / starts / chunk table of the tile path
   uint64_t cap_recB, cap_bins;
   // per part
@@ -1692,6 +1693,39 @@ __global__ void k_fb_compact(const uint32_t *__restrict__ keep, const uint32_t *
 
 __global__ void k_reset_posmode(PartStats *stats) { stats->posmode_kept = 0; }
 
+// Skip-ahead for text-window rounds (parts that do not cover the whole suffix array cannot use rank doubling, the
+// ranks of other parts' suffixes are unknown): a group tied on d symbols whose members go on agreeing for another
+// e windows of W real symbols is moved to depth d + e*W at once, so the next round meets the window in which the
+// group splits (or a special cuts it).  A repeat of length R then costs R/(maxwin*W) rounds instead of R/W.
+// The members of a group occupy consecutive suffix-array slots, so sa[gs[j]] is the group's first member: every
+// member counts the windows it shares with that one, the minimum over the group goes to the slot of the first
+// member's list entry (list index j - (idx[j] - gs[j])).  Equal keys with tag 0 = W equal real symbols.
+template <int BITS>
+__global__ void k_fb_extend_count(Text<BITS> T, const uint32_t *__restrict__ sa, const uint32_t *__restrict__ idx,
+                                  const uint32_t *__restrict__ gs, const uint32_t *__restrict__ dep, uint32_t A,
+                                  uint32_t maxwin, uint32_t *extmin) {
+  constexpr int W = Text<BITS>::W;
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= A) return;
+  const uint32_t d = dep[j], r = idx[j], g = gs[j];
+  if (d == GTB_POSMODE || r == g) return;
+  const uint64_t p = (uint64_t)sa[r] + d, q = (uint64_t)sa[g] + d;
+  uint32_t e = 0;
+  while (e < maxwin) {
+    const uint64_t ka = make_key<BITS>(T, p + (uint64_t)e * W);
+    if ((ka & 0xff) != 0 || ka != make_key<BITS>(T, q + (uint64_t)e * W)) break;
+    e++;
+  }
+  atomicMin(&extmin[j - (r - g)], e);
+}
+
+__global__ void k_fb_extend_apply(const uint32_t *__restrict__ idx, const uint32_t *__restrict__ gs, uint32_t A,
+                                  unsigned W, const uint32_t *__restrict__ extmin, uint32_t *dep) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= A || dep[j] == GTB_POSMODE) return;
+  dep[j] += extmin[j - (idx[j] - gs[j])] * W;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Prefix doubling (Larsson-Sadakane style) for parts that cover the whole suffix array: the rank
 // array ISA (group start index of every suffix; final index for resolved ones, tail suffixes
@@ -2290,6 +2324,8 @@ static gtb200_ctx *ctx_create(int device, unsigned numofchars, uint64_t totallen
   if (const char *e8 = getenv("GTB200_FUSED_WIDEN")) c->fused_widen = atoi(e8);
   c->doubling = 1;
   if (const char *e6 = getenv("GTB200_DOUBLING")) c->doubling = atoi(e6);
+  c->extend = 1;
+  if (const char *e7 = getenv("GTB200_EXTEND")) c->extend = atoi(e7);
   c->tile_mode = 1;
   if (const char *e4 = getenv("GTB200_TILE")) c->tile_mode = atoi(e4);
   c->keyed_mode = 1;
@@ -2599,7 +2635,7 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   const size_t o_pos = take(a4), o_head = take(a4), o_hscan = take(a4), o_headpos = take(a4 + 4), o_keep = take(a4);
   const size_t o_kscan = take(a4), o_newgs = take(a4), o_newdep = take(a4), o_hist = take((256ull * nblocks + 1) * 4);
   const size_t o_llvtmp = take(((size_t)A0 + 1) * sizeof(gtb200_largelcp));
-  const size_t o_idx00 = take(a4), o_gs00 = take(a4);
+  const size_t o_idx00 = take(a4), o_gs00 = take(a4), o_ext = take(a4);
   if (ensure_scratch(c, need)) return -1;
   char *S = (char *)c->d_scratch;
   uint32_t *wcnt = (uint32_t *)(S + o_wcnt), *codes = (uint32_t *)(S + o_codes), *sizes = (uint32_t *)(S + o_sizes);
@@ -2614,7 +2650,7 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   uint32_t *headpos = (uint32_t *)(S + o_headpos), *keep = (uint32_t *)(S + o_keep), *kscan = (uint32_t *)(S + o_kscan);
   uint32_t *newgs = (uint32_t *)(S + o_newgs), *newdep = (uint32_t *)(S + o_newdep), *hist = (uint32_t *)(S + o_hist);
   gtb200_largelcp *llvtmp = (gtb200_largelcp *)(S + o_llvtmp);
-  uint32_t *idx00 = (uint32_t *)(S + o_idx00), *gs00 = (uint32_t *)(S + o_gs00);
+  uint32_t *idx00 = (uint32_t *)(S + o_idx00), *gs00 = (uint32_t *)(S + o_gs00), *extmin = (uint32_t *)(S + o_ext);
   out.llv = llvtmp;
 
   // expand the two flagged-bucket bitmaps into the ordered element list
@@ -2655,6 +2691,13 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   while (A > 0 && (rounds < text_limit || posmode_open)) {
     rounds++;
     const unsigned g = grid_for(A, 256);
+    if (!can_double && c->extend && rounds >= 2) {
+      // what survived the first round is mostly repeats: jump over the windows each group shares entirely
+      CK(cudaMemsetAsync(extmin, 0xff, (size_t)A * 4, c->stream));
+      ProfScope ps(c, KC_REFINE, 2);
+      k_fb_extend_count<BITS><<<g, 256, 0, c->stream>>>(T, out.sa, idx[cur], gs[cur], dep[cur], A, 4096u, extmin);
+      k_fb_extend_apply<<<g, 256, 0, c->stream>>>(idx[cur], gs[cur], A, (unsigned)Text<BITS>::W, extmin, dep[cur]);
+    }
     {
       ProfScope ps(c, KC_REFINE, 1);
       k_fb_keys<BITS><<<g, 256, 0, c->stream>>>(T, out.sa, idx[cur], dep[cur], A, keys, posbuf, vals);

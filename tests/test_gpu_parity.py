@@ -226,6 +226,34 @@ def test_refinement_modes(case, doubling, monkeypatch):
     assert got["fallback_suffixes"] > 0
 
 
+@pytest.mark.parametrize("extend", ["1", "0"])
+def test_long_exact_repeat_in_sharded_parts(extend, monkeypatch):
+    """A 100 kb exact duplication (one copy cut by a separator) and a 3 kb unit in 5 tandem copies, sorted in parts:
+    parts cannot use rank doubling, so their text-window rounds jump over the windows a whole group shares
+    (k_fb_extend_count; GTB200_EXTEND=0 is the round-per-28-bases path it replaces).  Same bytes either way; the
+    number of rounds drops from repeat length / 28 to a handful per part."""
+    monkeypatch.setenv("GTB200_EXTEND", extend)
+    rng = np.random.default_rng(5)
+    u = rng.integers(0, 4, size=100_000, dtype=np.uint8)
+    t = rng.integers(0, 4, size=3_000, dtype=np.uint8)
+    enc = np.concatenate([rng.integers(0, 4, size=50_000, dtype=np.uint8), u, rng.integers(0, 4, size=70_000, dtype=np.uint8),
+                          u, np.array([254], dtype=np.uint8), rng.integers(0, 4, size=20_000, dtype=np.uint8),
+                          np.tile(t, 5), np.array([255], dtype=np.uint8), rng.integers(0, 4, size=9_000, dtype=np.uint8)])
+    want = oracle.build(enc, 4)
+    for parts in (2, 5):
+        got = sfx.suffixerator(enc, "dna", parts=parts)
+        _compare(got, want, f"longrepeat/extend{extend}/parts{parts}")
+        if extend == "1":
+            assert got["fallback_rounds"] <= 20 * parts, got["fallback_rounds"]
+        else:
+            assert got["fallback_rounds"] >= 100_000 // 28
+    monkeypatch.setenv("GTB200_DOUBLING", "0")          # a whole-array part on text-window rounds
+    got = sfx.suffixerator(enc, "dna")
+    _compare(got, want, f"longrepeat/extend{extend}/whole")
+    prot = np.concatenate([synth.random_protein(40, seed=8), synth.random_protein(40, seed=8)[:9000], synth.random_protein(30, seed=9)])
+    _compare(sfx.suffixerator(prot, "protein", parts=3), oracle.build(prot, 20), f"longrepeat/extend{extend}/protein")
+
+
 def test_config2_ecoli_size_full_parity():
     """BASELINE.json configs[1]: 4.6 Mbp random DNA, single sequence, seed 42, pl = 8."""
     enc = synth.random_dna(4_600_000, seed=42)
