@@ -1726,6 +1726,121 @@ __global__ void k_fb_extend_apply(const uint32_t *__restrict__ idx, const uint32
   dep[j] += extmin[j - (idx[j] - gs[j])] * W;
 }
 
+// Pivot rounds (GTB200_EXTEND=2): the skip-ahead above moves a group by what ALL members share, which is nothing for
+// a tandem array or a homopolymer run (some member always ends in the next window).  Here every group picks one
+// member as pivot (pseudo-random: largest hash of the position, k_fb_pivot_pick) and every member j walks along the
+// pivot until the first window e_j in which it differs from it, is cut by a special, or the cap is reached; k_j is
+// its key in that window, kp_j the pivot's.  Order inside the group: members below the pivot (k_j < kp_j) by
+// (e_j, k_j) ascending - one that leaves the pivot earlier towards smaller keys is smaller than one that still
+// agrees with it -, then the members equal to the pivot in its last window (still tied, or cut at the same place),
+// then the members above it by e_j DESCENDING, k_j ascending.  The class number c_j encodes exactly that order, so
+// one stable sort on (group, c, k) places every member; neighbours of different classes have
+// lcp = d + e_s*W + common(k_s, kp_s), s = the one that left the pivot first.  A group of m members whose ends
+// are spread out halves in expectation every round.
+#define GTB_PIVOT_MAXWIN 4096u      // c < 2^14 must hold: c <= 2 * GTB_PIVOT_MAXWIN
+
+__global__ void k_fb_pivot_pick(const uint32_t *__restrict__ sa, const uint32_t *__restrict__ idx,
+                                const uint32_t *__restrict__ gs, const uint32_t *__restrict__ dep, uint32_t A, uint32_t salt,
+                                unsigned long long *pvt) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= A || dep[j] == GTB_POSMODE) return;
+  const uint32_t r = idx[j], g = gs[j];
+  uint32_t h = (sa[r] + salt) * 0x9E3779B1u;
+  h ^= h >> 15; h *= 0x85EBCA77u; h ^= h >> 13;
+  atomicMax(&pvt[j - (r - g)], ((unsigned long long)h << 32) | (unsigned long long)(r - g));
+}
+
+template <int BITS>
+__global__ void k_fb_keys_pivot(Text<BITS> T, const uint32_t *__restrict__ sa, const uint32_t *__restrict__ idx,
+                                const uint32_t *__restrict__ gs, const uint32_t *__restrict__ dep, uint32_t A,
+                                const unsigned long long *__restrict__ pvt, uint64_t *keys, uint64_t *kp, uint32_t *ebuf,
+                                uint32_t *cbuf, uint32_t *posbuf, uint32_t *vals) {
+  constexpr int W = Text<BITS>::W;
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= A) return;
+  const uint32_t r = idx[j], g = gs[j], d = dep[j];
+  const uint32_t p = sa[r];
+  posbuf[j] = p;
+  vals[j] = j;
+  if (d == GTB_POSMODE) { keys[j] = p; kp[j] = 0; ebuf[j] = 0; cbuf[j] = 0; return; }
+  const uint32_t q = sa[g + (uint32_t)pvt[j - (r - g)]];
+  uint32_t e = 0;
+  uint64_t ka, kb;
+  for (;;) {
+    ka = make_key<BITS>(T, (uint64_t)p + d + (uint64_t)e * W);
+    kb = make_key<BITS>(T, (uint64_t)q + d + (uint64_t)e * W);
+    if (ka != kb || (ka & 0xff) != 0 || e == GTB_PIVOT_MAXWIN - 1) break;
+    e++;
+  }
+  keys[j] = ka;
+  kp[j] = kb;
+  ebuf[j] = e;
+  cbuf[j] = ka < kb ? e : (ka == kb ? GTB_PIVOT_MAXWIN : 2 * GTB_PIVOT_MAXWIN - e);
+}
+
+__global__ void k_fb_gather_gsc(const uint32_t *__restrict__ vals, const uint32_t *__restrict__ gs,
+                                const uint32_t *__restrict__ cbuf, uint32_t A, uint64_t *keys2) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < A) keys2[j] = ((uint64_t)gs[vals[j]] << 16) | cbuf[vals[j]];
+}
+
+template <int BITS>
+__global__ void k_fb_regroup_pivot(PartOut out, const uint32_t *__restrict__ vals, const uint32_t *__restrict__ idx,
+                                   const uint32_t *__restrict__ gs, const uint32_t *__restrict__ dep,
+                                   const uint64_t *__restrict__ keys, const uint64_t *__restrict__ kp,
+                                   const uint32_t *__restrict__ ebuf, const uint32_t *__restrict__ cbuf,
+                                   const uint32_t *__restrict__ posbuf, uint32_t A, uint32_t *head, uint32_t *newdep) {
+  constexpr int W = Text<BITS>::W;
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long sum = 0;
+  uint32_t mx = 0;
+  if (j < A) {
+    const uint32_t e = vals[j];
+    const uint32_t g = gs[e], d = dep[e];
+    const uint64_t kc = keys[e];
+    const uint32_t r = idx[j];
+    out.sa[r] = posbuf[e];
+    bool hd = true;
+    if (j > 0 && d != GTB_POSMODE) {
+      const uint32_t e0 = vals[j - 1];
+      if (gs[e0] == g) {
+        const uint32_t c0 = cbuf[e0], c1 = cbuf[e];
+        uint32_t l = 0;
+        bool emit = true;
+        if (c0 == c1) {                       // same class: both left the pivot in the same window (or never did)
+          const uint32_t D = d + ebuf[e] * W;
+          const uint64_t k0 = keys[e0];
+          if (k0 != kc) l = D + key_common<BITS>(k0, kc);
+          else if ((kc & 0xff) != 0) { l = D + (W - (uint32_t)(kc & 0xff)); hd = false; }   // cut at the same place: by position
+          else { hd = false; emit = false; }  // still tied on real symbols
+        } else {
+          // the one that left the pivot first (the other still agreed with the pivot in that window); with equal
+          // windows one of the two is a member of the pivot's own class and the other one left
+          const uint32_t w0 = ebuf[e0], w1 = ebuf[e];
+          const uint32_t s = w0 < w1 ? e0 : (w1 < w0 ? e : (c0 == GTB_PIVOT_MAXWIN ? e : e0));
+          l = d + ebuf[s] * W + key_common<BITS>(keys[s], kp[s]);
+        }
+        if (emit) {
+          out.lcp[r] = (uint8_t)(l < 255 ? l : 255);
+          if (l >= 255) emit_large(out, r, l);
+          sum = l; mx = l;
+        }
+      }
+    }
+    head[j] = hd ? 1u : 0u;
+    newdep[j] = (d == GTB_POSMODE) ? GTB_POSMODE : ((kc & 0xff) ? GTB_POSMODE : d + (ebuf[e] + 1) * W);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sum += __shfl_xor_sync(GTB_FULL, sum, o);
+    mx = max(mx, __shfl_xor_sync(GTB_FULL, mx, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (sum) atomicAdd(&out.stats->lcpsum, sum);
+    if (mx) atomicMax(&out.stats->maxdepth, mx);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Prefix doubling (Larsson-Sadakane style) for parts that cover the whole suffix array: the rank
 // array ISA (group start index of every suffix; final index for resolved ones, tail suffixes
@@ -2636,6 +2751,7 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   const size_t o_kscan = take(a4), o_newgs = take(a4), o_newdep = take(a4), o_hist = take((256ull * nblocks + 1) * 4);
   const size_t o_llvtmp = take(((size_t)A0 + 1) * sizeof(gtb200_largelcp));
   const size_t o_idx00 = take(a4), o_gs00 = take(a4), o_ext = take(a4);
+  const size_t o_pvt = take(a8), o_kpv = take(a8), o_ebuf = take(a4), o_cbuf = take(a4);
   if (ensure_scratch(c, need)) return -1;
   char *S = (char *)c->d_scratch;
   uint32_t *wcnt = (uint32_t *)(S + o_wcnt), *codes = (uint32_t *)(S + o_codes), *sizes = (uint32_t *)(S + o_sizes);
@@ -2651,6 +2767,9 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   uint32_t *newgs = (uint32_t *)(S + o_newgs), *newdep = (uint32_t *)(S + o_newdep), *hist = (uint32_t *)(S + o_hist);
   gtb200_largelcp *llvtmp = (gtb200_largelcp *)(S + o_llvtmp);
   uint32_t *idx00 = (uint32_t *)(S + o_idx00), *gs00 = (uint32_t *)(S + o_gs00), *extmin = (uint32_t *)(S + o_ext);
+  unsigned long long *pvt = (unsigned long long *)(S + o_pvt);
+  uint64_t *kpv = (uint64_t *)(S + o_kpv);
+  uint32_t *ebuf = (uint32_t *)(S + o_ebuf), *cbuf = (uint32_t *)(S + o_cbuf);
   out.llv = llvtmp;
 
   // expand the two flagged-bucket bitmaps into the ordered element list
@@ -2691,14 +2810,22 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
   while (A > 0 && (rounds < text_limit || posmode_open)) {
     rounds++;
     const unsigned g = grid_for(A, 256);
-    if (!can_double && c->extend && rounds >= 2) {
-      // what survived the first round is mostly repeats: jump over the windows each group shares entirely
-      CK(cudaMemsetAsync(extmin, 0xff, (size_t)A * 4, c->stream));
+    // what survived the first round is mostly repeats (c->extend: 1 = groups jump over the windows all members share,
+    // 2 = pivot rounds, see k_fb_keys_pivot)
+    const bool pivot = !can_double && c->extend == 2 && rounds >= 2;
+    if (pivot) {
+      CK(cudaMemsetAsync(pvt, 0, (size_t)A * 8, c->stream));
       ProfScope ps(c, KC_REFINE, 2);
-      k_fb_extend_count<BITS><<<g, 256, 0, c->stream>>>(T, out.sa, idx[cur], gs[cur], dep[cur], A, 4096u, extmin);
-      k_fb_extend_apply<<<g, 256, 0, c->stream>>>(idx[cur], gs[cur], A, (unsigned)Text<BITS>::W, extmin, dep[cur]);
-    }
-    {
+      k_fb_pivot_pick<<<g, 256, 0, c->stream>>>(out.sa, idx[cur], gs[cur], dep[cur], A, (uint32_t)rounds * 0x632BE5ABu, pvt);
+      k_fb_keys_pivot<BITS><<<g, 256, 0, c->stream>>>(T, out.sa, idx[cur], gs[cur], dep[cur], A, pvt, keys, kpv, ebuf, cbuf,
+                                                       posbuf, vals);
+    } else {
+      if (!can_double && c->extend == 1 && rounds >= 2) {
+        CK(cudaMemsetAsync(extmin, 0xff, (size_t)A * 4, c->stream));
+        ProfScope ps(c, KC_REFINE, 2);
+        k_fb_extend_count<BITS><<<g, 256, 0, c->stream>>>(T, out.sa, idx[cur], gs[cur], dep[cur], A, 4096u, extmin);
+        k_fb_extend_apply<<<g, 256, 0, c->stream>>>(idx[cur], gs[cur], A, (unsigned)Text<BITS>::W, extmin, dep[cur]);
+      }
       ProfScope ps(c, KC_REFINE, 1);
       k_fb_keys<BITS><<<g, 256, 0, c->stream>>>(T, out.sa, idx[cur], dep[cur], A, keys, posbuf, vals);
     }
@@ -2709,7 +2836,8 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
     uint64_t *k2 = (ko == kA) ? kB : kA;   // free key buffer
     {
       ProfScope ps(c, KC_REFINE, 1);
-      k_fb_gather_gs<<<g, 256, 0, c->stream>>>(vo, gs[cur], A, k2);
+      if (pivot) k_fb_gather_gsc<<<g, 256, 0, c->stream>>>(vo, gs[cur], cbuf, A, k2);
+      else k_fb_gather_gs<<<g, 256, 0, c->stream>>>(vo, gs[cur], A, k2);
     }
     // copy vo into vals so that both ping-pong value buffers are free again
     CK(cudaMemcpyAsync(vals, vo, (size_t)A * 4, cudaMemcpyDeviceToDevice, c->stream));
@@ -2719,10 +2847,14 @@ static int refine_impl(gtb200_ctx *c, const PartOut &out_in, uint64_t mincode, u
     // device_radix_sort never writes to its input on the first pass and alternates afterwards.
     const uint64_t *ko2;
     const uint32_t *vo2;
-    if (device_radix_sort(c, k2, vals, k3a, vA, k2, vB, hist, A, 0, gsbits, &ko2, &vo2)) return -1;
+    if (device_radix_sort(c, k2, vals, k3a, vA, k2, vB, hist, A, 0, pivot ? 16 + gsbits : gsbits, &ko2, &vo2)) return -1;
     {
       ProfScope ps(c, KC_REFINE, 1);
-      k_fb_regroup<BITS><<<g, 256, 0, c->stream>>>(out, vo2, idx[cur], gs[cur], dep[cur], keys, posbuf, A, head, newdep);
+      if (pivot)
+        k_fb_regroup_pivot<BITS><<<g, 256, 0, c->stream>>>(out, vo2, idx[cur], gs[cur], dep[cur], keys, kpv, ebuf, cbuf, posbuf, A,
+                                                            head, newdep);
+      else
+        k_fb_regroup<BITS><<<g, 256, 0, c->stream>>>(out, vo2, idx[cur], gs[cur], dep[cur], keys, posbuf, A, head, newdep);
     }
     if (device_scan(c, head, hscan, A, 0, &c->d_stats->scan_total, KC_REFINE)) return -1;
     {

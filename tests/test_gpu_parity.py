@@ -226,12 +226,13 @@ def test_refinement_modes(case, doubling, monkeypatch):
     assert got["fallback_suffixes"] > 0
 
 
-@pytest.mark.parametrize("extend", ["1", "0"])
+@pytest.mark.parametrize("extend", ["2", "1", "0"])
 def test_long_exact_repeat_in_sharded_parts(extend, monkeypatch):
     """A 100 kb exact duplication (one copy cut by a separator) and a 3 kb unit in 5 tandem copies, sorted in parts:
-    parts cannot use rank doubling, so their text-window rounds jump over the windows a whole group shares
-    (k_fb_extend_count; GTB200_EXTEND=0 is the round-per-28-bases path it replaces).  Same bytes either way; the
-    number of rounds drops from repeat length / 28 to a handful per part."""
+    parts cannot use rank doubling, so their text-window rounds either jump over the windows a whole group shares
+    (GTB200_EXTEND=1, k_fb_extend_count) or order every member by where it leaves a pivot member of its group
+    (GTB200_EXTEND=2, k_fb_keys_pivot); GTB200_EXTEND=0 is the round-per-28-bases path they replace.  Same bytes every
+    way; the number of rounds drops from repeat length / 28 to a handful per part."""
     monkeypatch.setenv("GTB200_EXTEND", extend)
     rng = np.random.default_rng(5)
     u = rng.integers(0, 4, size=100_000, dtype=np.uint8)
@@ -243,15 +244,30 @@ def test_long_exact_repeat_in_sharded_parts(extend, monkeypatch):
     for parts in (2, 5):
         got = sfx.suffixerator(enc, "dna", parts=parts)
         _compare(got, want, f"longrepeat/extend{extend}/parts{parts}")
-        if extend == "1":
+        if extend != "0":
             assert got["fallback_rounds"] <= 20 * parts, got["fallback_rounds"]
         else:
             assert got["fallback_rounds"] >= 100_000 // 28
     monkeypatch.setenv("GTB200_DOUBLING", "0")          # a whole-array part on text-window rounds
     got = sfx.suffixerator(enc, "dna")
     _compare(got, want, f"longrepeat/extend{extend}/whole")
+    monkeypatch.delenv("GTB200_DOUBLING")
     prot = np.concatenate([synth.random_protein(40, seed=8), synth.random_protein(40, seed=8)[:9000], synth.random_protein(30, seed=9)])
     _compare(sfx.suffixerator(prot, "protein", parts=3), oracle.build(prot, 20), f"longrepeat/extend{extend}/protein")
+    # members of one group that end at different depths: a homopolymer run, a 7-mer in 3,000 tandem copies, a
+    # run cut by a wildcard.  Only the pivot rounds bring these below run length / 28 rounds.
+    runs = np.concatenate([rng.integers(0, 4, size=30_000, dtype=np.uint8), np.full(20_000, 3, dtype=np.uint8),
+                           rng.integers(0, 4, size=30_000, dtype=np.uint8), np.tile(rng.integers(0, 4, size=7, dtype=np.uint8), 3000),
+                           np.array([2, 255], dtype=np.uint8), np.full(5_000, 0, dtype=np.uint8), np.array([255], dtype=np.uint8),
+                           rng.integers(0, 4, size=10_000, dtype=np.uint8)])
+    want = oracle.build(runs, 4)
+    for parts in (1, 3):
+        if parts == 1:
+            monkeypatch.setenv("GTB200_DOUBLING", "0")
+        got = sfx.suffixerator(runs, "dna", parts=parts)
+        _compare(got, want, f"runs/extend{extend}/parts{parts}")
+        if extend == "2":
+            assert got["fallback_rounds"] <= 80 * parts, got["fallback_rounds"]
 
 
 def test_config2_ecoli_size_full_parity():
