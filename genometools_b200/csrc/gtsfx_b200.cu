@@ -132,7 +132,7 @@ struct gtb200_ctx {
   uint32_t *d_isa;           // rank array of the prefix-doubling refinement (n+1 entries)
   uint64_t cap_isa;
   int doubling;              // 1 = prefix doubling when the part is the whole array (GTB200_DOUBLING, testing knob)
-  int extend;                // 1 = text-window rounds skip the windows a whole group shares (GTB200_EXTEND, testing knob)
+  int extend;                // text-window rounds of sharded parts: 2 = pivot rounds, 1 = skip shared windows, 0 = plain (GTB200_EXTEND)
   uint32_t *d_bins;          // bin cursors / starts / chunk table of the tile path
   uint64_t cap_recB, cap_bins;
   // per part
@@ -2439,7 +2439,7 @@ static gtb200_ctx *ctx_create(int device, unsigned numofchars, uint64_t totallen
   if (const char *e8 = getenv("GTB200_FUSED_WIDEN")) c->fused_widen = atoi(e8);
   c->doubling = 1;
   if (const char *e6 = getenv("GTB200_DOUBLING")) c->doubling = atoi(e6);
-  c->extend = 1;
+  c->extend = 2;
   if (const char *e7 = getenv("GTB200_EXTEND")) c->extend = atoi(e7);
   c->tile_mode = 1;
   if (const char *e4 = getenv("GTB200_TILE")) c->tile_mode = atoi(e4);
